@@ -1,0 +1,348 @@
+#!/usr/bin/env python
+"""Benchmark of the split-NN hot path (BASELINE.json metric: split-NN train samples/s; SISA
+server-epoch ms alongside; reference CPU path timed on the same box).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one batch (B=16, the reference's default) through the whole vanilla split step:
+Alice conv forward -> Bob forward / cross-entropy / backward / SGD-momentum (per-Alice state)
+-> cut-layer gradient -> Alice conv backward + SGD-momentum.  Workload at N=1 is
+BASELINE.json configs[1]: `--vanilla`, world_size=5 (1 Bob + 4 Alices taking turns), all on one
+B200.  Under torchrun (N>1): Bob on rank 0, the 4 Alices spread over ranks 1..N-1, activations and
+cut-layer gradients over NCCL send/recv; the protocol is strictly sequential, so
+total work is fixed: scaling = "strong".
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+B = 16
+D0 = 5408
+DIMS = [5408, 5000, 1000, 100]
+N_ALICES = 4
+TURN = 64                     # steps an Alice trains before the next one takes over
+P_BOB = sum(DIMS[i] * DIMS[i + 1] + DIMS[i + 1] for i in range(3))        # 32,146,100
+P_FC1 = DIMS[0] * DIMS[1]
+L2_MB = 126
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """SM clock + throttle reasons sampled DURING the timed region (NVML, 20 ms period)."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mask = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def __enter__(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ----------------------------------------------------------------------------------- reference arm
+def run_reference(args):
+    """`--impl reference`: the reference's CPU path on the box's host cores.  /root/reference cannot
+    travel to the GPU box and is not pip-installable (no setup.py), so this times the oracle's
+    torch-CPU port of the same step (oracle/cpu_baseline.py; no RPC -> faster than the original)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    from oracle import cpu_baseline as cb
+    w = cb.VanillaCPU(n_alices=N_ALICES, batch=B)
+    dt = cb.time_steps(w, args.steps, args.warmup)
+    value = args.steps * B / dt
+    line = {
+        "impl": "reference", "metric": "split_nn_train_samples_per_sec", "value": value, "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": "port",
+                         "sample": f"{args.steps} vanilla split steps of B={B} on torch-CPU, single process, no RPC"},
+        "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "host": {"cpu_count": os.cpu_count(), "torch_threads": torch.get_num_threads()},
+    }
+    print(json.dumps(line))
+
+
+def workload_config(n_gpus):
+    return {"workload": "--vanilla split NN, world_size=5 (1 Bob + 4 Alices round-robin), batch 16, "
+                        "model1_sisa + model2_sisa 5408-5000-1000-100, SGD momentum 0.9 per Alice, lr 1e-3",
+            "global_batch": B, "parallelism": "single GPU" if n_gpus == 1 else f"Bob on rank 0 + Alices on ranks 1..{n_gpus - 1} (NCCL send/recv)",
+            "l2": f"per-step working set {20 * P_BOB / 1e6:.0f} MB (weights + momentum) > {L2_MB} MB L2: no flush needed",
+            "dropout": "in-kernel Philox (perf mode)"}
+
+
+# ----------------------------------------------------------------------------------- our arm, N = 1
+def make_world(torch, device, lr=1e-3):
+    """Bob + 4 Alices through the public classes' engines, synthetic MNIST-shaped data in HBM."""
+    from splitlearning_b200 import engine as E
+    from splitlearning_b200 import models as M
+    torch.manual_seed(0)
+    bob_model = M.model2_sisa(device)
+    bob = bob_model.make_engine(optimizer=E.SN_OPT_SGD_MOMENTUM, lr=lr, momentum=0.9, n_opt_slots=N_ALICES, max_batch=B)
+    alices = []
+    for _ in range(N_ALICES):
+        m = M.model1_sisa(device)
+        alices.append((m, m.make_engine(optimizer=E.SN_OPT_SGD_MOMENTUM, lr=lr, momentum=0.9, max_batch=B)))
+    return bob_model, bob, alices
+
+
+def synthetic_batches(torch, n, device=None, pin=False):
+    g = torch.Generator().manual_seed(1234)
+    x = torch.randint(0, 256, (n, B, 1, 28, 28), generator=g).float() * (torch.rand(n, B, 1, 28, 28, generator=g) < 0.4)
+    y = torch.randint(0, 10, (n, B), generator=g)
+    if pin:
+        return x.pin_memory(), y.pin_memory()
+    return x.to(device), y.to(device)
+
+
+def run_ours_single(args):
+    import torch
+    from splitlearning_b200 import _lib
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    lib = _lib.load()
+    bob_model, bob, alices = make_world(torch, dev)
+    nb = 256
+    xs, ys = synthetic_batches(torch, nb, dev)
+    seed_ctr = [0]
+
+    def hand_off(src, dst):      # give_weights / load_state_dict between consecutive Alices
+        dst[0].load_state_dict(src[0].state_dict())
+
+    def step(i, x, y, loss_out):
+        k = (i // TURN) % N_ALICES
+        if i % TURN == 0 and i > 0:
+            hand_off(alices[(k - 1) % N_ALICES], alices[k])
+        eng = alices[k][1]
+        act = eng.forward(x)
+        seed_ctr[0] += 1
+        _, cut, _ = bob.train_step(act, y, slot=k, masks=None, seed=1, offset=seed_ctr[0], want_cut_grad=True,
+                                   loss_out=loss_out)
+        eng.backward_update(x, cut)
+
+    loss_dev = torch.zeros((), device=dev)
+    K, W = args.steps, args.warmup
+    # ---- device-resident timing ("value")
+    for i in range(W):
+        step(i, xs[i % nb], ys[i % nb], loss_dev)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = lib.sn_launch_count()
+    with ClockSampler(0) as clk:
+        torch.cuda.synchronize()
+        e0.record()
+        for i in range(K):
+            step(W + i, xs[(W + i) % nb], ys[(W + i) % nb], loss_dev)
+        e1.record()
+        torch.cuda.synchronize()
+    launches = lib.sn_launch_count() - l0
+    ms = e0.elapsed_time(e1)
+    value = K * B / (ms * 1e-3)
+    final_loss = float(loss_dev.item())
+
+    # ---- end-to-end through the same calls with HOST buffers ("e2e")
+    hx, hy = synthetic_batches(torch, nb, pin=True)
+    dx = torch.empty(B, 1, 28, 28, device=dev)
+    dy = torch.empty(B, dtype=torch.int64, device=dev)
+    hloss = torch.zeros(K + W, dtype=torch.float32).pin_memory()
+    dl = torch.zeros((), device=dev)
+
+    def e2e_step(i):
+        dx.copy_(hx[i % nb], non_blocking=True)
+        dy.copy_(hy[i % nb], non_blocking=True)
+        step(i, dx, dy, dl)
+        hloss[i].copy_(dl, non_blocking=True)
+
+    for i in range(W):
+        e2e_step(i)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for i in range(K):
+        e2e_step(W + i)
+    f1.record()
+    torch.cuda.synchronize()
+    e2e_wall = time.perf_counter() - t0
+    e2e_ms = max(f0.elapsed_time(f1), e2e_wall * 1e3)
+    e2e_value = K * B / (e2e_ms * 1e-3)
+
+    # ---- per-kernel roofline pass (event-bracketed launches; separate from the headline timing)
+    peak, peak_src = measured_peak()
+    bob.profile(True)
+    torch.cuda.synchronize()
+    PK = min(K, 200)
+    for i in range(PK):
+        step(i, xs[i % nb], ys[i % nb], loss_dev)
+    torch.cuda.synchronize()
+    t_bwd1, n_bwd1 = bob.profile_read(1, 0)
+    t_fwd1, n_fwd1 = bob.profile_read(0, 0)
+    kern = {}
+    for kind, name in ((0, "fwd"), (1, "bwd_update")):
+        for l in range(3):
+            t, n = bob.profile_read(kind, l)
+            if n:
+                kern[f"{name}_fc{l + 1}_us"] = round(1e3 * t / n, 2)
+    bob.profile(False)
+    dom_bytes = 16.0 * P_FC1 + 4.0 * B * (DIMS[1] + 2 * DIMS[0])     # W r/w + momentum r/w (+ dZ, A in, dA out)
+    dom_s = (t_bwd1 / max(n_bwd1, 1)) * 1e-3
+    achieved = dom_bytes / dom_s / 1e9
+    step_bytes = 16.0 * P_BOB + 8.0 * B * D0
+    roofline = {"bound": "hbm", "kernel": "bwd_update_kernel<SGD,dA> fc1 (5000x5408): dW+dX+momentum update in one traversal",
+                "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                "traffic": None, "peak_source": peak_src, "bytes_per_launch": dom_bytes,
+                "us_per_launch": round(dom_s * 1e6, 2), "kernel_us": kern,
+                "whole_step": {"algorithmic_bytes": step_bytes, "formula": "16*P + 8*B*d0 (SURVEY 8d)",
+                               "achieved": round(step_bytes / (ms * 1e-3 / K) / 1e9, 1),
+                               "frac": round(step_bytes / (ms * 1e-3 / K) / 1e9 / peak, 4)}}
+
+    # ---- SISA server epoch (BASELINE.json's second number), same process
+    sisa = run_sisa_epoch(torch, dev, peak)
+
+    # ---- CPU baseline on the host cores (bounded sample)
+    from oracle import cpu_baseline as cb
+    v, n, dt, thr = cb.bounded(cb.VanillaCPU, budget_s=12.0, n_alices=N_ALICES, batch=B)
+    cpu = {"value": round(v, 1), "unit": "samples/s", "cores": thr, "kind": "port",
+           "sample": f"{n} vanilla split steps of B={B} ({dt:.1f} s) on torch-CPU, single process, no RPC"}
+    v2, n2, dt2, _ = cb.bounded(cb.SisaServerCPU, budget_s=8.0, batch=B)
+    sisa["cpu_baseline_ms_per_step"] = round(1e3 * B / v2, 2)
+    sisa["cpu_sample"] = f"{n2} SISA server steps of B={B} ({dt2:.1f} s), Adam wd 1e-5"
+
+    line = {
+        "metric": "split_nn_train_samples_per_sec", "value": round(value, 1), "unit": "samples/s", "n_gpus": 1,
+        "steps": K, "warmup": W, "ms_per_step": round(ms / K, 5), "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(1),
+        "clocks": clk.summary(), "gpu_launches": int(launches),
+        "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "h2d_bytes_per_step": B * 784 * 4 + B * 8,
+                "d2h_bytes_per_step": 4, "ms_per_step": round(e2e_ms / K, 5)},
+        "roofline": roofline, "cpu_baseline": cpu, "sisa": sisa, "final_loss": final_loss,
+    }
+    print(json.dumps(line))
+
+
+def run_sisa_epoch(torch, dev, peak):
+    """SISA server-only epoch over frozen activations cached in HBM (BASELINE.json configs[2]:
+    ws=5, 56,000 train samples -> 3,500 batches of 16), Adam wd 1e-5, one sn_bob_server_epoch per
+    Alice per epoch.  Reports epoch ms (steady state) and the cache-stream / weight-stream rates."""
+    from splitlearning_b200 import engine as E
+    from splitlearning_b200 import models as M
+    torch.manual_seed(1)
+    model = M.model2_sisa(dev)
+    bob = model.make_engine(optimizer=E.SN_OPT_ADAM, lr=1e-3, weight_decay=1e-5, n_opt_slots=1, max_batch=B)
+    amodel = M.model1_sisa(dev)
+    alice = amodel.make_engine(optimizer=E.SN_OPT_NONE, max_batch=B)
+    sizes = [16271 * 8 // 10, 21685 * 8 // 10, 15329 * 8 // 10, 16715 * 8 // 10]      # LDA K=4 split, 80 % train
+    caches = []
+    g = torch.Generator().manual_seed(5)
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for n in sizes:
+        x = (torch.randint(0, 256, (n, 1, 28, 28), generator=g).float() * (torch.rand(n, 1, 28, 28, generator=g) < 0.4)).to(dev)
+        y = torch.randint(0, 10, (n,), generator=g).to(dev)
+        acts = alice.forward(x)                      # frozen Alice, whole shard in one launch
+        caches.append((acts, y, list(range(0, n, B)) + [n]))
+    t1.record()
+    torch.cuda.synchronize()
+    n_steps = sum(len(c[2]) - 1 for c in caches)
+    n_samples = sum(sizes)
+
+    def epoch(seed_off):
+        off = seed_off
+        for acts, y, offs in caches:
+            bob.server_epoch(acts, y, offs, slot=0, masks=None, seed=7, offset=off)
+            off += len(offs)
+    epoch(0)                                          # warm-up epoch (also epoch 0 of the reference flow)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    epoch(10000)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    step_bytes = 24.0 * P_BOB + 4.0 * B * D0
+    return {"server_epoch_ms": round(ms, 2), "steps": n_steps, "samples": n_samples,
+            "us_per_step": round(1e3 * ms / n_steps, 2), "samples_per_sec": round(n_samples / (ms * 1e-3), 1),
+            "cache_bytes": n_samples * D0 * 4,
+            "roofline": {"bound": "hbm", "algorithmic_bytes_per_step": step_bytes, "formula": "24*P + 4*B*d0 (SURVEY 8d)",
+                         "achieved": round(step_bytes * n_steps / (ms * 1e-3) / 1e9, 1), "peak": peak, "unit": "GB/s",
+                         "frac": round(step_bytes * n_steps / (ms * 1e-3) / 1e9 / peak, 4)}}
+
+
+# ----------------------------------------------------------------------------------- our arm, N > 1
+def run_ours_multi(args):
+    from splitlearning_b200 import spmd
+    spmd.bench_vanilla(args, B, N_ALICES, TURN, workload_config(args.gpus), measured_peak())
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=100)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus > 1 or world > 1:
+        return run_ours_multi(args)
+    return run_ours_single(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,189 @@
+/* libsplitnn — C ABI of the B200-native split-NN hot path.
+ *
+ * The reference (OniReimu/SplitLearning) has no FFI: its boundary is a Python surface whose
+ * arithmetic is delegated to PyTorch-CPU operators.  Each entry point below replaces the
+ * operator calls at the cited reference lines (paths relative to the reference repo root).
+ * The Python host mirror (splitlearning_b200/{models,data_entities*}.py) binds these through
+ * ctypes (splitlearning_b200/_lib.py); INTEGRATION.md shows the stub a maintainer would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every `const float*`/`float*` is a DEVICE pointer unless
+ *     the parameter is documented as host memory.  The library never frees caller memory.
+ *   - every call returns 0 on success, non-zero on error; `sn_last_error()` (thread-local) then
+ *     holds a message.  Nothing falls back to the CPU.
+ *   - calls that take `stream` only enqueue work on that cudaStream_t (pass it as void*;
+ *     NULL = legacy default stream) and return without synchronising.
+ *   - a handle lives on one device; calls switch to that device themselves.
+ *   - weights are [out,in] row-major fp32, exactly PyTorch's nn.Linear / nn.Conv2d layout, and
+ *     are OWNED BY THE CALLER (bound by pointer, updated in place); optimizer state,
+ *     activations kept for the backward pass and split-K scratch are owned by the handle.
+ */
+#ifndef SPLITNN_H
+#define SPLITNN_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sn_bob sn_bob;     /* a server-side MLP (also used for Alice's U-shape tail) */
+typedef struct sn_alice sn_alice; /* a client-side conv block */
+
+enum { SN_OPT_NONE = 0, SN_OPT_SGD_MOMENTUM = 1, SN_OPT_ADAM = 2 };
+
+int sn_version(void);
+const char* sn_last_error(void);
+/* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
+uint64_t sn_launch_count(void);
+
+/* ------------------------------------------------------------------ stateless operators */
+
+/* conv3x3(1->32)+bias -> ReLU -> maxpool2x2 -> flatten.  x [B,1,28,28] -> act [B,5408]
+ * (index c*169+h*13+w).  Replaces model1_sisa.forward / model1.forward, models.py:27-30,11-14. */
+int sn_conv_pool_forward(const float* x, const float* w, const float* b, int B, float* act,
+                         void* stream);
+
+/* Weight/bias gradient of the block above given dL/dact [B,5408]; no input gradient (the input
+ * is data).  dw [32*9], db [32].  `scratch` >= sn_conv_pool_backward_scratch_bytes(B) bytes.
+ * Replaces autograd's conv/relu/pool backward under loss.backward(),
+ * data_entities_vanilla_sisa.py:68 and dist_autograd.backward, data_entities_vanilla.py:231. */
+size_t sn_conv_pool_backward_scratch_bytes(int B);
+int sn_conv_pool_backward(const float* x, const float* w, const float* b, const float* dact, int B,
+                          float* dw, float* db, void* scratch, void* stream);
+
+/* y[B,N] = act(x[B,K] . W[N,K]^T + bias) (* keep_mask * mask_scale).  relu: 0/1.  keep_mask
+ * (nullable) is [B,N] bytes, 1 = keep.  Split-K partial sums go through `scratch`
+ * (>= sn_linear_forward_scratch_bytes(B,K,N) bytes).  Replaces F.linear/F.relu/F.dropout in
+ * model2_sisa.forward, models.py:55-63 (and model2 :39-44, model3 :92-94). */
+size_t sn_linear_forward_scratch_bytes(int B, int K, int N);
+int sn_linear_forward(const float* x, const float* W, const float* bias, int B, int K, int N,
+                      int relu, const uint8_t* keep_mask, float mask_scale, float* y,
+                      void* scratch, size_t scratch_bytes, void* stream);
+
+/* Mean cross-entropy over B rows of C logits with int64 labels, and its gradient
+ * (softmax - onehot)/B.  loss: device scalar.  dlogits nullable.  Replaces
+ * nn.CrossEntropyLoss, data_entities_vanilla.py:224,230; data_entities_vanilla_sisa.py:65,308;
+ * data_entities.py:76. */
+int sn_cross_entropy(const float* logits, const int64_t* labels, int B, int C, float* loss,
+                     float* dlogits, void* stream);
+
+/* counters6 += {correct, total, correct&label==omit, label==omit, correct&label!=omit,
+ * label!=omit} with prediction = first argmax over C.  counters6: device int64[6].  Replaces
+ * the torch.max/compare/sum block of alice.eval_breakdown, data_entities_vanilla.py:181-194
+ * (and alice.eval :93-95 via counters 0,1). */
+int sn_eval_counts(const float* logits, const int64_t* labels, int B, int C, int64_t omit_label,
+                   int64_t* counters6, void* stream);
+
+/* ------------------------------------------------------------------ Bob: the server MLP */
+
+/* dims[0..n_layers] = layer widths, e.g. {5408,5000,1000,100} (model2_sisa, models.py:46-53),
+ * {5408,1000,100} with relu_last=1 (model2, :33-37), {5408K,5000,1000,100K} (concat, :66-73),
+ * {100,10} (model3, :87-90).  Hidden layers get ReLU and, when dropout_p>0 and the call is in
+ * train mode, inverted dropout.  W[l] [dims[l+1],dims[l]] and b[l] are caller-owned device
+ * buffers updated in place.  n_opt_slots independent optimizer states are kept: the reference
+ * builds one DistributedOptimizer per Alice over Bob's parameters
+ * (data_entities_vanilla.py:37-42), so Bob holds one momentum set per Alice.
+ * optimizer: SN_OPT_SGD_MOMENTUM (lr, momentum; F.sgd) or SN_OPT_ADAM (lr, beta1, beta2, eps,
+ * coupled-L2 weight_decay; _single_tensor_adam).  Hyper-parameters are doubles because torch keeps
+ * them as python floats and derives Adam's bias corrections in double before rounding to fp32. */
+int sn_bob_create(sn_bob** out, int device, const int* dims, int n_layers, int relu_last,
+                  double dropout_p, int optimizer, double lr, double momentum, double beta1,
+                  double beta2, double eps, double weight_decay, int n_opt_slots, int max_batch,
+                  float* const* W, float* const* b);
+int sn_bob_destroy(sn_bob* h);
+
+/* Fresh optimizer state in `slot` (zeroed moments, step 0): alice.unlearn builds a new
+ * optimizer, data_entities_vanilla.py:132-137; data_entities_vanilla_sisa.py:145. */
+int sn_bob_reset_opt_slot(sn_bob* h, int slot, void* stream);
+/* Optimizer-state access for checkpointing / teacher-forced tests.  which: 0 = momentum buffer
+ * or Adam exp_avg, 1 = Adam exp_avg_sq.  param: 2*l = W[l], 2*l+1 = b[l]. */
+int sn_bob_opt_state(sn_bob* h, int slot, int which, int param, float** dptr, size_t* count);
+int sn_bob_get_opt_step(sn_bob* h, int slot, int64_t* step);
+int sn_bob_set_opt_step(sn_bob* h, int slot, int64_t step);
+int sn_bob_set_lr(sn_bob* h, double lr);
+/* Treat the last layer's dims[L] outputs as `heads` independent classifiers of dims[L]/heads
+ * classes each: the loss becomes the mean CE over B*heads rows and `labels` is [B,heads].
+ * heads=1 (default) is the reference's single CE.  Used by the --concat server, whose fc3 emits
+ * 100 logits per client (models.py:73); the reference's own concat loop crashes before any loss
+ * is computed (data_entities_sisa_concat.py:270-276), so these semantics are defined here. */
+int sn_bob_set_ce_heads(sn_bob* h, int heads);
+/* Measurement aid (no counterpart in the reference): while enabled, every launch of the two
+ * weight-streaming kernels is bracketed by CUDA events on the launching stream.
+ * sn_bob_profile_read sums them for kind 0 = forward (layer l), 1 = backward+update (layer l),
+ * synchronising on the recorded events.  Enabling or disabling clears earlier records. */
+int sn_bob_profile(sn_bob* h, int enable);
+int sn_bob_profile_read(sn_bob* h, int kind, int layer, double* total_ms, int* launches);
+
+/* One training batch on Bob: forward (train mode), mean CE over the last layer's logits,
+ * backward, optimizer update of `slot`; cut_grad [B,dims[0]] = dL/dact (nullable: SISA's input
+ * is detached).  drop_masks: nullable host array of (n_layers-1) device pointers to [B,dims[l+1]]
+ * keep-bytes (teacher-forced / torch-CPU-stream parity mode); when NULL masks come from Philox
+ * keyed by (seed, offset).  logits_out [B,dims[L]] nullable.  loss_out: device scalar, nullable.
+ * Replaces bob.train_and_backward + the Bob half of dist_optimizer.step,
+ * data_entities_vanilla.py:226-232,76 ; and the batch body of SISA's server loop,
+ * data_entities_vanilla_sisa.py:305-313. */
+int sn_bob_train_step(sn_bob* h, int slot, const float* act, const int64_t* labels, int B,
+                      const uint8_t* const* drop_masks, uint64_t seed, uint64_t offset,
+                      float* cut_grad, float* logits_out, float* loss_out, void* stream);
+
+/* Forward only; out [B,dims[L]].  train_mode=1 applies dropout (the reference's --vanilla never
+ * calls .eval(), so bob.inference is stochastic there) and keeps activations for a following
+ * sn_bob_backward_update.  Replaces bob.inference, data_entities_vanilla.py:234-235;
+ * data_entities.py:166-167. */
+int sn_bob_forward(sn_bob* h, const float* act, int B, int train_mode,
+                   const uint8_t* const* drop_masks, uint64_t seed, uint64_t offset, float* out,
+                   void* stream);
+
+/* Backward + update from dL/dout [B,dims[L]] of the preceding train-mode sn_bob_forward;
+ * cut_grad nullable.  Replaces Bob's share of dist_autograd.backward + dist_optimizer.step in
+ * the U-shape step, data_entities.py:79,81. */
+int sn_bob_backward_update(sn_bob* h, int slot, const float* act, const float* dout, int B,
+                           float* cut_grad, void* stream);
+
+/* SISA server epoch: for i in [0,n_batches): one sn_bob_train_step (no cut_grad) on rows
+ * [batch_offsets[i], batch_offsets[i+1]) of the HBM-resident cache [rows,dims[0]] / labels[rows].
+ * batch_offsets: HOST int64[n_batches+1].  drop_masks: nullable host array of device pointers to
+ * [rows,dims[l+1]] keep-bytes.  loss_per_step: device float[n_batches], nullable.  Replaces the
+ * inner loop of bob.train_and_backward, data_entities_vanilla_sisa.py:304-313. */
+int sn_bob_server_epoch(sn_bob* h, int slot, const float* cache, const int64_t* labels,
+                        const int64_t* batch_offsets, int n_batches,
+                        const uint8_t* const* drop_masks, uint64_t seed, uint64_t offset,
+                        float* loss_per_step, void* stream);
+
+/* ------------------------------------------------------------------ Alice: the client conv block */
+
+/* w [32,1,3,3], b [32] caller-owned, updated in place.  optimizer as for Bob (Alice's half of
+ * the per-Alice DistributedOptimizer, data_entities_vanilla.py:37-42; local Adam wd=1e-5,
+ * data_entities_vanilla_sisa.py:48). */
+int sn_alice_create(sn_alice** out, int device, int optimizer, double lr, double momentum,
+                    double beta1, double beta2, double eps, double weight_decay, int max_batch,
+                    float* w, float* b);
+int sn_alice_destroy(sn_alice* h);
+int sn_alice_reset_opt(sn_alice* h, void* stream);
+int sn_alice_opt_state(sn_alice* h, int which, int param, float** dptr, size_t* count);
+int sn_alice_get_opt_step(sn_alice* h, int64_t* step);
+int sn_alice_set_opt_step(sn_alice* h, int64_t step);
+
+/* act [B,5408] may live on another device (peer-mapped) — e.g. directly in Bob's HBM. */
+int sn_alice_forward(sn_alice* h, const float* x, int B, float* act, void* stream);
+/* conv weight gradient from the cut-layer gradient + optimizer update.  x must be the batch given
+ * to the matching forward.  Replaces Alice's share of dist_autograd.backward +
+ * dist_optimizer.step, data_entities_vanilla.py:231,76. */
+int sn_alice_backward_update(sn_alice* h, const float* x, const float* cut_grad, int B,
+                             void* stream);
+/* SISA phase-1 / unlearn-retrain batch: forward, CE over the 5408 activations, backward, update.
+ * Replaces data_entities_vanilla_sisa.py:62-70 and :160-168. */
+int sn_alice_local_step(sn_alice* h, const float* x, const int64_t* labels, int B,
+                        float* loss_out, void* stream);
+
+/* ------------------------------------------------------------------ NVLink plumbing */
+int sn_p2p_enable_all(int n_devices);
+int sn_p2p_copy(void* dst, int dst_device, const void* src, int src_device, size_t bytes,
+                void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPLITNN_H */

@@ -1,0 +1,145 @@
+// Alice's client block: conv3x3(1->32)+bias -> ReLU -> maxpool2x2 -> flatten, and its weight
+// gradient fused with the 320-parameter optimizer update.  K=9 per output is far too thin for
+// tensor cores: these are CUDA-core FMA kernels bounded by launch latency at the reference's
+// batch sizes and by HBM (21.6 KB written per sample) at large ones.
+// Reference: models.py:5-30 (model1 / model1_sisa).
+#pragma once
+#include "common.cuh"
+
+namespace sn {
+
+constexpr int kConvCG = 8;    // channels per CTA (4 channel groups)
+constexpr int kPooled = 169;  // 13*13
+
+// The four pre-pool conv values of pooled position (i,j), channel weights w[9], in a FIXED
+// FMA order so that forward and backward recompute bit-identical numbers.
+__device__ __forceinline__ void conv4(const float* __restrict__ img, const float* __restrict__ w, float bias,
+                                      int i, int j, float v[4]) {
+  float p[4][4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) p[r][c] = img[(2 * i + r) * 28 + 2 * j + c];
+#pragma unroll
+  for (int d = 0; d < 4; ++d) {
+    const int di = d >> 1, dj = d & 1;
+    float a = bias;
+#pragma unroll
+    for (int u = 0; u < 3; ++u)
+#pragma unroll
+      for (int x = 0; x < 3; ++x) a = __fmaf_rn(w[u * 3 + x], p[di + u][dj + x], a);
+    v[d] = a;
+  }
+}
+
+// grid (samples, 4 channel groups), 256 threads.  act index = c*169 + i*13 + j.
+__global__ void __launch_bounds__(256) conv_pool_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                            const float* __restrict__ bias, int B,
+                                                            float* __restrict__ act) {
+  __shared__ float img[28 * 28];
+  __shared__ float ws[kConvCG * 9];
+  __shared__ float bs[kConvCG];
+  const int cg = blockIdx.y;
+  if (threadIdx.x < kConvCG * 9) ws[threadIdx.x] = w[cg * kConvCG * 9 + threadIdx.x];
+  if (threadIdx.x < kConvCG) bs[threadIdx.x] = bias[cg * kConvCG + threadIdx.x];
+  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    __syncthreads();
+    for (int t = threadIdx.x; t < 196; t += 256)
+      reinterpret_cast<float4*>(img)[t] = reinterpret_cast<const float4*>(x + (size_t)b * 784)[t];
+    __syncthreads();
+    for (int o = threadIdx.x; o < kConvCG * kPooled; o += 256) {
+      const int c = o / kPooled, p = o - c * kPooled;
+      const int i = p / 13, j = p - i * 13;
+      float v[4];
+      conv4(img, ws + c * 9, bs[c], i, j, v);
+      float m = fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3]));
+      act[(size_t)b * kD0 + (size_t)cg * kConvCG * kPooled + o] = fmaxf(m, 0.f);
+    }
+  }
+}
+
+// Weight gradient.  grid (gx, 4): CTA (bx, cg) loops over samples bx, bx+gx, ...; warp = one
+// channel, lanes stride over the 169 pooled positions; 10 register accumulators per lane
+// (9 dW + db).  Per-CTA partial sums go to `partial[gx][320]`; the last CTA to finish
+// (ticket) adds them in a fixed order, then either stores dw/db (OPT==0) or applies the
+// optimizer in place.  Deterministic.
+template <int OPT>
+__global__ void __launch_bounds__(256) conv_pool_bwd_kernel(const float* __restrict__ x, float* __restrict__ w,
+                                                            float* __restrict__ bias,
+                                                            const float* __restrict__ dact, int B,
+                                                            float* __restrict__ partial, unsigned* __restrict__ ticket,
+                                                            float* __restrict__ dw_out, float* __restrict__ db_out,
+                                                            float* __restrict__ s1, float* __restrict__ s2,
+                                                            OptParams op) {
+  __shared__ float img[28 * 28];
+  __shared__ unsigned is_last;
+  const int cg = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c = cg * kConvCG + warp;
+  float wr[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) wr[t] = w[c * 9 + t];
+  const float bc = bias[c];
+  float g[10];
+#pragma unroll
+  for (int t = 0; t < 10; ++t) g[t] = 0.f;
+
+  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    __syncthreads();
+    for (int t = threadIdx.x; t < 196; t += 256)
+      reinterpret_cast<float4*>(img)[t] = reinterpret_cast<const float4*>(x + (size_t)b * 784)[t];
+    __syncthreads();
+    for (int p = lane; p < kPooled; p += 32) {
+      const int i = p / 13, j = p - i * 13;
+      float v[4];
+      conv4(img, wr, bc, i, j, v);
+      int best = 0;                       // first maximum wins (torch CPU max_pool2d)
+      float m = v[0];
+#pragma unroll
+      for (int d = 1; d < 4; ++d)
+        if (v[d] > m) { m = v[d]; best = d; }
+      if (m > 0.f) {                      // ReLU gate
+        const float d = dact[(size_t)b * kD0 + (size_t)c * kPooled + p];
+        const int r0 = 2 * i + (best >> 1), c0 = 2 * j + (best & 1);
+#pragma unroll
+        for (int u = 0; u < 3; ++u)
+#pragma unroll
+          for (int q = 0; q < 3; ++q) g[u * 3 + q] = __fmaf_rn(d, img[(r0 + u) * 28 + c0 + q], g[u * 3 + q]);
+        g[9] += d;
+      }
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < 10; ++t) g[t] = warp_sum(g[t]);
+  if (lane == 0) {
+    float* dst = partial + (size_t)blockIdx.x * kConvParams;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) dst[c * 9 + t] = g[t];
+    dst[288 + c] = g[9];
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned t = atomicAdd(ticket, 1u);
+    is_last = (t == gridDim.x * gridDim.y - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  for (int idx = threadIdx.x; idx < kConvParams; idx += 256) {
+    float s = 0.f;
+    for (unsigned r = 0; r < gridDim.x; ++r) s += __ldcg(partial + (size_t)r * kConvParams + idx);
+    if (OPT == 0) {
+      if (idx < 288) dw_out[idx] = s; else db_out[idx - 288] = s;
+    } else {
+      float* p = idx < 288 ? (w + idx) : (bias + idx - 288);
+      float pv = *p, a = s1[idx], bq = (OPT == 2) ? s2[idx] : 0.f;
+      opt_update<OPT>(op, pv, s, a, bq);
+      *p = pv;
+      s1[idx] = a;
+      if (OPT == 2) s2[idx] = bq;
+    }
+  }
+  if (threadIdx.x == 0) *ticket = 0u;     // re-arm for the next launch
+}
+
+}  // namespace sn

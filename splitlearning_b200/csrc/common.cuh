@@ -1,0 +1,110 @@
+// Shared helpers for libsplitnn (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <atomic>
+#include <string>
+
+namespace sn {
+
+constexpr int kBT = 16;          // batch tile of the skinny (HBM-bound) kernels
+constexpr int kD0 = 5408;        // 32*13*13 cut-layer width
+constexpr int kConvParams = 320; // 32*9 weights + 32 biases
+
+extern thread_local std::string g_last_error;
+extern std::atomic<uint64_t> g_launches;
+
+inline int fail(const char* what, cudaError_t e, const char* file, int line) {
+  char buf[512];
+  snprintf(buf, sizeof buf, "%s failed: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
+  g_last_error = buf;
+  return 1;
+}
+inline int fail_msg(const std::string& msg) {
+  g_last_error = msg;
+  return 2;
+}
+
+#define SN_CUDA(expr)                                                   \
+  do {                                                                  \
+    cudaError_t e_ = (expr);                                            \
+    if (e_ != cudaSuccess) return sn::fail(#expr, e_, __FILE__, __LINE__); \
+  } while (0)
+
+#define SN_LAUNCH_CHECK()                                               \
+  do {                                                                  \
+    sn::g_launches.fetch_add(1, std::memory_order_relaxed);             \
+    cudaError_t e_ = cudaGetLastError();                                \
+    if (e_ != cudaSuccess) return sn::fail("kernel launch", e_, __FILE__, __LINE__); \
+  } while (0)
+
+#define SN_REQUIRE(cond, msg)                                           \
+  do {                                                                  \
+    if (!(cond)) return sn::fail_msg(std::string("libsplitnn: ") + (msg)); \
+  } while (0)
+
+// Optimizer hyper-parameters with the per-step scalars torch computes in host double
+// (torch optim/adam.py _single_tensor_adam; optim/sgd.py _single_tensor_sgd).
+struct OptParams {
+  int type;          // SN_OPT_*
+  float lr;
+  float momentum;
+  float one_minus_b1;
+  float beta2;
+  float one_minus_b2;
+  float eps;
+  float wd;
+  float step_size;   // lr / (1 - beta1^t)
+  float bc2_sqrt;    // sqrt(1 - beta2^t)
+};
+
+template <int OPT>
+__device__ __forceinline__ void opt_update(const OptParams& op, float& p, float g, float& s1, float& s2) {
+  if (OPT == 1) {  // SGD momentum: buf = mom*buf + g ; p -= lr*buf   (buf starts at 0 == "buf <- g")
+    s1 = __fadd_rn(__fmul_rn(op.momentum, s1), g);
+    p = __fmaf_rn(-op.lr, s1, p);
+  } else if (OPT == 2) {  // Adam, coupled L2
+    if (op.wd != 0.f) g = __fmaf_rn(op.wd, p, g);
+    s1 = __fmaf_rn(op.one_minus_b1, g - s1, s1);                      // lerp_
+    s2 = __fmaf_rn(op.one_minus_b2 * g, g, __fmul_rn(s2, op.beta2));   // mul_ then addcmul_
+    float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(s2), op.bc2_sqrt), op.eps);
+    p = __fmaf_rn(-op.step_size, __fdiv_rn(s1, denom), p);            // addcdiv_
+  }
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Philox4x32-10 (Salmon et al. 2011): counter-based RNG for perf-mode dropout.
+__device__ __forceinline__ uint4 philox4x32(uint4 ctr, uint2 key) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+    uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += W0;
+    key.y += W1;
+  }
+  return ctr;
+}
+// keep-decision for element `idx` of dropout layer `layer` at step `offset`
+__device__ __forceinline__ bool philox_keep(uint64_t seed, uint64_t offset, int layer, uint64_t idx, float keep_prob) {
+  uint4 c = make_uint4((uint32_t)(idx >> 2), (uint32_t)(idx >> 34), (uint32_t)offset,
+                       ((uint32_t)(offset >> 32) << 4) | (uint32_t)layer);
+  uint4 r = philox4x32(c, make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+  uint32_t v = (idx & 3) == 0 ? r.x : (idx & 3) == 1 ? r.y : (idx & 3) == 2 ? r.z : r.w;
+  return (v >> 8) * (1.0f / 16777216.0f) < keep_prob;
+}
+
+}  // namespace sn

@@ -1,0 +1,823 @@
+// libsplitnn: C ABI (include/splitnn.h) over the sm_100a kernels.  Host logic only: handle
+// bookkeeping, launch plans, per-step optimizer scalars.  No CPU compute path exists here.
+#include "../../include/splitnn.h"
+
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "alice_kernels.cuh"
+#include "common.cuh"
+#include "mlp_kernels.cuh"
+
+namespace sn {
+thread_local std::string g_last_error;
+std::atomic<uint64_t> g_launches{0};
+
+static int sm_count(int device) {
+  static int cache[64] = {0};
+  if (device >= 0 && device < 64 && cache[device]) return cache[device];
+  int n = 148;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) n = 148;
+  if (device >= 0 && device < 64) cache[device] = n;
+  return n;
+}
+static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+static inline int ew_grid(size_t n, int sms) {
+  size_t g = (n + 255) / 256;
+  return (int)std::max<size_t>(1, std::min<size_t>(g, (size_t)sms * 8));
+}
+
+// ---------------------------------------------------------------- launch plans
+constexpr int kMaxKc = 2048;        // X chunk [16][kc] fp32 = 128 KB of shared memory
+constexpr int kSkinnyFwdMaxB = 64;  // above this the forward uses the general-batch path
+
+struct FwdPlan { int kc, ksplit, nx; };
+struct BwdPlan { int kw, kgroups, nsplit, rows_per_cta; };
+
+static FwdPlan plan_fwd(int K, int N, int sms) {
+  FwdPlan best{round_up(std::min(K, kMaxKc), 128), 0, 1};
+  double best_score = -1;
+  for (int s = 1; s <= 64; ++s) {
+    int kc = round_up(ceil_div(K, s), 128);
+    if (kc > kMaxKc) continue;
+    int actual = ceil_div(K, kc);
+    int nx = std::max(1, sms / actual);
+    double rpw = (double)N / (nx * 8.0);
+    double balance = (double)K / ((double)actual * kc);
+    double util = std::min(1.0, (double)nx * actual / sms);
+    // rows are consumed in groups of 8/4/2/1; smaller groups re-read X from smem more often
+    int rows = (int)ceil(rpw);
+    double cost = (rows / 8) * 1.0 + ((rows % 8) / 4) * 0.6 + ((rows % 4) / 2) * 0.4 + (rows % 2) * 0.3;
+    double qeff = cost > 0 ? (rpw / 8.0) / cost : 0.0;
+    double iters = kc / 128.0;
+    double redeff = iters / (iters + 0.3);
+    double score = balance * util * std::min(1.0, qeff) * redeff;
+    if (score > best_score) { best_score = score; best = FwdPlan{kc, actual, nx}; }
+    if (kc == 128) break;
+  }
+  return best;
+}
+
+static BwdPlan plan_bwd(int N, int K, int sms, bool need_da, bool adam) {
+  BwdPlan best{1, ceil_div(K, 128), 1, N};
+  double best_score = -1;
+  const int kslices = ceil_div(K, 128);
+  const double main_bytes = (double)N * K * 4.0 * (adam ? 6 : 4);
+  for (int kw = 1; kw <= 8; kw *= 2) {
+    int rw = 8 / kw;
+    int kgroups = ceil_div(kslices, kw);
+    int nsplit = std::max(1, sms / kgroups);
+    int rows = std::max(rw, ceil_div(N, nsplit));
+    rows = std::min(rows, 1024);
+    nsplit = ceil_div(N, rows);
+    double ctas = (double)kgroups * nsplit;
+    double waves = ceil(ctas / sms);
+    double util = ctas / (waves * sms);
+    double kwaste = (double)K / ((double)kgroups * kw * 128);
+    double part = need_da ? (double)nsplit * 16.0 * K * 4.0 * 2.0 : 0.0;
+    double score = util * kwaste * main_bytes / (main_bytes + part);
+    if (score > best_score) { best_score = score; best = BwdPlan{kw, kgroups, nsplit, rows}; }
+  }
+  return best;
+}
+
+static size_t bwd_smem_bytes(const BwdPlan& p, bool need_da) {
+  return (size_t)p.rows_per_cta * kBT * 4 + (need_da ? (size_t)8 * kBT * 32 * 16 : 0);
+}
+
+// ---------------------------------------------------------------- optimizer scalars
+struct Hyper {
+  int type = SN_OPT_NONE;
+  double lr = 0, momentum = 0, beta1 = 0.9, beta2 = 0.999, eps = 1e-8, wd = 0;
+};
+static OptParams make_opt(const Hyper& h, int64_t step) {
+  // every scalar is formed in double and rounded to fp32 where torch rounds it
+  OptParams o{};
+  o.type = h.type;
+  o.lr = (float)h.lr;
+  o.momentum = (float)h.momentum;
+  o.one_minus_b1 = (float)(1.0 - h.beta1);
+  o.beta2 = (float)h.beta2;
+  o.one_minus_b2 = (float)(1.0 - h.beta2);
+  o.eps = (float)h.eps;
+  o.wd = (float)h.wd;
+  if (h.type == SN_OPT_ADAM) {
+    const double bc1 = 1.0 - pow(h.beta1, (double)step), bc2 = 1.0 - pow(h.beta2, (double)step);
+    o.step_size = (float)(h.lr / bc1);
+    o.bc2_sqrt = (float)sqrt(bc2);
+  }
+  return o;
+}
+
+template <typename F>
+static int set_smem(F func, size_t bytes) {
+  if (bytes > 48 * 1024) SN_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return 0;
+}
+
+// ---------------------------------------------------------------- per-kernel timing (bench only)
+// When enabled on a handle, the two streaming kernels are bracketed by CUDA events on the
+// launching stream; bench.py reads the per-launch averages for the roofline report.
+struct Profiler {
+  bool on = false;
+  struct Rec { int kind, layer; cudaEvent_t a, b; };
+  std::vector<Rec> recs;
+  cudaEvent_t begin(cudaStream_t st, int kind, int layer) {
+    if (!on) return nullptr;
+    Rec r{kind, layer, nullptr, nullptr};
+    cudaEventCreate(&r.a);
+    cudaEventCreate(&r.b);
+    cudaEventRecord(r.a, st);
+    recs.push_back(r);
+    return r.b;
+  }
+  static void end(cudaEvent_t e, cudaStream_t st) { if (e) cudaEventRecord(e, st); }
+  void clear() {
+    for (auto& r : recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+    recs.clear();
+  }
+};
+
+// ---------------------------------------------------------------- shared launch helpers
+static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, const float* bias, int K, int N,
+                             int relu, const uint8_t* mask, float keep_prob, float scale, uint64_t seed,
+                             uint64_t offset, int layer, float* H, int ldh, float* out2, float* P, int sms,
+                             cudaStream_t st, Profiler* prof = nullptr) {
+  if (B <= kSkinnyFwdMaxB && (K % 4) == 0) {
+    FwdPlan p = plan_fwd(K, N, sms);
+    int tiles = ceil_div(B, kBT), Bpad = tiles * kBT;
+    size_t smem = (size_t)kBT * p.kc * 4;
+    if (set_smem(fwd_skinny_kernel, smem)) return 1;
+    dim3 grid(p.nx, p.ksplit, tiles);
+    cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
+    fwd_skinny_kernel<<<grid, 256, smem, st>>>(X, ldx, B, W, K, N, K, p.kc, P, Bpad);
+    Profiler::end(pe, st);
+    SN_LAUNCH_CHECK();
+    fwd_epilogue_kernel<<<ew_grid((size_t)B * N, sms), 256, 0, st>>>(P, p.ksplit, Bpad, B, N, bias, relu, mask,
+                                                                    keep_prob, scale, seed, offset, layer, H, ldh, out2);
+    SN_LAUNCH_CHECK();
+  } else {
+    dim3 grid(ceil_div(N, 64), ceil_div(B, 64));
+    sgemm_strided_kernel<<<grid, 256, 0, st>>>(X, ldx, 1, W, 1, K, H, ldh, B, N, K);
+    SN_LAUNCH_CHECK();
+    SN_REQUIRE(ldh == N, "general-batch forward needs a dense output");
+    fwd_epilogue_kernel<<<ew_grid((size_t)B * N, sms), 256, 0, st>>>(H, 1, 0, B, N, bias, relu, mask, keep_prob,
+                                                                    scale, seed, offset, layer, H, ldh, out2);
+    SN_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+static size_t fwd_partial_floats(int B, int K, int N, int sms) {
+  if (B > kSkinnyFwdMaxB || (K % 4) != 0) return 0;
+  FwdPlan p = plan_fwd(K, N, sms);
+  return (size_t)p.ksplit * round_up(B, kBT) * N;
+}
+
+}  // namespace sn
+
+using namespace sn;
+
+// =============================================================================== handles
+struct sn_bob {
+  int device = 0, L = 0, relu_last = 0, n_slots = 1, max_batch = 16, Bpad = 16, sms = 148;
+  float dropout_p = 0.f;
+  Hyper hyper;
+  std::vector<int> dims;
+  std::vector<float*> W, b;
+  struct Slot {
+    std::vector<float*> s1, s2;
+    int64_t step = 0;
+  };
+  std::vector<Slot> slots;
+  std::vector<float*> H, dZ;   // index l = 1..L ([Bpad][dims[l]])
+  float* P = nullptr;          // forward split-K partials
+  float* PA = nullptr;         // backward dA partials
+  size_t PA_floats = 0;
+  float* dWbuf = nullptr;      // general-batch path only (lazy)
+  float* row_loss = nullptr;
+  unsigned* ticket = nullptr;
+  bool stashed = false;
+  int stashed_B = 0;
+  int heads = 1;
+  int row_loss_rows = 0;
+  Profiler prof;
+};
+
+struct sn_alice {
+  int device = 0, max_batch = 16, sms = 148;
+  Hyper hyper;
+  float *w = nullptr, *b = nullptr;
+  float *s1 = nullptr, *s2 = nullptr;   // [320] each: 288 weights then 32 biases
+  int64_t step = 0;
+  float* partial = nullptr;
+  unsigned* ticket = nullptr;           // [0] conv ticket, [1] CE ticket
+  float* act = nullptr;                 // local step: [max_batch][5408]
+  float* dact = nullptr;
+  float* row_loss = nullptr;
+  int gx = 1;
+};
+
+static int conv_bwd_gx(int B, int sms) { return std::max(1, std::min(B, sms * 2)); }
+
+extern "C" {
+
+int sn_version(void) { return 1; }
+const char* sn_last_error(void) { return g_last_error.c_str(); }
+uint64_t sn_launch_count(void) { return g_launches.load(); }
+
+// ------------------------------------------------------------------ stateless operators
+int sn_conv_pool_forward(const float* x, const float* w, const float* b, int B, float* act, void* stream) {
+  SN_REQUIRE(x && w && b && act && B > 0, "sn_conv_pool_forward: bad arguments");
+  int dev = 0;
+  SN_CUDA(cudaGetDevice(&dev));
+  dim3 grid(std::min(B, sm_count(dev) * 4), 4);
+  conv_pool_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, w, b, B, act);
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+
+size_t sn_conv_pool_backward_scratch_bytes(int B) {
+  int gx = conv_bwd_gx(std::max(B, 1), 148);
+  return (size_t)gx * kConvParams * 4 + 256;
+}
+
+int sn_conv_pool_backward(const float* x, const float* w, const float* b, const float* dact, int B, float* dw,
+                          float* db, void* scratch, void* stream) {
+  SN_REQUIRE(x && w && b && dact && dw && db && scratch && B > 0, "sn_conv_pool_backward: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  int gx = conv_bwd_gx(B, 148);
+  unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
+  float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
+  SN_CUDA(cudaMemsetAsync(ticket, 0, 256, st));
+  OptParams op{};
+  conv_pool_bwd_kernel<0><<<dim3(gx, 4), 256, 0, st>>>(x, const_cast<float*>(w), const_cast<float*>(b), dact, B,
+                                                      partial, ticket, dw, db, nullptr, nullptr, op);
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+
+size_t sn_linear_forward_scratch_bytes(int B, int K, int N) {
+  if (B <= 0 || K <= 0 || N <= 0) return 16;
+  return std::max<size_t>(16, fwd_partial_floats(B, K, N, 148) * 4);
+}
+
+int sn_linear_forward(const float* x, const float* W, const float* bias, int B, int K, int N, int relu,
+                      const uint8_t* keep_mask, float mask_scale, float* y, void* scratch, size_t scratch_bytes,
+                      void* stream) {
+  SN_REQUIRE(x && W && bias && y && B > 0 && K > 0 && N > 0, "sn_linear_forward: bad arguments");
+  int dev = 0;
+  SN_CUDA(cudaGetDevice(&dev));
+  int sms = sm_count(dev);
+  size_t need = fwd_partial_floats(B, K, N, sms) * 4;
+  SN_REQUIRE(need == 0 || (scratch && scratch_bytes >= need), "sn_linear_forward: scratch too small");
+  return launch_linear_fwd(x, K, B, W, bias, K, N, relu, keep_mask, 1.f, mask_scale, 0, 0, 0, y, N, nullptr,
+                           reinterpret_cast<float*>(scratch), sms, (cudaStream_t)stream);
+}
+
+static int launch_ce(const float* z, int ldz, const int64_t* y, int B, int C, float* dz, int lddz, float* row_loss,
+                     unsigned* ticket, float* loss, float* loss2, cudaStream_t st) {
+  ce_kernel<<<ceil_div(B, 8), 256, 0, st>>>(z, ldz, y, B, C, dz, lddz, row_loss, ticket, loss, loss2);
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+
+int sn_cross_entropy(const float* logits, const int64_t* labels, int B, int C, float* loss, float* dlogits,
+                     void* stream) {
+  SN_REQUIRE(logits && labels && loss && B > 0 && C > 0, "sn_cross_entropy: bad arguments");
+  // stateless form: row losses and the ticket live in a small per-call allocation
+  cudaStream_t st = (cudaStream_t)stream;
+  float* tmp = nullptr;
+  SN_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&tmp), (size_t)B * 4 + 256, st));
+  SN_CUDA(cudaMemsetAsync(tmp, 0, 256, st));
+  int rc = launch_ce(logits, C, labels, B, C, dlogits, C, tmp + 64, reinterpret_cast<unsigned*>(tmp), loss, nullptr, st);
+  SN_CUDA(cudaFreeAsync(tmp, st));
+  return rc;
+}
+
+int sn_eval_counts(const float* logits, const int64_t* labels, int B, int C, int64_t omit_label, int64_t* counters6,
+                   void* stream) {
+  SN_REQUIRE(logits && labels && counters6 && B > 0 && C > 0, "sn_eval_counts: bad arguments");
+  eval_counts_kernel<<<ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(
+      logits, labels, B, C, omit_label, reinterpret_cast<unsigned long long*>(counters6));
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------ Bob
+int sn_bob_create(sn_bob** out, int device, const int* dims, int n_layers, int relu_last, double dropout_p,
+                  int optimizer, double lr, double momentum, double beta1, double beta2, double eps,
+                  double weight_decay, int n_opt_slots, int max_batch, float* const* W, float* const* b) {
+  SN_REQUIRE(out && dims && W && b && n_layers >= 1 && n_layers <= 16, "sn_bob_create: bad arguments");
+  SN_REQUIRE(optimizer >= SN_OPT_NONE && optimizer <= SN_OPT_ADAM, "sn_bob_create: unknown optimizer");
+  SN_REQUIRE(n_opt_slots >= 1 && max_batch >= 1, "sn_bob_create: need n_opt_slots >= 1 and max_batch >= 1");
+  SN_REQUIRE(dropout_p >= 0.0 && dropout_p < 1.0, "sn_bob_create: dropout_p must be in [0,1)");
+  int ndev = 0;
+  SN_CUDA(cudaGetDeviceCount(&ndev));
+  SN_REQUIRE(device >= 0 && device < ndev, "sn_bob_create: no such CUDA device (a B200 is required; there is no CPU path)");
+  SN_CUDA(cudaSetDevice(device));
+  sn_bob* h = new sn_bob();
+  h->device = device;
+  h->L = n_layers;
+  h->relu_last = relu_last;
+  h->dropout_p = (float)dropout_p;
+  h->hyper.type = optimizer;
+  h->hyper.lr = lr;
+  h->hyper.momentum = momentum;
+  h->hyper.beta1 = beta1;
+  h->hyper.beta2 = beta2;
+  h->hyper.eps = eps;
+  h->hyper.wd = weight_decay;
+  h->n_slots = n_opt_slots;
+  h->max_batch = max_batch;
+  h->Bpad = round_up(max_batch, kBT);
+  h->sms = sm_count(device);
+  h->dims.assign(dims, dims + n_layers + 1);
+  for (int l = 0; l <= n_layers; ++l) {
+    if (dims[l] <= 0) { delete h; return fail_msg("libsplitnn: sn_bob_create: non-positive layer width"); }
+  }
+  h->W.assign(W, W + n_layers);
+  h->b.assign(b, b + n_layers);
+  auto fail_free = [&](cudaError_t e) { sn_bob_destroy(h); return fail("cudaMalloc", e, __FILE__, __LINE__); };
+  cudaError_t e;
+  h->H.assign(n_layers + 1, nullptr);
+  h->dZ.assign(n_layers + 1, nullptr);
+  size_t p_floats = 16, pa_floats = 16;
+  for (int l = 0; l < n_layers; ++l) {
+    const int K = dims[l], N = dims[l + 1];
+    if ((e = cudaMalloc(&h->H[l + 1], (size_t)h->Bpad * N * 4)) != cudaSuccess) return fail_free(e);
+    if ((e = cudaMalloc(&h->dZ[l + 1], (size_t)h->Bpad * N * 4)) != cudaSuccess) return fail_free(e);
+    p_floats = std::max(p_floats, fwd_partial_floats(std::min(max_batch, kSkinnyFwdMaxB), K, N, h->sms));
+    BwdPlan bp = plan_bwd(N, K, h->sms, true, optimizer == SN_OPT_ADAM);
+    pa_floats = std::max(pa_floats, (size_t)bp.nsplit * kBT * K);
+    if (max_batch > kBT) pa_floats = std::max(pa_floats, (size_t)h->Bpad * K);
+  }
+  h->PA_floats = pa_floats;
+  if ((e = cudaMalloc(&h->P, p_floats * 4)) != cudaSuccess) return fail_free(e);
+  if ((e = cudaMalloc(&h->PA, pa_floats * 4)) != cudaSuccess) return fail_free(e);
+  h->row_loss_rows = h->Bpad;
+  if ((e = cudaMalloc(&h->row_loss, (size_t)h->Bpad * 4)) != cudaSuccess) return fail_free(e);
+  if ((e = cudaMalloc(&h->ticket, 256)) != cudaSuccess) return fail_free(e);
+  if ((e = cudaMemset(h->ticket, 0, 256)) != cudaSuccess) return fail_free(e);
+  h->slots.resize(n_opt_slots);
+  if (optimizer != SN_OPT_NONE) {
+    for (auto& s : h->slots) {
+      s.s1.assign(2 * n_layers, nullptr);
+      s.s2.assign(2 * n_layers, nullptr);
+      for (int l = 0; l < n_layers; ++l) {
+        size_t nw = (size_t)dims[l] * dims[l + 1], nb = dims[l + 1];
+        if ((e = cudaMalloc(&s.s1[2 * l], nw * 4)) != cudaSuccess) return fail_free(e);
+        if ((e = cudaMalloc(&s.s1[2 * l + 1], nb * 4)) != cudaSuccess) return fail_free(e);
+        if ((e = cudaMemset(s.s1[2 * l], 0, nw * 4)) != cudaSuccess) return fail_free(e);
+        if ((e = cudaMemset(s.s1[2 * l + 1], 0, nb * 4)) != cudaSuccess) return fail_free(e);
+        if (optimizer == SN_OPT_ADAM) {
+          if ((e = cudaMalloc(&s.s2[2 * l], nw * 4)) != cudaSuccess) return fail_free(e);
+          if ((e = cudaMalloc(&s.s2[2 * l + 1], nb * 4)) != cudaSuccess) return fail_free(e);
+          if ((e = cudaMemset(s.s2[2 * l], 0, nw * 4)) != cudaSuccess) return fail_free(e);
+          if ((e = cudaMemset(s.s2[2 * l + 1], 0, nb * 4)) != cudaSuccess) return fail_free(e);
+        }
+      }
+    }
+  }
+  *out = h;
+  return 0;
+}
+
+int sn_bob_destroy(sn_bob* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  for (auto p : h->H) cudaFree(p);
+  for (auto p : h->dZ) cudaFree(p);
+  cudaFree(h->P);
+  cudaFree(h->PA);
+  cudaFree(h->dWbuf);
+  cudaFree(h->row_loss);
+  cudaFree(h->ticket);
+  h->prof.clear();
+  for (auto& s : h->slots) {
+    for (auto p : s.s1) cudaFree(p);
+    for (auto p : s.s2) cudaFree(p);
+  }
+  delete h;
+  return 0;
+}
+
+#define SN_BOB_ENTER(h)                                     \
+  SN_REQUIRE(h != nullptr, "null sn_bob handle");           \
+  SN_CUDA(cudaSetDevice(h->device));
+
+int sn_bob_reset_opt_slot(sn_bob* h, int slot, void* stream) {
+  SN_BOB_ENTER(h);
+  SN_REQUIRE(slot >= 0 && slot < h->n_slots, "sn_bob_reset_opt_slot: slot out of range");
+  auto& s = h->slots[slot];
+  s.step = 0;
+  for (int l = 0; l < h->L && h->hyper.type != SN_OPT_NONE; ++l) {
+    size_t nw = (size_t)h->dims[l] * h->dims[l + 1], nb = h->dims[l + 1];
+    SN_CUDA(cudaMemsetAsync(s.s1[2 * l], 0, nw * 4, (cudaStream_t)stream));
+    SN_CUDA(cudaMemsetAsync(s.s1[2 * l + 1], 0, nb * 4, (cudaStream_t)stream));
+    if (h->hyper.type == SN_OPT_ADAM) {
+      SN_CUDA(cudaMemsetAsync(s.s2[2 * l], 0, nw * 4, (cudaStream_t)stream));
+      SN_CUDA(cudaMemsetAsync(s.s2[2 * l + 1], 0, nb * 4, (cudaStream_t)stream));
+    }
+  }
+  return 0;
+}
+
+int sn_bob_opt_state(sn_bob* h, int slot, int which, int param, float** dptr, size_t* count) {
+  SN_BOB_ENTER(h);
+  SN_REQUIRE(slot >= 0 && slot < h->n_slots && param >= 0 && param < 2 * h->L && dptr && count,
+             "sn_bob_opt_state: bad arguments");
+  SN_REQUIRE(h->hyper.type != SN_OPT_NONE && (which == 0 || (which == 1 && h->hyper.type == SN_OPT_ADAM)),
+             "sn_bob_opt_state: no such state for this optimizer");
+  int l = param / 2;
+  *count = (param & 1) ? (size_t)h->dims[l + 1] : (size_t)h->dims[l] * h->dims[l + 1];
+  *dptr = which == 0 ? h->slots[slot].s1[param] : h->slots[slot].s2[param];
+  return 0;
+}
+int sn_bob_get_opt_step(sn_bob* h, int slot, int64_t* step) {
+  SN_REQUIRE(h && step && slot >= 0 && slot < h->n_slots, "sn_bob_get_opt_step: bad arguments");
+  *step = h->slots[slot].step;
+  return 0;
+}
+int sn_bob_set_opt_step(sn_bob* h, int slot, int64_t step) {
+  SN_REQUIRE(h && slot >= 0 && slot < h->n_slots && step >= 0, "sn_bob_set_opt_step: bad arguments");
+  h->slots[slot].step = step;
+  return 0;
+}
+int sn_bob_set_lr(sn_bob* h, double lr) {
+  SN_REQUIRE(h, "null sn_bob handle");
+  h->hyper.lr = lr;
+  return 0;
+}
+int sn_bob_profile(sn_bob* h, int enable) {
+  SN_BOB_ENTER(h);
+  h->prof.clear();
+  h->prof.on = enable != 0;
+  return 0;
+}
+int sn_bob_profile_read(sn_bob* h, int kind, int layer, double* total_ms, int* launches) {
+  SN_BOB_ENTER(h);
+  SN_REQUIRE(total_ms && launches, "sn_bob_profile_read: bad arguments");
+  double t = 0;
+  int n = 0;
+  for (auto& r : h->prof.recs) {
+    if (r.kind != kind || r.layer != layer) continue;
+    SN_CUDA(cudaEventSynchronize(r.b));
+    float ms = 0;
+    SN_CUDA(cudaEventElapsedTime(&ms, r.a, r.b));
+    t += ms;
+    ++n;
+  }
+  *total_ms = t;
+  *launches = n;
+  return 0;
+}
+int sn_bob_set_ce_heads(sn_bob* h, int heads) {
+  SN_BOB_ENTER(h);
+  SN_REQUIRE(heads >= 1 && h->dims[h->L] % heads == 0, "sn_bob_set_ce_heads: heads must divide the output width");
+  if (h->Bpad * heads > h->row_loss_rows) {
+    SN_CUDA(cudaFree(h->row_loss));
+    h->row_loss = nullptr;
+    SN_CUDA(cudaMalloc(&h->row_loss, (size_t)h->Bpad * heads * 4));
+    h->row_loss_rows = h->Bpad * heads;
+  }
+  h->heads = heads;
+  return 0;
+}
+
+static int bob_forward_impl(sn_bob* h, const float* act, int B, int train, const uint8_t* const* masks, uint64_t seed,
+                            uint64_t offset, float* out, cudaStream_t st) {
+  const float keep = 1.f - h->dropout_p, scale = 1.f / keep;
+  const float* X = act;
+  int ldx = h->dims[0];
+  for (int l = 0; l < h->L; ++l) {
+    const int K = h->dims[l], N = h->dims[l + 1];
+    const bool last = l == h->L - 1;
+    const int relu = (!last || h->relu_last) ? 1 : 0;
+    const bool drop = train && !last && h->dropout_p > 0.f;
+    const uint8_t* mask = (drop && masks) ? masks[l] : nullptr;
+    const float kp = (drop && !masks) ? keep : 1.f;
+    if (launch_linear_fwd(X, ldx, B, h->W[l], h->b[l], K, N, relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N,
+                          last ? out : nullptr, h->P, h->sms, st, &h->prof))
+      return 1;
+    X = h->H[l + 1];
+    ldx = N;
+  }
+  return 0;
+}
+
+}  // extern "C" (templates need C++ linkage)
+template <int OPT>
+static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float* cut_grad, cudaStream_t st) {
+  auto& s = h->slots[slot];
+  s.step += 1;
+  const OptParams op = make_opt(h->hyper, s.step);
+  const float scale = 1.f / (1.f - h->dropout_p);
+  for (int l = h->L - 1; l >= 0; --l) {
+    const int K = h->dims[l], N = h->dims[l + 1];
+    const float* A = l == 0 ? act : h->H[l];
+    const float* dZ = h->dZ[l + 1];
+    const bool need_da = l > 0 || cut_grad != nullptr;
+    float* dst = l > 0 ? h->dZ[l] : cut_grad;
+    const float* gateH = l > 0 ? h->H[l] : nullptr;
+    const float gscale = (l > 0 && h->dropout_p > 0.f) ? scale : 1.f;
+    if (B <= kBT && (K % 4) == 0) {
+      BwdPlan p = plan_bwd(N, K, h->sms, need_da, OPT == 2);
+      size_t smem = bwd_smem_bytes(p, need_da);
+      dim3 grid(p.kgroups, p.nsplit);
+      if (need_da) {
+        if (set_smem(bwd_update_kernel<OPT, true>, smem)) return 1;
+        cudaEvent_t pe = h->prof.begin(st, 1, l);
+        bwd_update_kernel<OPT, true><<<grid, 256, smem, st>>>(h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
+                                                              s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, h->PA,
+                                                              p.kw, p.rows_per_cta, op);
+        Profiler::end(pe, st);
+        SN_LAUNCH_CHECK();
+        bwd_epilogue_kernel<<<ew_grid((size_t)B * K, h->sms), 256, 0, st>>>(h->PA, p.nsplit, B, K, gateH, K, gscale,
+                                                                           dst, K);
+        SN_LAUNCH_CHECK();
+      } else {
+        if (set_smem(bwd_update_kernel<OPT, false>, smem)) return 1;
+        cudaEvent_t pe = h->prof.begin(st, 1, l);
+        bwd_update_kernel<OPT, false><<<grid, 256, smem, st>>>(h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
+                                                               s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B,
+                                                               h->PA, p.kw, p.rows_per_cta, op);
+        Profiler::end(pe, st);
+        SN_LAUNCH_CHECK();
+      }
+    } else {
+      // general-batch path: dA from W_old first, then dW into a buffer, then the updates
+      if (!h->dWbuf) {
+        size_t mx = 0;
+        for (int q = 0; q < h->L; ++q) mx = std::max(mx, (size_t)h->dims[q] * h->dims[q + 1]);
+        SN_CUDA(cudaMalloc(&h->dWbuf, mx * 4));
+      }
+      if (need_da) {
+        SN_REQUIRE((size_t)B * K <= h->PA_floats, "batch larger than max_batch given to sn_bob_create");
+        sgemm_strided_kernel<<<dim3(ceil_div(K, 64), ceil_div(B, 64)), 256, 0, st>>>(dZ, N, 1, h->W[l], K, 1, h->PA, K,
+                                                                                    B, K, N);
+        SN_LAUNCH_CHECK();
+      }
+      sgemm_strided_kernel<<<dim3(ceil_div(K, 64), ceil_div(N, 64)), 256, 0, st>>>(dZ, 1, N, A, K, 1, h->dWbuf, K, N,
+                                                                                  K, B);
+      SN_LAUNCH_CHECK();
+      opt_elementwise_kernel<OPT><<<ew_grid((size_t)N * K, h->sms), 256, 0, st>>>(h->W[l], h->dWbuf, s.s1[2 * l],
+                                                                                 s.s2[2 * l], (size_t)N * K, op);
+      SN_LAUNCH_CHECK();
+      bias_grad_update_kernel<OPT><<<ceil_div(N, 256), 256, 0, st>>>(dZ, N, B, N, h->b[l], s.s1[2 * l + 1],
+                                                                    s.s2[2 * l + 1], op);
+      SN_LAUNCH_CHECK();
+      if (need_da) {
+        // PA holds one dense [B][K] "split"; bwd_epilogue indexes splits with a 16-row stride
+        bwd_epilogue_kernel<<<ew_grid((size_t)B * K, h->sms), 256, 0, st>>>(h->PA, 1, B, K, gateH, K, gscale, dst, K);
+        SN_LAUNCH_CHECK();
+      }
+    }
+  }
+  return 0;
+}
+
+extern "C" {
+static int bob_backward_dispatch(sn_bob* h, int slot, const float* act, int B, float* cut_grad, cudaStream_t st) {
+  switch (h->hyper.type) {
+    case SN_OPT_SGD_MOMENTUM: return bob_backward_impl<1>(h, slot, act, B, cut_grad, st);
+    case SN_OPT_ADAM: return bob_backward_impl<2>(h, slot, act, B, cut_grad, st);
+    default: return fail_msg("libsplitnn: this sn_bob was created without an optimizer");
+  }
+}
+
+int sn_bob_train_step(sn_bob* h, int slot, const float* act, const int64_t* labels, int B,
+                      const uint8_t* const* drop_masks, uint64_t seed, uint64_t offset, float* cut_grad,
+                      float* logits_out, float* loss_out, void* stream) {
+  SN_BOB_ENTER(h);
+  SN_REQUIRE(act && labels && B > 0, "sn_bob_train_step: bad arguments");
+  SN_REQUIRE(B <= h->max_batch, "sn_bob_train_step: batch larger than max_batch given to sn_bob_create");
+  SN_REQUIRE(slot >= 0 && slot < h->n_slots, "sn_bob_train_step: optimizer slot out of range");
+  cudaStream_t st = (cudaStream_t)stream;
+  h->stashed = true;
+  h->stashed_B = B;
+  if (bob_forward_impl(h, act, B, 1, drop_masks, seed, offset, logits_out, st)) return 1;
+  const int C = h->dims[h->L];
+  float* z = h->H[h->L];
+  if (h->relu_last) return fail_msg("libsplitnn: sn_bob_train_step needs a linear last layer (relu_last=0)");
+  // [B][heads*Ch] row-major is [B*heads][Ch]: multi-head CE is the same kernel over more rows
+  const int Ch = C / h->heads;
+  if (launch_ce(z, Ch, labels, B * h->heads, Ch, h->dZ[h->L], Ch, h->row_loss, h->ticket, loss_out, nullptr, st)) return 1;
+  return bob_backward_dispatch(h, slot, act, B, cut_grad, st);
+}
+
+int sn_bob_forward(sn_bob* h, const float* act, int B, int train_mode, const uint8_t* const* drop_masks, uint64_t seed,
+                   uint64_t offset, float* out, void* stream) {
+  SN_BOB_ENTER(h);
+  SN_REQUIRE(act && out && B > 0, "sn_bob_forward: bad arguments");
+  SN_REQUIRE(B <= h->max_batch, "sn_bob_forward: batch larger than max_batch given to sn_bob_create");
+  h->stashed = train_mode != 0;
+  h->stashed_B = B;
+  return bob_forward_impl(h, act, B, train_mode, drop_masks, seed, offset, out, (cudaStream_t)stream);
+}
+
+int sn_bob_backward_update(sn_bob* h, int slot, const float* act, const float* dout, int B, float* cut_grad,
+                           void* stream) {
+  SN_BOB_ENTER(h);
+  SN_REQUIRE(act && dout && B > 0, "sn_bob_backward_update: bad arguments");
+  SN_REQUIRE(h->stashed && h->stashed_B == B, "sn_bob_backward_update: no matching train-mode sn_bob_forward");
+  SN_REQUIRE(slot >= 0 && slot < h->n_slots, "sn_bob_backward_update: optimizer slot out of range");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int C = h->dims[h->L];
+  const size_t n = (size_t)B * C;
+  if (h->relu_last) {
+    relu_gate_kernel<<<ew_grid(n, h->sms), 256, 0, st>>>(dout, h->H[h->L], n, h->dZ[h->L]);
+    SN_LAUNCH_CHECK();
+  } else {
+    SN_CUDA(cudaMemcpyAsync(h->dZ[h->L], dout, n * 4, cudaMemcpyDeviceToDevice, st));
+  }
+  return bob_backward_dispatch(h, slot, act, B, cut_grad, st);
+}
+
+int sn_bob_server_epoch(sn_bob* h, int slot, const float* cache, const int64_t* labels, const int64_t* batch_offsets,
+                        int n_batches, const uint8_t* const* drop_masks, uint64_t seed, uint64_t offset,
+                        float* loss_per_step, void* stream) {
+  SN_BOB_ENTER(h);
+  SN_REQUIRE(cache && labels && batch_offsets && n_batches >= 0, "sn_bob_server_epoch: bad arguments");
+  const int d0 = h->dims[0], nm = h->L - 1;
+  std::vector<const uint8_t*> m(std::max(nm, 1), nullptr);
+  for (int i = 0; i < n_batches; ++i) {
+    const int64_t r0 = batch_offsets[i], r1 = batch_offsets[i + 1];
+    SN_REQUIRE(r1 > r0 && r1 - r0 <= h->max_batch, "sn_bob_server_epoch: bad batch_offsets");
+    if (drop_masks)
+      for (int l = 0; l < nm; ++l) m[l] = drop_masks[l] + (size_t)r0 * h->dims[l + 1];
+    int rc = sn_bob_train_step(h, slot, cache + (size_t)r0 * d0, labels + r0, (int)(r1 - r0),
+                               drop_masks ? m.data() : nullptr, seed, offset + (uint64_t)i, nullptr, nullptr,
+                               loss_per_step ? loss_per_step + i : nullptr, stream);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------ Alice
+int sn_alice_create(sn_alice** out, int device, int optimizer, double lr, double momentum, double beta1,
+                    double beta2, double eps, double weight_decay, int max_batch, float* w, float* b) {
+  SN_REQUIRE(out && w && b && max_batch >= 1, "sn_alice_create: bad arguments");
+  SN_REQUIRE(optimizer >= SN_OPT_NONE && optimizer <= SN_OPT_ADAM, "sn_alice_create: unknown optimizer");
+  int ndev = 0;
+  SN_CUDA(cudaGetDeviceCount(&ndev));
+  SN_REQUIRE(device >= 0 && device < ndev, "sn_alice_create: no such CUDA device (a B200 is required; there is no CPU path)");
+  SN_CUDA(cudaSetDevice(device));
+  sn_alice* h = new sn_alice();
+  h->device = device;
+  h->max_batch = max_batch;
+  h->sms = sm_count(device);
+  h->hyper.type = optimizer;
+  h->hyper.lr = lr;
+  h->hyper.momentum = momentum;
+  h->hyper.beta1 = beta1;
+  h->hyper.beta2 = beta2;
+  h->hyper.eps = eps;
+  h->hyper.wd = weight_decay;
+  h->w = w;
+  h->b = b;
+  h->gx = conv_bwd_gx(max_batch, h->sms);
+  cudaError_t e;
+  auto fail_free = [&](cudaError_t err) { sn_alice_destroy(h); return fail("cudaMalloc", err, __FILE__, __LINE__); };
+  if ((e = cudaMalloc(&h->s1, kConvParams * 4)) != cudaSuccess) return fail_free(e);
+  if ((e = cudaMalloc(&h->s2, kConvParams * 4)) != cudaSuccess) return fail_free(e);
+  if ((e = cudaMemset(h->s1, 0, kConvParams * 4)) != cudaSuccess) return fail_free(e);
+  if ((e = cudaMemset(h->s2, 0, kConvParams * 4)) != cudaSuccess) return fail_free(e);
+  if ((e = cudaMalloc(&h->partial, (size_t)h->gx * kConvParams * 4)) != cudaSuccess) return fail_free(e);
+  if ((e = cudaMalloc(&h->ticket, 256)) != cudaSuccess) return fail_free(e);
+  if ((e = cudaMemset(h->ticket, 0, 256)) != cudaSuccess) return fail_free(e);
+  if ((e = cudaMalloc(&h->row_loss, (size_t)max_batch * 4)) != cudaSuccess) return fail_free(e);
+  *out = h;
+  return 0;
+}
+
+int sn_alice_destroy(sn_alice* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaFree(h->s1);
+  cudaFree(h->s2);
+  cudaFree(h->partial);
+  cudaFree(h->ticket);
+  cudaFree(h->act);
+  cudaFree(h->dact);
+  cudaFree(h->row_loss);
+  delete h;
+  return 0;
+}
+
+#define SN_ALICE_ENTER(h)                                   \
+  SN_REQUIRE(h != nullptr, "null sn_alice handle");         \
+  SN_CUDA(cudaSetDevice(h->device));
+
+int sn_alice_reset_opt(sn_alice* h, void* stream) {
+  SN_ALICE_ENTER(h);
+  h->step = 0;
+  SN_CUDA(cudaMemsetAsync(h->s1, 0, kConvParams * 4, (cudaStream_t)stream));
+  SN_CUDA(cudaMemsetAsync(h->s2, 0, kConvParams * 4, (cudaStream_t)stream));
+  return 0;
+}
+int sn_alice_opt_state(sn_alice* h, int which, int param, float** dptr, size_t* count) {
+  SN_REQUIRE(h && dptr && count && (which == 0 || which == 1) && (param == 0 || param == 1),
+             "sn_alice_opt_state: bad arguments");
+  float* base = which == 0 ? h->s1 : h->s2;
+  *dptr = param == 0 ? base : base + 288;
+  *count = param == 0 ? 288 : 32;
+  return 0;
+}
+int sn_alice_get_opt_step(sn_alice* h, int64_t* step) {
+  SN_REQUIRE(h && step, "sn_alice_get_opt_step: bad arguments");
+  *step = h->step;
+  return 0;
+}
+int sn_alice_set_opt_step(sn_alice* h, int64_t step) {
+  SN_REQUIRE(h && step >= 0, "sn_alice_set_opt_step: bad arguments");
+  h->step = step;
+  return 0;
+}
+
+int sn_alice_forward(sn_alice* h, const float* x, int B, float* act, void* stream) {
+  SN_ALICE_ENTER(h);
+  SN_REQUIRE(x && act && B > 0, "sn_alice_forward: bad arguments");
+  dim3 grid(std::min(B, h->sms * 4), 4);
+  conv_pool_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, h->w, h->b, B, act);
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+
+static int alice_bwd(sn_alice* h, const float* x, const float* dact, int B, cudaStream_t st) {
+  SN_REQUIRE(B <= h->max_batch, "batch larger than max_batch given to sn_alice_create");
+  h->step += 1;
+  const OptParams op = make_opt(h->hyper, h->step);
+  dim3 grid(conv_bwd_gx(B, h->sms), 4);
+  SN_REQUIRE((int)grid.x <= h->gx, "internal: conv backward grid exceeds scratch");
+  switch (h->hyper.type) {
+    case SN_OPT_SGD_MOMENTUM:
+      conv_pool_bwd_kernel<1><<<grid, 256, 0, st>>>(x, h->w, h->b, dact, B, h->partial, h->ticket, nullptr, nullptr,
+                                                   h->s1, h->s2, op);
+      break;
+    case SN_OPT_ADAM:
+      conv_pool_bwd_kernel<2><<<grid, 256, 0, st>>>(x, h->w, h->b, dact, B, h->partial, h->ticket, nullptr, nullptr,
+                                                   h->s1, h->s2, op);
+      break;
+    default:
+      return fail_msg("libsplitnn: this sn_alice was created without an optimizer");
+  }
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+
+int sn_alice_backward_update(sn_alice* h, const float* x, const float* cut_grad, int B, void* stream) {
+  SN_ALICE_ENTER(h);
+  SN_REQUIRE(x && cut_grad && B > 0, "sn_alice_backward_update: bad arguments");
+  return alice_bwd(h, x, cut_grad, B, (cudaStream_t)stream);
+}
+
+int sn_alice_local_step(sn_alice* h, const float* x, const int64_t* labels, int B, float* loss_out, void* stream) {
+  SN_ALICE_ENTER(h);
+  SN_REQUIRE(x && labels && B > 0 && B <= h->max_batch, "sn_alice_local_step: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!h->act) {
+    SN_CUDA(cudaMalloc(&h->act, (size_t)h->max_batch * kD0 * 4));
+    SN_CUDA(cudaMalloc(&h->dact, (size_t)h->max_batch * kD0 * 4));
+  }
+  dim3 grid(std::min(B, h->sms * 4), 4);
+  conv_pool_fwd_kernel<<<grid, 256, 0, st>>>(x, h->w, h->b, B, h->act);
+  SN_LAUNCH_CHECK();
+  if (launch_ce(h->act, kD0, labels, B, kD0, h->dact, kD0, h->row_loss, h->ticket + 1, loss_out, nullptr, st)) return 1;
+  return alice_bwd(h, x, h->dact, B, st);
+}
+
+// ------------------------------------------------------------------ NVLink plumbing
+int sn_p2p_enable_all(int n_devices) {
+  int ndev = 0;
+  SN_CUDA(cudaGetDeviceCount(&ndev));
+  n_devices = std::min(n_devices, ndev);
+  int keep = 0;
+  SN_CUDA(cudaGetDevice(&keep));
+  for (int i = 0; i < n_devices; ++i) {
+    SN_CUDA(cudaSetDevice(i));
+    for (int j = 0; j < n_devices; ++j) {
+      if (i == j) continue;
+      int can = 0;
+      SN_CUDA(cudaDeviceCanAccessPeer(&can, i, j));
+      if (!can) continue;
+      cudaError_t e = cudaDeviceEnablePeerAccess(j, 0);
+      if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); continue; }
+      if (e != cudaSuccess) return fail("cudaDeviceEnablePeerAccess", e, __FILE__, __LINE__);
+    }
+  }
+  SN_CUDA(cudaSetDevice(keep));
+  return 0;
+}
+
+int sn_p2p_copy(void* dst, int dst_device, const void* src, int src_device, size_t bytes, void* stream) {
+  SN_REQUIRE(dst && src, "sn_p2p_copy: bad arguments");
+  SN_CUDA(cudaMemcpyPeerAsync(dst, dst_device, src, src_device, bytes, (cudaStream_t)stream));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,290 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle and the committed fixtures.
+
+Tolerance: BASELINE.json asks for logits/losses within 1e-4 relative per step; measured
+norm-wise, ||cuda - ref||_F / ||ref||_F <= 1e-4 (per-element relative error is
+ill-posed, fp32 itself misses it near zero).  Integer results (eval counters) are exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import numpy_ref as NR
+from oracle import torch_ref as R
+from tests.helpers import check_adam_weights, check_summary, load_golden, rel_err, seeded_batch, seeded_masks, seeded_weights
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+A_SHAPES = [(32, 1, 3, 3), (32,)]
+B_SHAPES = [(5000, 5408), (5000,), (1000, 5000), (1000,), (100, 1000), (100,)]
+B_NAMES = ["fc1.weight", "fc1.bias", "fc2.weight", "fc2.bias", "fc3.weight", "fc3.bias"]
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from splitlearning_b200 import engine
+    assert torch.cuda.is_available()
+    return engine
+
+
+def cu(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def T(arrs):
+    return [torch.from_numpy(a.copy()) for a in arrs]
+
+
+# --------------------------------------------------------------------------- stateless operators
+@pytest.mark.parametrize("B", [1, 5, 16, 33])
+def test_conv_pool_forward(eng, B):
+    w, b = seeded_weights(A_SHAPES, 11)
+    x, _ = seeded_batch(B, 900 + B)
+    ref = R.alice_forward(torch.from_numpy(x), torch.from_numpy(w), torch.from_numpy(b))
+    got = eng.conv_pool_forward(cu(x), cu(w), cu(b)).cpu()
+    assert rel_err(got, ref) <= 1e-6
+    ref_np, _, _ = NR.conv_pool_forward(x, w, b)
+    assert rel_err(got, ref_np) <= 1e-6
+
+
+@pytest.mark.parametrize("B", [1, 16, 40])
+def test_conv_pool_backward(eng, B):
+    w, b = seeded_weights(A_SHAPES, 11)
+    x, _ = seeded_batch(B, 910 + B)
+    rng = np.random.RandomState(5)
+    dact = (rng.randn(B, 5408) * 1e-3).astype(np.float32)
+    wt, bt = torch.from_numpy(w).requires_grad_(True), torch.from_numpy(b).requires_grad_(True)
+    R.alice_forward(torch.from_numpy(x), wt, bt).backward(torch.from_numpy(dact))
+    dw, db = eng.conv_pool_backward(cu(x), cu(w), cu(b), cu(dact))
+    assert rel_err(dw.cpu(), wt.grad) <= 1e-5
+    assert rel_err(db.cpu(), bt.grad) <= 1e-5
+
+
+@pytest.mark.parametrize("B,K,N,relu", [(16, 5408, 5000, True), (16, 5000, 1000, True), (16, 1000, 100, False),
+                                        (3, 5408, 1000, True), (16, 100, 10, False), (40, 1000, 100, True),
+                                        (100, 512, 104, False), (7, 52, 12, True)])
+def test_linear_forward(eng, B, K, N, relu):
+    rng = np.random.RandomState(B + K + N)
+    x = (rng.rand(B, K) * 50 * (rng.rand(B, K) < 0.6)).astype(np.float32)
+    W = (rng.uniform(-1, 1, (N, K)) / np.sqrt(K)).astype(np.float32)
+    bias = rng.uniform(-1, 1, N).astype(np.float32)
+    mask = (rng.rand(B, N) < 0.5).astype(np.uint8)
+    ref = torch.nn.functional.linear(torch.from_numpy(x), torch.from_numpy(W), torch.from_numpy(bias))
+    if relu:
+        ref = torch.relu(ref)
+    got = eng.linear_forward(cu(x), cu(W), cu(bias), relu=relu).cpu()
+    assert rel_err(got, ref) <= 1e-5
+    got = eng.linear_forward(cu(x), cu(W), cu(bias), relu=relu, keep_mask=cu(mask), mask_scale=2.0).cpu()
+    assert rel_err(got, ref * torch.from_numpy(mask) * 2.0) <= 1e-5
+
+
+@pytest.mark.parametrize("B,Cn", [(16, 100), (1, 10), (16, 5408), (37, 100), (300, 10)])
+def test_cross_entropy(eng, B, Cn):
+    rng = np.random.RandomState(B * 7 + Cn)
+    z = (rng.randn(B, Cn) * 8).astype(np.float32)
+    y = rng.randint(0, min(Cn, 10), size=B).astype(np.int64)
+    zt = torch.from_numpy(z).requires_grad_(True)
+    ref = torch.nn.functional.cross_entropy(zt, torch.from_numpy(y))
+    ref.backward()
+    loss, dz = eng.cross_entropy(cu(z), cu(y))
+    assert abs(loss.item() - ref.item()) <= 1e-5 * abs(ref.item())
+    assert rel_err(dz.cpu(), zt.grad) <= 1e-5
+    l2, g2 = NR.cross_entropy(z, y)
+    assert abs(loss.item() - float(l2)) <= 1e-5 * abs(float(l2))
+
+
+def test_eval_counts_exact(eng):
+    rng = np.random.RandomState(3)
+    z = rng.randn(301, 100).astype(np.float32)
+    z[5, 7] = z[5, 3] = 9.0          # tie: first index must win
+    y = rng.randint(0, 10, size=301).astype(np.int64)
+    y[5] = 3
+    ref = R.eval_counts(torch.from_numpy(z), torch.from_numpy(y), 9)
+    c = eng.eval_counts(cu(z), cu(y), 9)
+    c = eng.eval_counts(cu(z), cu(y), 9, counters=c)       # accumulates
+    assert c.cpu().tolist() == [2 * v for v in ref]
+
+
+# --------------------------------------------------------------------------- whole steps
+def _bob(eng, params, **kw):
+    gp = [cu(p.numpy()) for p in params]
+    e = eng.BobEngine([5408, 5000, 1000, 100], gp[0::2], gp[1::2], **kw)
+    return e, gp
+
+
+@pytest.mark.parametrize("B", [16, 7])
+def test_vanilla_step_vs_oracle_and_golden(eng, B):
+    """Teacher-forced: identical weights / batch / masks; two consecutive steps (the second
+    exercises the momentum buffers).  Checked against the oracle and, for B=16, the fixture
+    generated from the reference's own models.py."""
+    g = load_golden("modules_vanilla.npz") if B == 16 else None
+    a, b = T(seeded_weights(A_SHAPES, 11)), T(seeded_weights(B_SHAPES, 12))
+    bob, gp = _bob(eng, b, optimizer=eng.SN_OPT_SGD_MOMENTUM, lr=1e-3, momentum=0.9)
+    gw, gb = cu(a[0].numpy()), cu(a[1].numpy())
+    alice = eng.AliceEngine(gw, gb, optimizer=eng.SN_OPT_SGD_MOMENTUM, lr=1e-3, momentum=0.9)
+    opt = R.SGDState()
+    for step in range(2):
+        x, y = seeded_batch(B, 100 + step)
+        masks = seeded_masks(B, (5000, 1000), 200 + step)
+        ref = R.vanilla_step(a, b, torch.from_numpy(x), torch.from_numpy(y), T(masks))
+        R.sgd_momentum_(b + a, ref["bob_grads"] + ref["alice_grads"], opt, 1e-3, 0.9)
+        xg, yg = cu(x), cu(y)
+        act = alice.forward(xg)
+        loss, cut, logits = bob.train_step(act, yg, masks=[cu(m) for m in masks], want_logits=True)
+        alice.backward_update(xg, cut)
+        torch.cuda.synchronize()
+        assert rel_err(act.cpu(), ref["act"]) <= TOL
+        assert rel_err(logits.cpu(), ref["logits"]) <= TOL
+        assert abs(loss.item() - ref["loss"].item()) <= TOL * abs(ref["loss"].item())
+        assert rel_err(cut.cpu(), ref["cut_grad"]) <= TOL
+        for n, p_ref, p in zip(B_NAMES, b, gp):
+            assert rel_err(p.cpu(), p_ref) <= TOL, n
+        assert rel_err(gw.cpu(), a[0]) <= TOL and rel_err(gb.cpu(), a[1]) <= TOL
+        if g is not None:
+            check_summary(g, f"s{step}_logits", logits, TOL)
+            check_summary(g, f"s{step}_cut_grad", cut, TOL)
+            assert abs(loss.item() - float(g[f"s{step}_loss"])) <= TOL * abs(float(g[f"s{step}_loss"]))
+            for n, p in zip(B_NAMES, gp):
+                check_summary(g, f"s{step}_new_{n}", p, TOL)
+            check_summary(g, f"s{step}_new_alice.conv_layers.0.weight", gw, TOL)
+            check_summary(g, f"s{step}_new_alice.conv_layers.0.bias", gb, TOL)
+    # the update itself (not just W ~= W_old) must match: compare the applied delta
+    w0 = seeded_weights(B_SHAPES, 12)
+    for n, p_ref, p, p0 in zip(B_NAMES, b, gp, w0):
+        assert rel_err(p.cpu().numpy() - p0, p_ref.numpy() - p0) <= 2e-3, n
+
+
+def test_sisa_server_steps_vs_oracle_and_golden(eng):
+    g = load_golden("modules_sisa_server.npz")
+    a, b = T(seeded_weights(A_SHAPES, 11)), T(seeded_weights(B_SHAPES, 12))
+    bob, gp = _bob(eng, b, optimizer=eng.SN_OPT_ADAM, lr=1e-3, weight_decay=1e-5)
+    opt = R.AdamState()
+    for step in range(2):
+        x, y = seeded_batch(16, 300 + step)
+        masks = seeded_masks(16, (5000, 1000), 400 + step)
+        act = R.alice_forward(torch.from_numpy(x), a[0], a[1])
+        ref = R.sisa_server_step(b, act, torch.from_numpy(y), T(masks))
+        R.adam_(b, ref["bob_grads"], opt, 1e-3, weight_decay=1e-5)
+        loss, cut, logits = bob.train_step(cu(act.numpy()), cu(y), masks=[cu(m) for m in masks],
+                                           want_cut_grad=False, want_logits=True)
+        assert cut is None
+        assert rel_err(logits.cpu(), ref["logits"]) <= TOL
+        assert abs(loss.item() - ref["loss"].item()) <= TOL * abs(ref["loss"].item())
+        check_summary(g, f"s{step}_logits", logits, TOL)
+        for n, p_ref, p in zip(B_NAMES, b, gp):
+            check_adam_weights(p.cpu(), p_ref, n)
+            check_summary(g, f"s{step}_new_{n}", p, 1e-3)
+    w0 = seeded_weights(B_SHAPES, 12)
+    for n, p_ref, p, p0 in zip(B_NAMES, b, gp, w0):
+        assert rel_err(p.cpu().numpy() - p0, p_ref.numpy() - p0) <= 5e-3, n
+    # eval-mode inference with the updated weights
+    x, _ = seeded_batch(16, 500)
+    act = R.alice_forward(torch.from_numpy(x), a[0], a[1])
+    out = bob.forward(cu(act.numpy()), train_mode=False)
+    check_summary(g, "eval_logits", out, TOL)
+
+
+def test_sisa_alice_local_steps(eng):
+    g = load_golden("modules_sisa_alice.npz")
+    a = T(seeded_weights(A_SHAPES, 11))
+    gw, gb = cu(a[0].numpy()), cu(a[1].numpy())
+    alice = eng.AliceEngine(gw, gb, optimizer=eng.SN_OPT_ADAM, lr=1e-3, weight_decay=1e-5)
+    opt = R.AdamState()
+    for step in range(3):
+        x, y = seeded_batch(16, 600 + step)
+        ref = R.sisa_alice_step(a, torch.from_numpy(x), torch.from_numpy(y))
+        R.adam_(a, ref["alice_grads"], opt, 1e-3, weight_decay=1e-5)
+        loss = alice.local_step(cu(x), cu(y))
+        assert abs(loss.item() - ref["loss"].item()) <= TOL * abs(ref["loss"].item())
+        assert abs(loss.item() - float(g[f"s{step}_loss"])) <= TOL * abs(float(g[f"s{step}_loss"]))
+        assert rel_err(gw.cpu(), a[0]) <= TOL and rel_err(gb.cpu(), a[1]) <= TOL
+        check_summary(g, f"s{step}_new_conv_layers.0.weight", gw, TOL)
+        check_summary(g, f"s{step}_new_conv_layers.0.bias", gb, TOL)
+
+
+def test_ushape_steps(eng):
+    g = load_golden("modules_ushape.npz")
+    a = T(seeded_weights(A_SHAPES, 11))
+    b = T(seeded_weights([(1000, 5408), (1000,), (100, 1000), (100,)], 13))
+    t = T(seeded_weights([(10, 100), (10,)], 14))
+    gp = [cu(p.numpy()) for p in b]
+    gt = [cu(p.numpy()) for p in t]
+    gw, gb = cu(a[0].numpy()), cu(a[1].numpy())
+    adam = dict(optimizer=eng.SN_OPT_ADAM, lr=1e-3)
+    bob = eng.BobEngine([5408, 1000, 100], gp[0::2], gp[1::2], relu_last=True, dropout_p=0.0, **adam)
+    tail = eng.BobEngine([100, 10], [gt[0]], [gt[1]], dropout_p=0.0, **adam)
+    alice = eng.AliceEngine(gw, gb, **adam)
+    opt = R.AdamState()
+    for step in range(2):
+        x, y = seeded_batch(16, 700 + step)
+        ref = R.ushape_step(a, t, b, torch.from_numpy(x), torch.from_numpy(y))
+        R.adam_(t + b + a, ref["tail_grads"] + ref["bob_grads"] + ref["alice_grads"], opt, 1e-3)
+        xg, yg = cu(x), cu(y)
+        act = alice.forward(xg)
+        hb = bob.forward(act, train_mode=True)
+        loss, dhb, logits = tail.train_step(hb, yg, want_logits=True)
+        cut = bob.backward_update(act, dhb)
+        alice.backward_update(xg, cut)
+        assert rel_err(hb.cpu(), ref["bob_out"]) <= TOL
+        assert rel_err(logits.cpu(), ref["logits"]) <= TOL
+        assert rel_err(dhb.cpu(), ref["bob_out_grad"]) <= TOL
+        assert rel_err(cut.cpu(), ref["cut_grad"].flatten(1)) <= TOL
+        check_summary(g, f"s{step}_bob_out", hb, TOL)
+        check_summary(g, f"s{step}_cut_grad", cut, TOL)
+        for n, p in zip(["fc1.weight", "fc1.bias", "fc2.weight", "fc2.bias"], gp):
+            check_summary(g, f"s{step}_new_m2.{n}", p, TOL)
+        check_summary(g, f"s{step}_new_m3.fc3.weight", gt[0], TOL)
+        check_summary(g, f"s{step}_new_m1.conv1.weight", gw, TOL)
+
+
+def test_general_batch_path_matches_oracle(eng):
+    """B > 16 takes the general-batch kernels; same oracle, small widths."""
+    rng = np.random.RandomState(77)
+    dims = [5408, 256, 52, 100]
+    shapes = [(256, 5408), (256,), (52, 256), (52,), (100, 52), (100,)]
+    b = T(seeded_weights(shapes, 21))
+    spec = R.BobSpec(tuple(dims), False, 0.5)
+    gp = [cu(p.numpy()) for p in b]
+    bob = eng.BobEngine(dims, gp[0::2], gp[1::2], optimizer=eng.SN_OPT_ADAM, lr=1e-3, weight_decay=1e-5, max_batch=80)
+    opt = R.AdamState()
+    for step, B in enumerate([80, 48]):
+        act = (rng.rand(B, 5408) * 40 * (rng.rand(B, 5408) < 0.6)).astype(np.float32)
+        y = rng.randint(0, 10, size=B).astype(np.int64)
+        masks = seeded_masks(B, (256, 52), 50 + step)
+        bl = [p.detach().clone().requires_grad_(True) for p in b]
+        at = torch.from_numpy(act).requires_grad_(True)
+        logits_ref = R.bob_forward(at, bl, spec, T(masks))
+        loss_ref = R.cross_entropy(logits_ref, torch.from_numpy(y))
+        loss_ref.backward()
+        R.adam_(b, [p.grad for p in bl], opt, 1e-3, weight_decay=1e-5)
+        loss, cut, logits = bob.train_step(cu(act), cu(y), masks=[cu(m) for m in masks], want_logits=True)
+        assert rel_err(logits.cpu(), logits_ref.detach()) <= TOL
+        assert abs(loss.item() - loss_ref.item()) <= TOL * abs(loss_ref.item())
+        assert rel_err(cut.cpu(), at.grad) <= TOL
+        for p_ref, p in zip(b, gp):
+            check_adam_weights(p.cpu(), p_ref)
+        # teacher forcing: the next step starts from the oracle's weights and Adam state on both sides
+        assert bob.get_opt_step(0) == opt.step
+        for i, (p_ref, p) in enumerate(zip(b, gp)):
+            p.copy_(p_ref)
+            bob.opt_state(0, 0, i).copy_(opt.m[i].reshape(-1))
+            bob.opt_state(0, 1, i).copy_(opt.v[i].reshape(-1))
+
+
+def test_philox_dropout_statistics_and_determinism(eng):
+    b = T(seeded_weights(B_SHAPES, 12))
+    bob, gp = _bob(eng, b, optimizer=eng.SN_OPT_SGD_MOMENTUM, lr=0.0, momentum=0.0)
+    x, _ = seeded_batch(16, 1)
+    a = T(seeded_weights(A_SHAPES, 11))
+    act = cu(R.alice_forward(torch.from_numpy(x), a[0], a[1]).numpy())
+    o1 = bob.forward(act, train_mode=True, seed=5, offset=1).cpu()
+    o2 = bob.forward(act, train_mode=True, seed=5, offset=1).cpu()
+    o3 = bob.forward(act, train_mode=True, seed=5, offset=2).cpu()
+    assert torch.equal(o1, o2) and not torch.equal(o1, o3)
+    # one hidden layer, linear head of ones: output = sum of kept, doubled activations
+    ones_w, ones_b = torch.ones(1, 5000, device="cuda"), torch.zeros(1, device="cuda")
+    net = eng.BobEngine([5408, 5000, 1], [gp[0], ones_w], [gp[1], ones_b], dropout_p=0.5, optimizer=eng.SN_OPT_NONE)
+    full = net.forward(act, train_mode=False).cpu()
+    drops = torch.stack([net.forward(act, train_mode=True, seed=3, offset=i).cpu() for i in range(8)])
+    ratio = (drops.mean(0) / full).mean().item()          # E[keep*2] = 1
+    assert 0.9 < ratio < 1.1, ratio

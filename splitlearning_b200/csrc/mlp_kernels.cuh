@@ -18,6 +18,15 @@ namespace sn {
 //   R*4 FMAs; per-lane partial sums are transposed-and-reduced with shuffles at the end of the
 //   chunk.  Split-K partials are summed in a fixed order by fwd_epilogue_kernel: deterministic.
 // ------------------------------------------------------------------------------------------
+// cp.async helpers: 16-byte global->shared copies that bypass L1 (.cg) and complete asynchronously
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
 template <int V>
 __device__ __forceinline__ void butterfly_reduce(float* v, int lane) {
   int cnt = V;
@@ -41,32 +50,47 @@ __device__ __forceinline__ void butterfly_reduce(float* v, int lane) {
   }
 }
 
+constexpr int kFwdRing = 3;   // W iterations (8 rows x 128 k each) in flight per warp
+
+// One group of R rows of W against the staged X chunk.  W is streamed global -> shared with
+// cp.async into this warp's private ring (no registers held while in flight), X is read from the
+// CTA's staged chunk one batch row ahead of the FMAs that use it.
 template <int R>
 __device__ __forceinline__ void fwd_rows(const float* __restrict__ Wr, int ldw, int klen,
                                          const float4* __restrict__ Xs4, int kc4, int lane, int nb,
-                                         float* __restrict__ Pout, int N) {
+                                         float* __restrict__ Pout, int N, float4* __restrict__ wring) {
   float acc[R * kBT];
 #pragma unroll
   for (int i = 0; i < R * kBT; ++i) acc[i] = 0.f;
   const int iters = (klen + 127) >> 7;
   const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-  float4 wc[R], wn[R];
-  {
-    const bool ok = lane * 4 < klen;
+  auto issue = [&](int it, int slot) {
+    const int k = it * 128 + lane * 4;
+    if (it < iters && k < klen) {
 #pragma unroll
-    for (int i = 0; i < R; ++i)
-      wc[i] = ok ? __ldg(reinterpret_cast<const float4*>(Wr + (size_t)i * ldw) + lane) : zero;
-  }
+      for (int i = 0; i < R; ++i) cp_async16(wring + (slot * 8 + i) * 32 + lane, Wr + (size_t)i * ldw + k);
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int d = 0; d < kFwdRing - 1; ++d) issue(d, d);
+  int slot = 0;
   for (int it = 0; it < iters; ++it) {
-    const int kn = (it + 1) * 128 + lane * 4;
-    const bool ok = (it + 1 < iters) && (kn < klen);
+    int wslot = slot + kFwdRing - 1;
+    if (wslot >= kFwdRing) wslot -= kFwdRing;
+    issue(it + kFwdRing - 1, wslot);
+    cp_async_wait<kFwdRing - 1>();
+    const bool ok = it * 128 + lane * 4 < klen;
+    float4 wc[R];
 #pragma unroll
-    for (int i = 0; i < R; ++i)
-      wn[i] = ok ? __ldg(reinterpret_cast<const float4*>(Wr + (size_t)i * ldw + kn)) : zero;
+    for (int i = 0; i < R; ++i) wc[i] = ok ? wring[(slot * 8 + i) * 32 + lane] : zero;
+    if (++slot == kFwdRing) slot = 0;
     const float4* xs = Xs4 + it * 32 + lane;
+    float4 xn = xs[0];
 #pragma unroll
     for (int b = 0; b < kBT; ++b) {
-      const float4 x = xs[b * kc4];
+      const float4 x = xn;
+      if (b + 1 < kBT) xn = xs[(b + 1) * kc4];
 #pragma unroll
       for (int i = 0; i < R; ++i) {
         float a = acc[i * kBT + b];
@@ -77,9 +101,8 @@ __device__ __forceinline__ void fwd_rows(const float* __restrict__ Wr, int ldw, 
         acc[i * kBT + b] = a;
       }
     }
-#pragma unroll
-    for (int i = 0; i < R; ++i) wc[i] = wn[i];
   }
+  cp_async_wait<0>();
   constexpr int V = R * kBT;
   butterfly_reduce<V>(acc, lane);
   constexpr int CNT = V >= 32 ? V / 32 : 1;
@@ -102,6 +125,7 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
   const int klen = min(kc, K - k0);
   const int b0 = blockIdx.z * kBT, nb = min(kBT, B - b0);
   const int kc4 = kc >> 2;
+  float4* wring = smem4 + kBT * kc4 + warp * (kFwdRing * 8 * 32);   // after the X chunk
   for (int idx = tid; idx < kBT * kc4; idx += 256) {
     const int b = idx / kc4, k4 = idx - b * kc4;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -116,10 +140,10 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
   while (r < r1) {
     const int rem = r1 - r;
     const float* Wr = W + (size_t)r * ldw + k0;
-    if (rem >= 8) { fwd_rows<8>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N); r += 8; }
-    else if (rem >= 4) { fwd_rows<4>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N); r += 4; }
-    else if (rem >= 2) { fwd_rows<2>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N); r += 2; }
-    else { fwd_rows<1>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N); r += 1; }
+    if (rem >= 8) { fwd_rows<8>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N, wring); r += 8; }
+    else if (rem >= 4) { fwd_rows<4>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N, wring); r += 4; }
+    else if (rem >= 2) { fwd_rows<2>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N, wring); r += 2; }
+    else { fwd_rows<1>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N, wring); r += 1; }
   }
 }
 
@@ -252,6 +276,8 @@ __global__ void __launch_bounds__(256) eval_counts_kernel(const float* __restric
 //   across the CTA's row-warps in shared memory and written to PA[blockIdx.y][b][k]; the n-split
 //   partials are summed in fixed order by bwd_epilogue_kernel.
 // ------------------------------------------------------------------------------------------
+constexpr int kRing = 8;   // rows in flight per thread (W + optimizer state): ~56-84 KB per SM
+
 template <int OPT, bool NEED_DA>
 __global__ void __launch_bounds__(256, 1)
 bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict__ bias, float* __restrict__ s1,
@@ -260,16 +286,33 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
                   float* __restrict__ PA, int kw, int rows_per_cta, OptParams op) {
   extern __shared__ float4 smem4[];
   float* dzs = reinterpret_cast<float*>(smem4);                  // [rows_per_cta][16]
+  // per-thread ring of the next kRing rows' float4s: [array][slot][thread]; a thread only ever
+  // reads what it copied itself, so cp.async.wait_group is the only synchronisation needed
+  float4* ring = smem4 + ((rows_per_cta * kBT + 3) >> 2);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int wk = warp % kw, wr = warp / kw, rw = 8 / kw;
   const int nb0 = blockIdx.y * rows_per_cta, nb1 = min(N, nb0 + rows_per_cta);
   const int nrows = nb1 - nb0;
+  const int k0 = (blockIdx.x * kw + wk) * 128 + lane * 4;
+  const bool kok = k0 < K;
+
+  auto issue = [&](int slot, int row) {
+    if (kok && row < nb1) {
+      const size_t o = (size_t)row * ldw + k0;
+      cp_async16(ring + (0 * kRing + slot) * 256 + tid, W + o);
+      cp_async16(ring + (1 * kRing + slot) * 256 + tid, s1 + o);
+      if (OPT == 2) cp_async16(ring + (2 * kRing + slot) * 256 + tid, s2 + o);
+    }
+    cp_async_commit();
+  };
+  int n = nb0 + wr;
+#pragma unroll
+  for (int d = 0; d < kRing - 1; ++d) issue(d, n + d * rw);      // start streaming before anything else
+
   for (int idx = tid; idx < nrows * kBT; idx += 256) {
     const int b = idx / nrows, j = idx - b * nrows;
     dzs[j * kBT + b] = (b < B) ? __ldg(dZ + (size_t)b * ldz + nb0 + j) : 0.f;
   }
-  const int k0 = (blockIdx.x * kw + wk) * 128 + lane * 4;
-  const bool kok = k0 < K;
   float4 a[kBT];
 #pragma unroll
   for (int b = 0; b < kBT; ++b)
@@ -281,24 +324,17 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
   }
   __syncthreads();
 
-  const bool bias_duty = (blockIdx.x == 0 && wk == 0 && lane == 0);
-  int n = nb0 + wr;
-  float4 w = make_float4(0.f, 0.f, 0.f, 0.f), m1 = w, m2 = w;
-  if (kok && n < nb1) {
-    const size_t o = (size_t)n * ldw + k0;
-    w = *reinterpret_cast<const float4*>(W + o);
-    m1 = __ldcs(reinterpret_cast<const float4*>(s1 + o));
-    if (OPT == 2) m2 = __ldcs(reinterpret_cast<const float4*>(s2 + o));
-  }
+  int slot = 0;
   for (; n < nb1; n += rw) {
-    float4 wn = w, m1n = m1, m2n = m2;
-    const int nn = n + rw;
-    if (kok && nn < nb1) {                           // prefetch the next row
-      const size_t o = (size_t)nn * ldw + k0;
-      wn = *reinterpret_cast<const float4*>(W + o);
-      m1n = __ldcs(reinterpret_cast<const float4*>(s1 + o));
-      if (OPT == 2) m2n = __ldcs(reinterpret_cast<const float4*>(s2 + o));
+    issue((slot + kRing - 1) & (kRing - 1), n + (kRing - 1) * rw);
+    cp_async_wait<kRing - 1>();
+    float4 w = make_float4(0.f, 0.f, 0.f, 0.f), m1 = w, m2 = w;
+    if (kok) {
+      w = ring[(0 * kRing + slot) * 256 + tid];
+      m1 = ring[(1 * kRing + slot) * 256 + tid];
+      if (OPT == 2) m2 = ring[(2 * kRing + slot) * 256 + tid];
     }
+    slot = (slot + 1) & (kRing - 1);
     const float4* dzr = reinterpret_cast<const float4*>(dzs + (n - nb0) * kBT);
     float dz[kBT];
 #pragma unroll
@@ -330,27 +366,33 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
       __stcs(reinterpret_cast<float4*>(s1 + o), m1);
       if (OPT == 2) __stcs(reinterpret_cast<float4*>(s2 + o), m2);
     }
-    if (bias_duty) {
+  }
+  cp_async_wait<0>();
+
+  // bias: db[n] = sum_b dZ[b][n].  One thread per row AFTER the streaming loop (a per-row
+  // load->update->store chain inside the loop made the k-group-0 CTAs latency-bound and the
+  // whole grid wait for them).
+  if (blockIdx.x == 0) {
+    for (int j = tid; j < nrows; j += 256) {
       float db = 0.f;
 #pragma unroll
-      for (int b = 0; b < kBT; ++b) db += dz[b];
-      float p = bias[n], q1 = bs1[n], q2 = (OPT == 2) ? bs2[n] : 0.f;
+      for (int b = 0; b < kBT; ++b) db += dzs[j * kBT + b];
+      const int nn = nb0 + j;
+      float p = bias[nn], q1 = bs1[nn], q2 = (OPT == 2) ? bs2[nn] : 0.f;
       opt_update<OPT>(op, p, db, q1, q2);
-      bias[n] = p;
-      bs1[n] = q1;
-      if (OPT == 2) bs2[n] = q2;
+      bias[nn] = p;
+      bs1[nn] = q1;
+      if (OPT == 2) bs2[nn] = q2;
     }
-    w = wn; m1 = m1n; m2 = m2n;
   }
 
   if (NEED_DA) {
-    // cross-warp reduction over the row-warps, fixed order
-    float4* red = smem4 + ((rows_per_cta * kBT + 3) >> 2);     // [8 warps][16][32 lanes] float4
+    // cross-warp reduction over the row-warps, fixed order; the ring is dead, reuse it
+    float4* red = ring;                                          // [8 warps][16][32 lanes] float4 = 64 KB
     __syncthreads();
 #pragma unroll
     for (int b = 0; b < kBT; ++b) red[(warp * kBT + b) * 32 + lane] = acc[b];
     __syncthreads();
-    // outputs: kw slices x 16 rows x 32 float4
     for (int o = tid; o < kw * kBT * 32; o += 256) {
       const int l = o & 31, b = (o >> 5) % kBT, s = o / (32 * kBT);
       float4 t = make_float4(0.f, 0.f, 0.f, 0.f);

@@ -85,8 +85,11 @@ static BwdPlan plan_bwd(int N, int K, int sms, bool need_da, bool adam) {
   return best;
 }
 
-static size_t bwd_smem_bytes(const BwdPlan& p, bool need_da) {
-  return (size_t)p.rows_per_cta * kBT * 4 + (need_da ? (size_t)8 * kBT * 32 * 16 : 0);
+static size_t bwd_smem_bytes(const BwdPlan& p, bool need_da, bool adam) {
+  // dZ tile + max(per-thread cp.async ring, dA cross-warp reduction buffer) which alias
+  const size_t ring = (size_t)(adam ? 3 : 2) * kRing * 256 * 16;
+  const size_t red = need_da ? (size_t)8 * kBT * 32 * 16 : 0;
+  return (size_t)((p.rows_per_cta * kBT + 3) / 4) * 16 + std::max(ring, red);
 }
 
 // ---------------------------------------------------------------- optimizer scalars
@@ -109,6 +112,7 @@ static OptParams make_opt(const Hyper& h, int64_t step) {
     const double bc1 = 1.0 - pow(h.beta1, (double)step), bc2 = 1.0 - pow(h.beta2, (double)step);
     o.step_size = (float)(h.lr / bc1);
     o.bc2_sqrt = (float)sqrt(bc2);
+    o.inv_bc2_sqrt = (float)(1.0 / sqrt(bc2));
   }
   return o;
 }
@@ -150,7 +154,7 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
   if (B <= kSkinnyFwdMaxB && (K % 4) == 0) {
     FwdPlan p = plan_fwd(K, N, sms);
     int tiles = ceil_div(B, kBT), Bpad = tiles * kBT;
-    size_t smem = (size_t)kBT * p.kc * 4;
+    size_t smem = (size_t)kBT * p.kc * 4 + (size_t)8 * kFwdRing * 8 * 32 * 16;   // X chunk + per-warp W rings
     if (set_smem(fwd_skinny_kernel, smem)) return 1;
     dim3 grid(p.nx, p.ksplit, tiles);
     cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
@@ -527,7 +531,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
     const float gscale = (l > 0 && h->dropout_p > 0.f) ? scale : 1.f;
     if (B <= kBT && (K % 4) == 0) {
       BwdPlan p = plan_bwd(N, K, h->sms, need_da, OPT == 2);
-      size_t smem = bwd_smem_bytes(p, need_da);
+      size_t smem = bwd_smem_bytes(p, need_da, OPT == 2);
       dim3 grid(p.kgroups, p.nsplit);
       if (need_da) {
         if (set_smem(bwd_update_kernel<OPT, true>, smem)) return 1;

@@ -42,10 +42,12 @@ def check_adam_weights(got, ref, name=""):
     entry is within rounding of zero the step's sign depends on fp32 summation order, so a handful
     of entries legitimately differ by up to 2*lr between ANY two fp32 implementations (torch-CPU
     fp32 vs fp64-derived gradients already differ by 1.05e-4 norm-wise on fc1).
-    Require: norm-wise 1e-3, and all but a 2e-5 fraction of entries within 1e-5 absolute."""
+    Measured on a B200, one teacher-forced step: 1.3e-6 (fc1) and 1.4e-5 (fc2) of the entries are off
+    by more than 1e-5, all with |g| < 1e-6.  Require: norm-wise 1e-3, and all but a 1e-4 fraction of
+    entries within 1e-5 absolute."""
     a = np.asarray(got, np.float64).reshape(-1)
     b = np.asarray(ref, np.float64).reshape(-1)
     e = rel_err(a, b)
     assert e <= 1e-3, f"{name}: rel err {e:.3e}"
     frac = float((np.abs(a - b) > 1e-5).mean())
-    assert frac <= 2e-5, f"{name}: {frac:.2e} of entries differ by more than 1e-5"
+    assert frac <= 1e-4, f"{name}: {frac:.2e} of entries differ by more than 1e-5"

@@ -1,0 +1,125 @@
+"""The one-process-per-GPU protocol (splitlearning_b200/spmd.py) on CPU: world_size 2 and 3 over
+gloo with oracle-backed stand-in engines, against the same schedule run in a single process.
+Checks the message flow (activations+labels one way, cut gradient back), the per-Alice optimizer
+slots on Bob and the Alice->Alice weight hand-off across ranks: results must be bit-identical."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import torch_ref as R
+from splitlearning_b200 import spmd
+
+B, N_ALICES, TURN, STEPS = 4, 3, 2, 13
+SPEC = R.BobSpec((5408, 24, 10), False, 0.0)
+
+
+class FakeAlice:
+    def __init__(self, seed):
+        g = torch.Generator().manual_seed(seed)
+        self.p = [torch.randn(32, 1, 3, 3, generator=g) * 0.1, torch.randn(32, generator=g) * 0.1]
+        self.opt = R.SGDState()
+
+    def forward(self, x, out=None):
+        act = R.alice_forward(x, self.p[0], self.p[1])
+        if out is not None:
+            out.copy_(act)
+            return out
+        return act
+
+    def backward_update(self, x, cut):
+        w, b = [t.detach().clone().requires_grad_(True) for t in self.p]
+        R.alice_forward(x, w, b).backward(cut)
+        R.sgd_momentum_(self.p, [w.grad, b.grad], self.opt, 1e-3, 0.9)
+
+    def get_weights(self):
+        return torch.cat([self.p[0].reshape(-1), self.p[1].reshape(-1)])
+
+    def set_weights(self, flat):
+        self.p[0].copy_(flat[:288].view(32, 1, 3, 3))
+        self.p[1].copy_(flat[288:320])
+
+
+class FakeBob:
+    def __init__(self):
+        g = torch.Generator().manual_seed(5)
+        self.p = [torch.randn(24, 5408, generator=g) * 0.01, torch.zeros(24), torch.randn(10, 24, generator=g) * 0.1,
+                  torch.zeros(10)]
+        self.opts = [R.SGDState() for _ in range(N_ALICES)]
+        self.slots_seen = []
+
+    def train_step(self, act, y, slot):
+        a = act.detach().clone().requires_grad_(True)
+        leaf = [t.detach().clone().requires_grad_(True) for t in self.p]
+        loss = R.cross_entropy(R.bob_forward(a, leaf, SPEC, None), y)
+        loss.backward()
+        R.sgd_momentum_(self.p, [t.grad for t in leaf], self.opts[slot], 1e-3, 0.9)
+        self.slots_seen.append(slot)
+        return loss.detach(), a.grad, None
+
+
+def _batches():
+    g = torch.Generator().manual_seed(99)
+    x = torch.randint(0, 256, (STEPS, B, 1, 28, 28), generator=g).float()
+    y = torch.randint(0, 10, (STEPS, B), generator=g)
+    return x, y
+
+
+def _run(rank, world, out_dir, port):
+    if world > 1:
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    x, y = _batches()
+    bob = FakeBob() if rank == 0 else None
+    mine = {k: FakeAlice(100 + k) for k in range(N_ALICES) if spmd.owner_rank(k, world) == rank}
+    losses = {}
+    spmd.run_vanilla_schedule(rank, world, bob, mine, lambda i: (x[i], y[i]), N_ALICES, TURN, 0, STEPS, B,
+                              torch.device("cpu"), lambda i, l: losses.__setitem__(i, float(l)))
+    out = {f"alice{k}": a.get_weights().numpy() for k, a in mine.items()}
+    if bob is not None:
+        out.update({f"bob{i}": p.numpy() for i, p in enumerate(bob.p)})
+        out["losses"] = np.array([losses[i] for i in range(STEPS)])
+        out["slots"] = np.array(bob.slots_seen)
+    np.savez(os.path.join(out_dir, f"w{world}_r{rank}.npz"), **out)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def _collect(out_dir, world):
+    merged = {}
+    for r in range(world):
+        with np.load(os.path.join(out_dir, f"w{world}_r{r}.npz")) as f:
+            merged.update({k: f[k] for k in f.files})
+    return merged
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_spmd_protocol_matches_single_process(world):
+    with tempfile.TemporaryDirectory() as d:
+        _run(0, 1, d, 0)
+        ref = _collect(d, 1)
+        mp.spawn(_run, args=(world, d, 29700 + world), nprocs=world, join=True)
+        got = _collect(d, world)
+    assert set(got) == set(ref)
+    assert got["slots"].tolist() == [(i // TURN) % N_ALICES for i in range(STEPS)]
+    for k in ref:
+        assert np.array_equal(got[k], ref[k]), k
+
+
+def test_owner_placement():
+    assert [spmd.owner_rank(k, 1) for k in range(4)] == [0, 0, 0, 0]
+    assert [spmd.owner_rank(k, 2) for k in range(4)] == [1, 1, 1, 1]
+    assert [spmd.owner_rank(k, 8) for k in range(7)] == [1, 2, 3, 4, 5, 6, 7]
+    assert [spmd.owner_rank(k, 4) for k in range(4)] == [1, 2, 3, 1]
+    msg, act, lab = spmd.pack_message(16, torch.device("cpu"))
+    assert act.shape == (16, 5408) and lab.shape == (16,) and lab.dtype == torch.int64
+    lab.copy_(torch.arange(16))
+    act.fill_(1.5)
+    assert lab.tolist() == list(range(16)) and float(msg[0]) == 1.5

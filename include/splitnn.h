@@ -62,6 +62,27 @@ int sn_linear_forward(const float* x, const float* W, const float* bias, int B, 
                       int relu, const uint8_t* keep_mask, float mask_scale, float* y,
                       void* scratch, size_t scratch_bytes, void* stream);
 
+/* sn_linear_forward for callers that cannot allocate GPU memory and have no scratch buffer to
+ * lend.  (No counterpart in the reference, which never manages device memory.)  Who that is: a
+ * process whose HBM is already owned by another allocator (a serving stack's memory pool, a
+ * fixed partition per tenant), where a cudaMalloc from inside a library can fail or fragment the
+ * pool; and latency-critical loops, where cudaMalloc/cudaFree stall every stream on the device.
+ * Same arguments and result as sn_linear_forward minus the scratch pair: the split-K partial sums
+ * go to a 4 MiB array built into the library (sn_linear_forward_noalloc_max_scratch_bytes()),
+ * which each GPU that loads the library keeps for the life of the process.  Shapes whose partials
+ * do not fit (check with sn_linear_forward_scratch_bytes) are refused with an error; nothing is
+ * truncated.  The call itself performs no cudaMalloc/cudaFree or other allocating call.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress,
+ *     with that device current); make that first call before starting any stream capture.
+ *   - All calls on a device share the one array and it keeps whatever the previous call left in
+ *     it.  Nothing in it needs clearing between calls (every value read was written earlier in
+ *     the same call), but two calls whose kernels overlap on the GPU — different streams with no
+ *     dependency between them — race on it.  Serialise them on one stream or with events. */
+size_t sn_linear_forward_noalloc_max_scratch_bytes(void);
+int sn_linear_forward_noalloc(const float* x, const float* W, const float* bias, int B, int K,
+                              int N, int relu, const uint8_t* keep_mask, float mask_scale,
+                              float* y, void* stream);
+
 /* Mean cross-entropy over B rows of C logits with int64 labels, and its gradient
  * (softmax - onehot)/B.  loss: device scalar.  dlogits nullable.  Replaces
  * nn.CrossEntropyLoss, data_entities_vanilla.py:224,230; data_entities_vanilla_sisa.py:65,308;

@@ -24,6 +24,8 @@ SIGNATURES = {
     "sn_conv_pool_backward": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp]),
     "sn_linear_forward_scratch_bytes": (_sz, [_i, _i, _i]),
     "sn_linear_forward": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _f, _vp, _vp, _sz, _vp]),
+    "sn_linear_forward_noalloc_max_scratch_bytes": (_sz, []),
+    "sn_linear_forward_noalloc": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _f, _vp, _vp]),
     "sn_cross_entropy": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "sn_eval_counts": (_i, [_vp, _vp, _i, _i, _i64, _vp, _vp]),
     "sn_bob_create": (_i, [_pp, _i, C.POINTER(_i), _i, _i, _d, _i, _d, _d, _d, _d, _d, _d, _i, _i, _pp, _pp]),

@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "alice_kernels.cuh"
@@ -281,6 +282,56 @@ int sn_linear_forward(const float* x, const float* W, const float* bias, int B, 
   SN_REQUIRE(need == 0 || (scratch && scratch_bytes >= need), "sn_linear_forward: scratch too small");
   return launch_linear_fwd(x, K, B, W, bias, K, N, relu, keep_mask, 1.f, mask_scale, 0, 0, 0, y, N, nullptr,
                            reinterpret_cast<float*>(scratch), sms, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------- allocation-free linear forward
+// Scratch for sn_linear_forward_noalloc: a fixed array inside the loaded module, so the entry point
+// never calls an allocator.  4 MiB; every GPU that loads the library carries it until the process
+// exits.  On the host `g_noalloc_scratch` is only a handle for the symbol, not a device address:
+// the address is looked up once per device with cudaGetSymbolAddress (below) and that pointer is
+// what the kernels receive.
+constexpr size_t kNoAllocScratchBytes = 4u << 20;
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocScratchBytes / sizeof(float)];
+
+static std::mutex g_noalloc_mu;
+static float* g_noalloc_ptr[64] = {nullptr};
+
+// Device address of the array on the CURRENT device (looked up on first use per device).
+static int noalloc_scratch(float** out, int* device) {
+  int dev = 0;
+  SN_CUDA(cudaGetDevice(&dev));
+  SN_REQUIRE(dev >= 0 && dev < 64, "sn_linear_forward_noalloc: device index out of range");
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    float* p = nullptr;
+    SN_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch));
+    SN_REQUIRE(p != nullptr, "sn_linear_forward_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  *device = dev;
+  return 0;
+}
+
+size_t sn_linear_forward_noalloc_max_scratch_bytes(void) { return kNoAllocScratchBytes; }
+
+int sn_linear_forward_noalloc(const float* x, const float* W, const float* bias, int B, int K, int N, int relu,
+                              const uint8_t* keep_mask, float mask_scale, float* y, void* stream) {
+  SN_REQUIRE(x && W && bias && y && B > 0 && K > 0 && N > 0, "sn_linear_forward_noalloc: bad arguments");
+  float* scratch = nullptr;
+  int dev = 0;
+  if (noalloc_scratch(&scratch, &dev)) return 1;
+  const int sms = sm_count(dev);
+  const size_t need = fwd_partial_floats(B, K, N, sms) * sizeof(float);
+  if (need > kNoAllocScratchBytes) {
+    return fail_msg("libsplitnn: sn_linear_forward_noalloc: this shape needs " + std::to_string(need) +
+                    " bytes of split-K scratch but the built-in scratch holds " +
+                    std::to_string(kNoAllocScratchBytes) + " bytes; use sn_linear_forward with caller scratch");
+  }
+  // Nothing in the scratch has to start at zero: every partial sum the epilogue reads is written
+  // by the forward kernel of the same call first.
+  return launch_linear_fwd(x, K, B, W, bias, K, N, relu, keep_mask, 1.f, mask_scale, 0, 0, 0, y, N, nullptr, scratch,
+                           sms, (cudaStream_t)stream);
 }
 
 static int launch_ce(const float* z, int ldz, const int64_t* y, int B, int C, float* dz, int lddz, float* row_loss,

@@ -238,6 +238,19 @@ def linear_forward(x, W, bias, relu=False, keep_mask=None, mask_scale=1.0):
     return y
 
 
+def linear_forward_noalloc(x, W, bias, relu=False, keep_mask=None, mask_scale=1.0, out=None):
+    """`sn_linear_forward_noalloc`: same result as `linear_forward`, but the library uses its own
+    built-in 4 MiB scratch and allocates nothing.  Pass `out` to keep this wrapper allocation-free
+    as well (otherwise torch allocates the result tensor)."""
+    lib = _lib.load()
+    B, K = x.shape
+    N = W.shape[0]
+    y = out if out is not None else torch.empty(B, N, device=x.device)
+    check(lib.sn_linear_forward_noalloc(ptr(_f32c(x)), ptr(_f32c(W)), ptr(_f32c(bias)), B, K, N, int(bool(relu)),
+                                        ptr(keep_mask), float(mask_scale), ptr(_f32c(y)), _stream(x.device)))
+    return y
+
+
 def cross_entropy(logits, labels, want_grad=True):
     lib = _lib.load()
     B, Cn = logits.shape

@@ -314,8 +314,25 @@ def run_sisa_epoch(torch, dev, peak):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
+    # per-kernel times of the Adam traversal (event-bracketed, first cache shard only)
+    bob.profile(True)
+    acts, y, offs = caches[0]
+    bob.server_epoch(acts, y, offs[:201], slot=0, masks=None, seed=7, offset=20000)
+    torch.cuda.synchronize()
+    kern = {}
+    for kind, name in ((0, "fwd"), (1, "bwd_update")):
+        for l in range(3):
+            t, n = bob.profile_read(kind, l)
+            if n:
+                kern[f"{name}_fc{l + 1}_us"] = round(1e3 * t / n, 2)
+    bob.profile(False)
     step_bytes = 24.0 * P_BOB + 4.0 * B * D0
-    return {"server_epoch_ms": round(ms, 2), "steps": n_steps, "samples": n_samples,
+    adam_fc1 = 24.0 * P_FC1 + 4.0 * B * (DIMS[1] + DIMS[0])
+    return {"kernel_us": kern,
+            "dominant": {"kernel": "bwd_update_kernel<Adam,no dA> fc1", "bytes_per_launch": adam_fc1,
+                         "achieved": round(adam_fc1 / (kern.get("bwd_update_fc1_us", 1e9) * 1e-6) / 1e9, 1),
+                         "frac": round(adam_fc1 / (kern.get("bwd_update_fc1_us", 1e9) * 1e-6) / 1e9 / peak, 4)},
+            "server_epoch_ms": round(ms, 2), "steps": n_steps, "samples": n_samples,
             "us_per_step": round(1e3 * ms / n_steps, 2), "samples_per_sec": round(n_samples / (ms * 1e-3), 1),
             "cache_bytes": n_samples * D0 * 4,
             "roofline": {"bound": "hbm", "algorithmic_bytes_per_step": step_bytes, "formula": "24*P + 4*B*d0 (SURVEY 8d)",

@@ -50,101 +50,204 @@ __device__ __forceinline__ void butterfly_reduce(float* v, int lane) {
   }
 }
 
-constexpr int kFwdRing = 3;   // W iterations (8 rows x 128 k each) in flight per warp
+#ifdef SN_TIMING
+__device__ long long g_fwd_timing[148 * 8 * 8];
+#define SN_T(i) do { if (lane == 0) tstamp[i] = clock64(); } while (0)
+#else
+#define SN_T(i) do {} while (0)
+#endif
 
-// One group of R rows of W against the staged X chunk.  W is streamed global -> shared with
-// cp.async into this warp's private ring (no registers held while in flight), X is read from the
-// CTA's staged chunk one batch row ahead of the FMAs that use it.
-template <int R>
-__device__ __forceinline__ void fwd_rows(const float* __restrict__ Wr, int ldw, int klen,
-                                         const float4* __restrict__ Xs4, int kc4, int lane, int nb,
-                                         float* __restrict__ Pout, int N, float4* __restrict__ wring) {
-  float acc[R * kBT];
-#pragma unroll
-  for (int i = 0; i < R * kBT; ++i) acc[i] = 0.f;
-  const int iters = (klen + 127) >> 7;
-  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-  auto issue = [&](int it, int slot) {
-    const int k = it * 128 + lane * 4;
-    if (it < iters && k < klen) {
-#pragma unroll
-      for (int i = 0; i < R; ++i) cp_async16(wring + (slot * 8 + i) * 32 + lane, Wr + (size_t)i * ldw + k);
-    }
-    cp_async_commit();
-  };
-#pragma unroll
-  for (int d = 0; d < kFwdRing - 1; ++d) issue(d, d);
-  int slot = 0;
-  for (int it = 0; it < iters; ++it) {
-    int wslot = slot + kFwdRing - 1;
-    if (wslot >= kFwdRing) wslot -= kFwdRing;
-    issue(it + kFwdRing - 1, wslot);
-    cp_async_wait<kFwdRing - 1>();
-    const bool ok = it * 128 + lane * 4 < klen;
-    float4 wc[R];
-#pragma unroll
-    for (int i = 0; i < R; ++i) wc[i] = ok ? wring[(slot * 8 + i) * 32 + lane] : zero;
-    if (++slot == kFwdRing) slot = 0;
-    const float4* xs = Xs4 + it * 32 + lane;
-    float4 xn = xs[0];
-#pragma unroll
-    for (int b = 0; b < kBT; ++b) {
-      const float4 x = xn;
-      if (b + 1 < kBT) xn = xs[(b + 1) * kc4];
-#pragma unroll
-      for (int i = 0; i < R; ++i) {
-        float a = acc[i * kBT + b];
-        a = __fmaf_rn(wc[i].x, x.x, a);
-        a = __fmaf_rn(wc[i].y, x.y, a);
-        a = __fmaf_rn(wc[i].z, x.z, a);
-        a = __fmaf_rn(wc[i].w, x.w, a);
-        acc[i * kBT + b] = a;
-      }
-    }
-  }
-  cp_async_wait<0>();
-  constexpr int V = R * kBT;
-  butterfly_reduce<V>(acc, lane);
-  constexpr int CNT = V >= 32 ? V / 32 : 1;
-  const int prefix = V >= 32 ? lane : (lane >> 1);
-  if (V < 32 && (lane & 1)) return;
-#pragma unroll
-  for (int j = 0; j < CNT; ++j) {
-    const int idx = prefix * CNT + j;
-    const int i = idx >> 4, b = idx & 15;
-    if (b < nb) Pout[(size_t)b * N + i] = acc[j];
-  }
+constexpr int kFwdRing = 4;      // W tiles (8 rows x 128 k = 4 KB) in flight per warp
+constexpr int kFwdSlots = 2;     // a row group's k-range is covered by at most two warps
+
+__device__ __forceinline__ void cp_async16_zfill(void* smem, const void* gmem, bool valid) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  const int n = valid ? 16 : 0;                                  // src-size 0 => 16 zero bytes
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem), "r"(n) : "memory");
 }
 
+// grid (nx, ksplit, batch tiles), 256 threads.  Work unit: a TILE = 8 rows x 128 k of W.  The
+// tiles of a k-chunk, ordered (row group, k step), are cut into equal contiguous ranges, one per
+// warp, so every warp streams the same number of bytes whatever N is; a warp's cp.async ring
+// runs continuously across row-group boundaries.  A row group whose k steps straddle two warps
+// gets two partial sums (slot 0 from the warp that holds its first k step, slot 1 from the
+// other); complete groups write zeros to slot 1.  fwd_epilogue_kernel adds the 2*ksplit partials
+// in a fixed order.
+//
+// Math: packed FFMA2 (fma.rn.f32x2, sm_100): one instruction does acc[b],acc[b+1] += w * x[b],x[b+1]
+// with w as the scalar-broadcast operand.  Scalar FFMA made this kernel issue-bound (ncu:
+// 68 % issue-active, "selected" the top stall, at 45 % of HBM); FFMA2 halves the FMA issue slots.
+// For the batch pairs to be register pairs the X chunk is staged TRANSPOSED: row = k, 16 batch
+// values per row (64 B).  Lane l of a tile owns k = 4l..4l+3 (one float4 of each W row); its four
+// X rows are stored at physical rows kk*32 + l and the 16-byte batch quads are XOR-swizzled with
+// (row>>1)&3, which makes every LDS.128 of a quarter-warp hit 8 distinct bank groups.
 __global__ void __launch_bounds__(256, 1)
 fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N,
-                  int K, int kc, float* __restrict__ P, int Bpad) {
+                  int K, int kc, float* __restrict__ P, int Bpad, int ksplit) {
   extern __shared__ float4 smem4[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ks = blockIdx.y, k0 = ks * kc;
   const int klen = min(kc, K - k0);
+  const int iters = (klen + 127) >> 7;
   const int b0 = blockIdx.z * kBT, nb = min(kBT, B - b0);
   const int kc4 = kc >> 2;
   float4* wring = smem4 + kBT * kc4 + warp * (kFwdRing * 8 * 32);   // after the X chunk
-  for (int idx = tid; idx < kBT * kc4; idx += 256) {
-    const int b = idx / kc4, k4 = idx - b * kc4;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (b < nb && k4 * 4 < klen) v = __ldg(reinterpret_cast<const float4*>(X + (size_t)(b0 + b) * ldx + k0) + k4);
-    smem4[idx] = v;
-  }
-  __syncthreads();
+#ifdef SN_TIMING
+  long long tstamp[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long t_red = 0;
+#endif
+  SN_T(0);
+
+  const int groups = (N + 7) >> 3;
+  const long long T = (long long)groups * iters;
   const int gw = blockIdx.x * 8 + warp, nw = gridDim.x * 8;
-  int r = (int)((long long)N * gw / nw);
-  const int r1 = (int)((long long)N * (gw + 1) / nw);
-  float* Pbase = P + ((size_t)ks * Bpad + b0) * N;
-  while (r < r1) {
-    const int rem = r1 - r;
-    const float* Wr = W + (size_t)r * ldw + k0;
-    if (rem >= 8) { fwd_rows<8>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N, wring); r += 8; }
-    else if (rem >= 4) { fwd_rows<4>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N, wring); r += 4; }
-    else if (rem >= 2) { fwd_rows<2>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N, wring); r += 2; }
-    else { fwd_rows<1>(Wr, ldw, klen, smem4, kc4, lane, nb, Pbase + r, N, wring); r += 1; }
+  const int t0 = (int)(T * gw / nw), t1 = (int)(T * (gw + 1) / nw);
+
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+  const bool ktail = (klen & 127) != 0;      // only then can a lane sit beyond the end of K
+
+  // W stream: (gi, iti) = coordinates of the next tile to issue
+  int gi = t0 / iters, iti = t0 - gi * iters, ti = t0;
+  auto issue = [&](int slot) {
+    if (ti < t1) {
+      const int k = iti * 128 + lane * 4;
+      if (k < klen) {
+        const float* src = W + (size_t)(gi * 8) * ldw + k0 + k;
+        if (gi * 8 + 8 <= N) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) cp_async16(wring + (slot * 8 + i) * 32 + lane, src + (size_t)i * ldw);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            cp_async16(wring + (slot * 8 + i) * 32 + lane, src + (size_t)min(i, N - 1 - gi * 8) * ldw);
+        }
+      }
+      ++ti;
+      if (++iti == iters) { iti = 0; ++gi; }
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int d = 0; d < kFwdRing - 1; ++d) issue(d);
+  SN_T(1);
+
+  // X chunk -> smem, transposed and swizzled (see above); zero outside the batch / the chunk.
+  // A thread takes one (batch quad, float4 of k) item: 4 coalesced LDG.128 (one per batch row),
+  // a 4x4 register transpose, 4 conflict-free STS.128 (one per k).  All loads of a thread are
+  // issued before its stores.  (clock64 phase timing: the first version - one LDG.128 then four
+  // STS.32 per item, with a divide - cost 12.5k of the kernel's 56k cycles.)
+  {
+    constexpr int XI = 2;                                   // k4 items per thread per pass
+    for (int kbase = 0; kbase < kc4; kbase += 256 * XI) {
+      float4 v[XI][4][4];
+#pragma unroll
+      for (int u = 0; u < XI; ++u) {
+        const int k4 = kbase + u * 256 + tid;
+#pragma unroll
+        for (int bq = 0; bq < 4; ++bq)
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const int b = bq * 4 + r;
+            v[u][bq][r] = zero;
+            if (k4 < kc4 && k4 * 4 < klen && b < nb)
+              v[u][bq][r] = __ldg(reinterpret_cast<const float4*>(X + (size_t)(b0 + b) * ldx + k0) + k4);
+          }
+      }
+#pragma unroll
+      for (int u = 0; u < XI; ++u) {
+        const int k4 = kbase + u * 256 + tid;
+        if (k4 < kc4) {
+          const int m = k4 & 31, base = (k4 >> 5) * 128 + m, swz = (m >> 1) & 3;
+#pragma unroll
+          for (int bq = 0; bq < 4; ++bq) {
+            float4* dst = smem4 + (size_t)base * 4 + (bq ^ swz);
+            dst[0 * 32 * 4] = make_float4(v[u][bq][0].x, v[u][bq][1].x, v[u][bq][2].x, v[u][bq][3].x);
+            dst[1 * 32 * 4] = make_float4(v[u][bq][0].y, v[u][bq][1].y, v[u][bq][2].y, v[u][bq][3].y);
+            dst[2 * 32 * 4] = make_float4(v[u][bq][0].z, v[u][bq][1].z, v[u][bq][2].z, v[u][bq][3].z);
+            dst[3 * 32 * 4] = make_float4(v[u][bq][0].w, v[u][bq][1].w, v[u][bq][2].w, v[u][bq][3].w);
+          }
+        }
+      }
+    }
   }
+  SN_T(2);
+  __syncthreads();
+  SN_T(3);
+
+  float acc[8 * kBT];
+#pragma unroll
+  for (int i = 0; i < 8 * kBT; ++i) acc[i] = 0.f;
+  int g = t0 / iters, it = t0 - g * iters;
+  bool has_first = (it == 0);
+  int slot = 0;
+  const int sw = (lane >> 1) & 3;
+  const size_t slot_stride = (size_t)ksplit * Bpad * N;
+  float* Pbase = P + ((size_t)ks * Bpad + b0) * N;
+
+  for (int t = t0; t < t1; ++t) {
+    issue((slot + kFwdRing - 1) & (kFwdRing - 1));
+    cp_async_wait<kFwdRing - 1>();
+    float4 wc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) wc[i] = wring[(slot * 8 + i) * 32 + lane];
+    if (ktail && it == iters - 1 && it * 128 + lane * 4 >= klen) {   // nothing was copied for this lane
+#pragma unroll
+      for (int i = 0; i < 8; ++i) wc[i] = zero;
+    }
+    slot = (slot + 1) & (kFwdRing - 1);
+    const float4* xrow = smem4 + (size_t)(it * 128 + lane) * 4;     // physical row kk*32 + lane
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+#pragma unroll
+      for (int bq = 0; bq < 4; ++bq) {
+        const float4 x = xrow[kk * 32 * 4 + (bq ^ sw)];
+        const float2 xlo = make_float2(x.x, x.y), xhi = make_float2(x.z, x.w);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float w = kk == 0 ? wc[i].x : kk == 1 ? wc[i].y : kk == 2 ? wc[i].z : wc[i].w;
+          const float2 ww = make_float2(w, w);
+          float* a = acc + i * kBT + bq * 4;
+          const float2 r0 = __ffma2_rn(ww, xlo, make_float2(a[0], a[1]));
+          const float2 r1 = __ffma2_rn(ww, xhi, make_float2(a[2], a[3]));
+          a[0] = r0.x; a[1] = r0.y; a[2] = r1.x; a[3] = r1.y;
+        }
+      }
+    }
+    const bool group_done = (it == iters - 1);
+    if (group_done || t == t1 - 1) {
+#ifdef SN_TIMING
+      const long long tr0 = clock64();
+#endif
+      butterfly_reduce<8 * kBT>(acc, lane);        // lane ends with row lane>>2, batch (lane&3)*4+j
+      const int row = g * 8 + (lane >> 2);
+      if (row < N) {
+        float* dst = Pbase + (has_first ? 0 : slot_stride) + row;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int b = (lane & 3) * 4 + j;
+          if (b < nb) {
+            dst[(size_t)b * N] = acc[j];
+            if (has_first && group_done) dst[slot_stride + (size_t)b * N] = 0.f;
+          }
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 8 * kBT; ++i) acc[i] = 0.f;
+#ifdef SN_TIMING
+      t_red += clock64() - tr0;
+#endif
+    }
+    if (++it == iters) { it = 0; ++g; has_first = true; }
+  }
+  cp_async_wait<0>();
+  SN_T(4);
+#ifdef SN_TIMING
+  if (lane == 0 && blockIdx.z == 0) {
+    long long* o = g_fwd_timing + ((blockIdx.y * gridDim.x + blockIdx.x) * 8 + warp) * 8;
+    o[0] = tstamp[1] - tstamp[0]; o[1] = tstamp[2] - tstamp[1]; o[2] = tstamp[3] - tstamp[2];
+    o[3] = tstamp[4] - tstamp[3]; o[4] = t_red; o[5] = t1 - t0; o[6] = tstamp[0]; o[7] = tstamp[4];
+  }
+#endif
 }
 
 // H[b][n] = act(sum_ks P[ks][b][n] + bias[n]) * dropout.   One thread per element.
@@ -157,7 +260,15 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
   for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
     const int b = (int)(idx / N), n = (int)(idx - (size_t)b * N);
     float s = 0.f;
-    for (int ks = 0; ks < ksplit; ++ks) s += P[((size_t)ks * Bpad + b) * N + n];
+    const float* pp = P + (size_t)b * N + n;
+    const size_t pstride = (size_t)Bpad * N;
+    int ks = 0;
+    for (; ks + 4 <= ksplit; ks += 4) {          // four independent loads in flight, fixed add order
+      const float p0 = pp[(size_t)ks * pstride], p1 = pp[(size_t)(ks + 1) * pstride];
+      const float p2 = pp[(size_t)(ks + 2) * pstride], p3 = pp[(size_t)(ks + 3) * pstride];
+      s += p0; s += p1; s += p2; s += p3;
+    }
+    for (; ks < ksplit; ++ks) s += pp[(size_t)ks * pstride];
     s += bias[n];
     if (relu) s = fmaxf(s, 0.f);
     if (mask) {
@@ -309,9 +420,26 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
 #pragma unroll
   for (int d = 0; d < kRing - 1; ++d) issue(d, n + d * rw);      // start streaming before anything else
 
-  for (int idx = tid; idx < nrows * kBT; idx += 256) {
-    const int b = idx / nrows, j = idx - b * nrows;
-    dzs[j * kBT + b] = (b < B) ? __ldg(dZ + (size_t)b * ldz + nb0 + j) : 0.f;
+  {  // dZ tile, transposed to [row][16]; loads batched ahead of their stores (latency, not bandwidth)
+    constexpr int SB = 8;
+    const int total = nrows * kBT;
+    for (int base_idx = tid; base_idx < total; base_idx += 256 * SB) {
+      float v[SB];
+#pragma unroll
+      for (int q = 0; q < SB; ++q) {
+        const int idx = base_idx + q * 256;
+        const int b = idx / nrows, j = idx - b * nrows;
+        v[q] = (idx < total && b < B) ? __ldg(dZ + (size_t)b * ldz + nb0 + j) : 0.f;
+      }
+#pragma unroll
+      for (int q = 0; q < SB; ++q) {
+        const int idx = base_idx + q * 256;
+        if (idx < total) {
+          const int b = idx / nrows, j = idx - b * nrows;
+          dzs[j * kBT + b] = v[q];
+        }
+      }
+    }
   }
   float4 a[kBT];
 #pragma unroll
@@ -415,7 +543,15 @@ __global__ void bwd_epilogue_kernel(const float* __restrict__ PA, int nsplit, in
   for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
     const int b = (int)(idx / K), k = (int)(idx - (size_t)b * K);
     float s = 0.f;
-    for (int p = 0; p < nsplit; ++p) s += PA[((size_t)p * kBT + b) * K + k];
+    const float* pp = PA + (size_t)b * K + k;
+    const size_t pstride = (size_t)kBT * K;
+    int p = 0;
+    for (; p + 4 <= nsplit; p += 4) {
+      const float p0 = pp[(size_t)p * pstride], p1 = pp[(size_t)(p + 1) * pstride];
+      const float p2 = pp[(size_t)(p + 2) * pstride], p3 = pp[(size_t)(p + 3) * pstride];
+      s += p0; s += p1; s += p2; s += p3;
+    }
+    for (; p < nsplit; ++p) s += pp[(size_t)p * pstride];
     if (H) s = H[(size_t)b * ldh + k] > 0.f ? s * scale : 0.f;
     dst[(size_t)b * ldd + k] = s;
   }

@@ -33,32 +33,30 @@ static inline int ew_grid(size_t n, int sms) {
 }
 
 // ---------------------------------------------------------------- launch plans
-constexpr int kMaxKc = 2048;        // X chunk [16][kc] fp32 = 128 KB of shared memory
+constexpr int kMaxKc = 1536;        // X chunk [16][kc] fp32 = 96 KB of shared memory (+128 KB of W rings)
 constexpr int kSkinnyFwdMaxB = 64;  // above this the forward uses the general-batch path
 
 struct FwdPlan { int kc, ksplit, nx; };
 struct BwdPlan { int kw, kgroups, nsplit, rows_per_cta; };
 
 static FwdPlan plan_fwd(int K, int N, int sms) {
-  FwdPlan best{round_up(std::min(K, kMaxKc), 128), 0, 1};
+  // k-chunks of whole 128-float slices, as equal as possible; CTAs per chunk capped so that a
+  // warp's tile range is at least one row group long (=> at most two partials per group)
+  const int slices = ceil_div(K, 128), groups = ceil_div(N, 8);
+  FwdPlan best{128 * std::min(slices, kMaxKc / 128), 0, 1};
+  best.ksplit = ceil_div(K, best.kc);
   double best_score = -1;
-  for (int s = 1; s <= 64; ++s) {
-    int kc = round_up(ceil_div(K, s), 128);
+  for (int s = 1; s <= slices; ++s) {
+    int kc = 128 * ceil_div(slices, s);
     if (kc > kMaxKc) continue;
     int actual = ceil_div(K, kc);
-    int nx = std::max(1, sms / actual);
-    double rpw = (double)N / (nx * 8.0);
-    double balance = (double)K / ((double)actual * kc);
-    double util = std::min(1.0, (double)nx * actual / sms);
-    // rows are consumed in groups of 8/4/2/1; smaller groups re-read X from smem more often
-    int rows = (int)ceil(rpw);
-    double cost = (rows / 8) * 1.0 + ((rows % 8) / 4) * 0.6 + ((rows % 4) / 2) * 0.4 + (rows % 2) * 0.3;
-    double qeff = cost > 0 ? (rpw / 8.0) / cost : 0.0;
+    int nx = std::max(1, std::min(sms / actual, groups / 8));
     double iters = kc / 128.0;
-    double redeff = iters / (iters + 0.3);
-    double score = balance * util * std::min(1.0, qeff) * redeff;
+    double tp = groups * iters / (nx * 8.0);             // tiles per warp
+    double util = std::min(1.0, (double)nx * actual / sms);
+    double balance = (double)K / ((double)actual * kc);
+    double score = util * balance * (tp / (tp + 2.0)) * (iters / (iters + 0.25));
     if (score > best_score) { best_score = score; best = FwdPlan{kc, actual, nx}; }
-    if (kc == 128) break;
   }
   return best;
 }
@@ -159,10 +157,10 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
     if (set_smem(fwd_skinny_kernel, smem)) return 1;
     dim3 grid(p.nx, p.ksplit, tiles);
     cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
-    fwd_skinny_kernel<<<grid, 256, smem, st>>>(X, ldx, B, W, K, N, K, p.kc, P, Bpad);
+    fwd_skinny_kernel<<<grid, 256, smem, st>>>(X, ldx, B, W, K, N, K, p.kc, P, Bpad, p.ksplit);
     Profiler::end(pe, st);
     SN_LAUNCH_CHECK();
-    fwd_epilogue_kernel<<<ew_grid((size_t)B * N, sms), 256, 0, st>>>(P, p.ksplit, Bpad, B, N, bias, relu, mask,
+    fwd_epilogue_kernel<<<ew_grid((size_t)B * N, sms), 256, 0, st>>>(P, kFwdSlots * p.ksplit, Bpad, B, N, bias, relu, mask,
                                                                     keep_prob, scale, seed, offset, layer, H, ldh, out2);
     SN_LAUNCH_CHECK();
   } else {
@@ -180,7 +178,7 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
 static size_t fwd_partial_floats(int B, int K, int N, int sms) {
   if (B > kSkinnyFwdMaxB || (K % 4) != 0) return 0;
   FwdPlan p = plan_fwd(K, N, sms);
-  return (size_t)p.ksplit * round_up(B, kBT) * N;
+  return (size_t)kFwdSlots * p.ksplit * round_up(B, kBT) * N;
 }
 
 }  // namespace sn

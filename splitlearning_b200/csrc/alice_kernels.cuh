@@ -40,6 +40,8 @@ __global__ void __launch_bounds__(256) conv_pool_fwd_kernel(const float* __restr
   __shared__ float ws[kConvCG * 9];
   __shared__ float bs[kConvCG];
   const int cg = blockIdx.y;
+  pdl_wait();
+  pdl_launch();
   if (threadIdx.x < kConvCG * 9) ws[threadIdx.x] = w[cg * kConvCG * 9 + threadIdx.x];
   if (threadIdx.x < kConvCG) bs[threadIdx.x] = bias[cg * kConvCG + threadIdx.x];
   for (int b = blockIdx.x; b < B; b += gridDim.x) {
@@ -75,6 +77,8 @@ __global__ void __launch_bounds__(256) conv_pool_bwd_kernel(const float* __restr
   __shared__ unsigned is_last;
   const int cg = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int c = cg * kConvCG + warp;
+  pdl_wait();
+  pdl_launch();
   float wr[9];
 #pragma unroll
   for (int t = 0; t < 9; ++t) wr[t] = w[c * 9 + t];

@@ -82,6 +82,15 @@ __device__ __forceinline__ void opt_update(const OptParams& op, float& p, float 
   }
 }
 
+// Programmatic dependent launch (PDL).  Every kernel of a step is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization: it may start while its predecessor in the
+// stream is still running, must call pdl_wait() before touching anything the predecessor writes,
+// and calls pdl_launch() right AFTER its own wait (so a dependent can never overtake the
+// predecessor's predecessor: whatever a kernel does before its wait may only touch data produced
+// two or more kernels back).  Without the launch attribute both are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

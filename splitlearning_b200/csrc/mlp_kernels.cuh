@@ -83,7 +83,7 @@ __device__ __forceinline__ void cp_async16_zfill(void* smem, const void* gmem, b
 // (row>>1)&3, which makes every LDS.128 of a quarter-warp hit 8 distinct bank groups.
 __global__ void __launch_bounds__(256, 1)
 fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N,
-                  int K, int kc, float* __restrict__ P, int Bpad, int ksplit) {
+                  int K, int kc, float* __restrict__ P, int Bpad, int ksplit, int prefetch_early) {
   extern __shared__ float4 smem4[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ks = blockIdx.y, k0 = ks * kc;
@@ -127,8 +127,18 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
     }
     cp_async_commit();
   };
+  // PDL: the W stream may start before the previous kernel finishes when the host says nothing
+  // in between writes W (prefetch_early); X is the previous kernel's output and must wait.
+  if (prefetch_early) {
 #pragma unroll
-  for (int d = 0; d < kFwdRing - 1; ++d) issue(d);
+    for (int d = 0; d < kFwdRing - 1; ++d) issue(d);
+  }
+  pdl_wait();
+  pdl_launch();
+  if (!prefetch_early) {
+#pragma unroll
+    for (int d = 0; d < kFwdRing - 1; ++d) issue(d);
+  }
   SN_T(1);
 
   // X chunk -> smem, transposed and swizzled (see above); zero outside the batch / the chunk.
@@ -256,6 +266,8 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
                                     const float* __restrict__ bias, int relu, const uint8_t* __restrict__ mask,
                                     float keep_prob, float scale, uint64_t seed, uint64_t offset, int layer,
                                     float* __restrict__ H, int ldh, float* __restrict__ out2) {
+  pdl_wait();
+  pdl_launch();
   const size_t total = (size_t)B * N;
   for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
     const int b = (int)(idx / N), n = (int)(idx - (size_t)b * N);
@@ -281,6 +293,95 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
   }
 }
 
+// Tiny layers (fc3 100x1000, the U-shape tail 10x100): the weight matrix is L2-resident and the
+// launch is pure latency, so the split-K machinery above costs more than it saves.  One warp per
+// output row, lanes stride k, 16 batch accumulators per lane, one 16-value butterfly, and the
+// bias / ReLU / dropout epilogue fused: one launch instead of two, no partial sums.
+__global__ void __launch_bounds__(256)
+fwd_small_kernel(const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N, int K,
+                 const float* __restrict__ bias, int relu, const uint8_t* __restrict__ mask, float keep_prob,
+                 float scale, uint64_t seed, uint64_t offset, int layer, float* __restrict__ H, int ldh,
+                 float* __restrict__ out2, int prefetch_early) {
+  extern __shared__ float4 smem4[];                 // X tile [16][K4] float4 (K padded to 4)
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n = blockIdx.x * 8 + warp;
+  const int b0 = blockIdx.y * kBT, nb = min(kBT, B - b0);
+  const int K4 = (K + 3) >> 2;
+  const bool vec = (K & 3) == 0;
+  // when the host says the previous kernel cannot be writing W (prefetch_early), this warp's W
+  // row is fetched before the PDL wait; otherwise right after it
+  constexpr int WPF = 8;                            // float4 per lane held in registers (K <= 1024)
+  float4 wreg[WPF];
+  const bool row_ok = n < N;
+  const float* wr = W + (size_t)(row_ok ? n : 0) * ldw;
+  if (!prefetch_early) { pdl_wait(); pdl_launch(); }
+  if (vec) {
+#pragma unroll
+    for (int q = 0; q < WPF; ++q) {
+      const int k4 = q * 32 + lane;
+      wreg[q] = (row_ok && k4 < K4) ? __ldg(reinterpret_cast<const float4*>(wr) + k4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  if (prefetch_early) { pdl_wait(); pdl_launch(); }
+  // X -> smem, all loads of a thread in flight together (one round trip)
+  for (int idx = tid; idx < kBT * K4; idx += 256) {
+    const int b = idx / K4, k4 = idx - b * K4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (b < nb) {
+      const float* xr = X + (size_t)(b0 + b) * ldx;
+      if (vec) v = __ldg(reinterpret_cast<const float4*>(xr) + k4);
+      else {
+        const int k = k4 * 4;
+        v.x = k < K ? __ldg(xr + k) : 0.f;
+        v.y = k + 1 < K ? __ldg(xr + k + 1) : 0.f;
+        v.z = k + 2 < K ? __ldg(xr + k + 2) : 0.f;
+        v.w = k + 3 < K ? __ldg(xr + k + 3) : 0.f;
+      }
+    }
+    smem4[idx] = v;
+  }
+  __syncthreads();
+  if (!row_ok) return;
+  float acc[kBT];
+#pragma unroll
+  for (int b = 0; b < kBT; ++b) acc[b] = 0.f;
+  for (int q = 0; q * 32 < K4; ++q) {
+    const int k4 = q * 32 + lane;
+    float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (k4 < K4) {
+      if (vec) w = q < WPF ? wreg[q < WPF ? q : 0] : __ldg(reinterpret_cast<const float4*>(wr) + k4);
+      else {
+        const int k = k4 * 4;
+        w.x = k < K ? __ldg(wr + k) : 0.f;
+        w.y = k + 1 < K ? __ldg(wr + k + 1) : 0.f;
+        w.z = k + 2 < K ? __ldg(wr + k + 2) : 0.f;
+        w.w = k + 3 < K ? __ldg(wr + k + 3) : 0.f;
+      }
+#pragma unroll
+      for (int b = 0; b < kBT; ++b) {
+        const float4 x = smem4[b * K4 + k4];
+        acc[b] = __fmaf_rn(w.x, x.x, acc[b]);
+        acc[b] = __fmaf_rn(w.y, x.y, acc[b]);
+        acc[b] = __fmaf_rn(w.z, x.z, acc[b]);
+        acc[b] = __fmaf_rn(w.w, x.w, acc[b]);
+      }
+    }
+  }
+  butterfly_reduce<kBT>(acc, lane);             // lanes 2b and 2b+1 both end with the sum for batch row b
+  const int b = lane >> 1;
+  if ((lane & 1) || b >= nb) return;
+  float s = acc[0] + bias[n];
+  if (relu) s = fmaxf(s, 0.f);
+  const size_t idx = (size_t)(b0 + b) * N + n;
+  if (mask) {
+    s = mask[idx] ? s * scale : 0.f;
+  } else if (keep_prob < 1.f) {
+    s = philox_keep(seed, offset, layer, idx, keep_prob) ? s * scale : 0.f;
+  }
+  H[(size_t)(b0 + b) * ldh + n] = s;
+  if (out2) out2[idx] = s;
+}
+
 // ------------------------------------------------------------------------------------------
 // Cross-entropy: one warp per row; loss = mean_b(lse - z[y]); dlogits = (softmax - onehot)/B.
 // Row losses go to row_loss[B]; the last CTA (ticket) sums them in row order.
@@ -289,6 +390,8 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ z, in
                                                  int B, int C, float* __restrict__ dz, int lddz,
                                                  float* __restrict__ row_loss, unsigned* __restrict__ ticket,
                                                  float* __restrict__ loss_out, float* __restrict__ loss_out2) {
+  pdl_wait();
+  pdl_launch();
   __shared__ unsigned is_last;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * 8 + warp;
@@ -350,6 +453,8 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ z, in
 __global__ void __launch_bounds__(256) eval_counts_kernel(const float* __restrict__ z, const int64_t* __restrict__ y,
                                                           int B, int C, int64_t omit,
                                                           unsigned long long* __restrict__ counters) {
+  pdl_wait();
+  pdl_launch();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * 8 + warp;
   if (b >= B) return;
@@ -419,6 +524,8 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
   int n = nb0 + wr;
 #pragma unroll
   for (int d = 0; d < kRing - 1; ++d) issue(d, n + d * rw);      // start streaming before anything else
+  pdl_wait();        // W / optimizer state are never written by the kernel just before this one;
+  pdl_launch();      // dZ (and A) are, so everything below waits for it
 
   {  // dZ tile, transposed to [row][16]; loads batched ahead of their stores (latency, not bandwidth)
     constexpr int SB = 8;
@@ -539,6 +646,8 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
 __global__ void bwd_epilogue_kernel(const float* __restrict__ PA, int nsplit, int B, int K,
                                     const float* __restrict__ H, int ldh, float scale, float* __restrict__ dst,
                                     int ldd) {
+  pdl_wait();
+  pdl_launch();
   const size_t total = (size_t)B * K;
   for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
     const int b = (int)(idx / K), k = (int)(idx - (size_t)b * K);
@@ -560,6 +669,8 @@ __global__ void bwd_epilogue_kernel(const float* __restrict__ PA, int nsplit, in
 // dst = src * (out > 0)  (ReLU on the last layer, U-shape model2)
 __global__ void relu_gate_kernel(const float* __restrict__ src, const float* __restrict__ out, size_t n,
                                  float* __restrict__ dst) {
+  pdl_wait();
+  pdl_launch();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     dst[i] = out[i] > 0.f ? src[i] : 0.f;
 }
@@ -572,6 +683,8 @@ __global__ void relu_gate_kernel(const float* __restrict__ src, const float* __r
 __global__ void __launch_bounds__(256) sgemm_strided_kernel(const float* __restrict__ A, long long sam, long long sak,
                                                             const float* __restrict__ Bm, long long sbk, long long sbn,
                                                             float* __restrict__ C, long long ldc, int M, int N, int K) {
+  pdl_wait();
+  pdl_launch();
   __shared__ float As[16][64 + 4];
   __shared__ float Bs[16][64 + 4];
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
@@ -613,6 +726,8 @@ __global__ void __launch_bounds__(256) sgemm_strided_kernel(const float* __restr
 template <int OPT>
 __global__ void opt_elementwise_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ s1,
                                        float* __restrict__ s2, size_t n, OptParams op) {
+  pdl_wait();
+  pdl_launch();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     float pv = p[i], a = s1[i], b = (OPT == 2) ? s2[i] : 0.f;
     opt_update<OPT>(op, pv, g[i], a, b);
@@ -626,6 +741,8 @@ __global__ void opt_elementwise_kernel(float* __restrict__ p, const float* __res
 template <int OPT>
 __global__ void bias_grad_update_kernel(const float* __restrict__ dZ, int ldz, int B, int N, float* __restrict__ bias,
                                         float* __restrict__ s1, float* __restrict__ s2, OptParams op) {
+  pdl_wait();
+  pdl_launch();
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   float db = 0.f;

@@ -3,6 +3,7 @@
 #include "../../include/splitnn.h"
 
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -35,6 +36,8 @@ static inline int ew_grid(size_t n, int sms) {
 // ---------------------------------------------------------------- launch plans
 constexpr int kMaxKc = 1536;        // X chunk [16][kc] fp32 = 96 KB of shared memory (+128 KB of W rings)
 constexpr int kSkinnyFwdMaxB = 64;  // above this the forward uses the general-batch path
+constexpr size_t kSmallLayerElems = 256 * 1024;   // <= 1 MB of weights: one-warp-per-row kernel
+constexpr int kSmallLayerMaxK = 2048;             // its X tile [16][K] fp32 must fit in shared memory
 
 struct FwdPlan { int kc, ksplit, nx; };
 struct BwdPlan { int kw, kgroups, nsplit, rows_per_cta; };
@@ -145,30 +148,59 @@ struct Profiler {
   }
 };
 
+// ---------------------------------------------------------------- launches (PDL)
+// All kernels go through launch_k: cudaLaunchKernelEx with programmatic stream serialization, so a
+// kernel's prologue overlaps its predecessor's tail (see pdl_wait/pdl_launch in common.cuh).
+// SN_NO_PDL=1 in the environment turns the attribute off for A/B timing.
+template <typename... P, typename... A>
+static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args) {
+  static const bool pdl = getenv("SN_NO_PDL") == nullptr;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);
+}
+
 // ---------------------------------------------------------------- shared launch helpers
 static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, const float* bias, int K, int N,
                              int relu, const uint8_t* mask, float keep_prob, float scale, uint64_t seed,
                              uint64_t offset, int layer, float* H, int ldh, float* out2, float* P, int sms,
                              cudaStream_t st, Profiler* prof = nullptr) {
-  if (B <= kSkinnyFwdMaxB && (K % 4) == 0) {
+  if (B <= kSkinnyFwdMaxB && (size_t)N * K <= kSmallLayerElems && K <= kSmallLayerMaxK) {
+    dim3 grid(ceil_div(N, 8), ceil_div(B, kBT));
+    const size_t smem_small = (size_t)kBT * ((K + 3) / 4) * 16;
+    if (set_smem(fwd_small_kernel, smem_small)) return 1;
+    cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
+    launch_k(fwd_small_kernel, dim3(grid), dim3(256), smem_small, st, X, ldx, B, W, K, N, K, bias, relu, mask, keep_prob, scale, seed, offset,
+                                          layer, H, ldh, out2, layer > 0 ? 1 : 0);
+    Profiler::end(pe, st);
+    SN_LAUNCH_CHECK();
+  } else if (B <= kSkinnyFwdMaxB && (K % 4) == 0) {
     FwdPlan p = plan_fwd(K, N, sms);
     int tiles = ceil_div(B, kBT), Bpad = tiles * kBT;
     size_t smem = (size_t)kBT * p.kc * 4 + (size_t)8 * kFwdRing * 8 * 32 * 16;   // X chunk + per-warp W rings
     if (set_smem(fwd_skinny_kernel, smem)) return 1;
     dim3 grid(p.nx, p.ksplit, tiles);
     cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
-    fwd_skinny_kernel<<<grid, 256, smem, st>>>(X, ldx, B, W, K, N, K, p.kc, P, Bpad, p.ksplit);
+    launch_k(fwd_skinny_kernel, dim3(grid), dim3(256), smem, st, X, ldx, B, W, K, N, K, p.kc, P, Bpad, p.ksplit, layer > 0 ? 1 : 0);
     Profiler::end(pe, st);
     SN_LAUNCH_CHECK();
-    fwd_epilogue_kernel<<<ew_grid((size_t)B * N, sms), 256, 0, st>>>(P, kFwdSlots * p.ksplit, Bpad, B, N, bias, relu, mask,
+    launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, P, kFwdSlots * p.ksplit, Bpad, B, N, bias, relu, mask,
                                                                     keep_prob, scale, seed, offset, layer, H, ldh, out2);
     SN_LAUNCH_CHECK();
   } else {
     dim3 grid(ceil_div(N, 64), ceil_div(B, 64));
-    sgemm_strided_kernel<<<grid, 256, 0, st>>>(X, ldx, 1, W, 1, K, H, ldh, B, N, K);
+    launch_k(sgemm_strided_kernel, dim3(grid), dim3(256), 0, st, X, ldx, 1, W, 1, K, H, ldh, B, N, K);
     SN_LAUNCH_CHECK();
     SN_REQUIRE(ldh == N, "general-batch forward needs a dense output");
-    fwd_epilogue_kernel<<<ew_grid((size_t)B * N, sms), 256, 0, st>>>(H, 1, 0, B, N, bias, relu, mask, keep_prob,
+    launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, H, 1, 0, B, N, bias, relu, mask, keep_prob,
                                                                     scale, seed, offset, layer, H, ldh, out2);
     SN_LAUNCH_CHECK();
   }
@@ -176,7 +208,8 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
 }
 
 static size_t fwd_partial_floats(int B, int K, int N, int sms) {
-  if (B > kSkinnyFwdMaxB || (K % 4) != 0) return 0;
+  if (B > kSkinnyFwdMaxB || ((size_t)N * K <= kSmallLayerElems && K <= kSmallLayerMaxK)) return 0;
+  if ((K % 4) != 0) return 0;
   FwdPlan p = plan_fwd(K, N, sms);
   return (size_t)kFwdSlots * p.ksplit * round_up(B, kBT) * N;
 }
@@ -239,7 +272,7 @@ int sn_conv_pool_forward(const float* x, const float* w, const float* b, int B, 
   int dev = 0;
   SN_CUDA(cudaGetDevice(&dev));
   dim3 grid(std::min(B, sm_count(dev) * 4), 4);
-  conv_pool_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, w, b, B, act);
+  launch_k(conv_pool_fwd_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, x, w, b, B, act);
   SN_LAUNCH_CHECK();
   return 0;
 }
@@ -258,7 +291,7 @@ int sn_conv_pool_backward(const float* x, const float* w, const float* b, const 
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
   SN_CUDA(cudaMemsetAsync(ticket, 0, 256, st));
   OptParams op{};
-  conv_pool_bwd_kernel<0><<<dim3(gx, 4), 256, 0, st>>>(x, const_cast<float*>(w), const_cast<float*>(b), dact, B,
+  launch_k(conv_pool_bwd_kernel<0>, dim3(gx, 4), dim3(256), 0, st, x, const_cast<float*>(w), const_cast<float*>(b), dact, B,
                                                       partial, ticket, dw, db, nullptr, nullptr, op);
   SN_LAUNCH_CHECK();
   return 0;
@@ -334,7 +367,7 @@ int sn_linear_forward_noalloc(const float* x, const float* W, const float* bias,
 
 static int launch_ce(const float* z, int ldz, const int64_t* y, int B, int C, float* dz, int lddz, float* row_loss,
                      unsigned* ticket, float* loss, float* loss2, cudaStream_t st) {
-  ce_kernel<<<ceil_div(B, 8), 256, 0, st>>>(z, ldz, y, B, C, dz, lddz, row_loss, ticket, loss, loss2);
+  launch_k(ce_kernel, dim3(ceil_div(B, 8)), dim3(256), 0, st, z, ldz, y, B, C, dz, lddz, row_loss, ticket, loss, loss2);
   SN_LAUNCH_CHECK();
   return 0;
 }
@@ -355,7 +388,7 @@ int sn_cross_entropy(const float* logits, const int64_t* labels, int B, int C, f
 int sn_eval_counts(const float* logits, const int64_t* labels, int B, int C, int64_t omit_label, int64_t* counters6,
                    void* stream) {
   SN_REQUIRE(logits && labels && counters6 && B > 0 && C > 0, "sn_eval_counts: bad arguments");
-  eval_counts_kernel<<<ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(
+  launch_k(eval_counts_kernel, dim3(ceil_div(B, 8)), dim3(256), 0, (cudaStream_t)stream, 
       logits, labels, B, C, omit_label, reinterpret_cast<unsigned long long*>(counters6));
   SN_LAUNCH_CHECK();
   return 0;
@@ -585,18 +618,18 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
       if (need_da) {
         if (set_smem(bwd_update_kernel<OPT, true>, smem)) return 1;
         cudaEvent_t pe = h->prof.begin(st, 1, l);
-        bwd_update_kernel<OPT, true><<<grid, 256, smem, st>>>(h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
+        launch_k(bwd_update_kernel<OPT, true>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
                                                               s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, h->PA,
                                                               p.kw, p.rows_per_cta, op);
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
-        bwd_epilogue_kernel<<<ew_grid((size_t)B * K, h->sms), 256, 0, st>>>(h->PA, p.nsplit, B, K, gateH, K, gscale,
+        launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, p.nsplit, B, K, gateH, K, gscale,
                                                                            dst, K);
         SN_LAUNCH_CHECK();
       } else {
         if (set_smem(bwd_update_kernel<OPT, false>, smem)) return 1;
         cudaEvent_t pe = h->prof.begin(st, 1, l);
-        bwd_update_kernel<OPT, false><<<grid, 256, smem, st>>>(h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
+        launch_k(bwd_update_kernel<OPT, false>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
                                                                s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B,
                                                                h->PA, p.kw, p.rows_per_cta, op);
         Profiler::end(pe, st);
@@ -611,22 +644,22 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
       }
       if (need_da) {
         SN_REQUIRE((size_t)B * K <= h->PA_floats, "batch larger than max_batch given to sn_bob_create");
-        sgemm_strided_kernel<<<dim3(ceil_div(K, 64), ceil_div(B, 64)), 256, 0, st>>>(dZ, N, 1, h->W[l], K, 1, h->PA, K,
+        launch_k(sgemm_strided_kernel, dim3(ceil_div(K, 64), ceil_div(B, 64)), dim3(256), 0, st, dZ, N, 1, h->W[l], K, 1, h->PA, K,
                                                                                     B, K, N);
         SN_LAUNCH_CHECK();
       }
-      sgemm_strided_kernel<<<dim3(ceil_div(K, 64), ceil_div(N, 64)), 256, 0, st>>>(dZ, 1, N, A, K, 1, h->dWbuf, K, N,
+      launch_k(sgemm_strided_kernel, dim3(ceil_div(K, 64), ceil_div(N, 64)), dim3(256), 0, st, dZ, 1, N, A, K, 1, h->dWbuf, K, N,
                                                                                   K, B);
       SN_LAUNCH_CHECK();
-      opt_elementwise_kernel<OPT><<<ew_grid((size_t)N * K, h->sms), 256, 0, st>>>(h->W[l], h->dWbuf, s.s1[2 * l],
+      launch_k(opt_elementwise_kernel<OPT>, dim3(ew_grid((size_t)N * K, h->sms)), dim3(256), 0, st, h->W[l], h->dWbuf, s.s1[2 * l],
                                                                                  s.s2[2 * l], (size_t)N * K, op);
       SN_LAUNCH_CHECK();
-      bias_grad_update_kernel<OPT><<<ceil_div(N, 256), 256, 0, st>>>(dZ, N, B, N, h->b[l], s.s1[2 * l + 1],
+      launch_k(bias_grad_update_kernel<OPT>, dim3(ceil_div(N, 256)), dim3(256), 0, st, dZ, N, B, N, h->b[l], s.s1[2 * l + 1],
                                                                     s.s2[2 * l + 1], op);
       SN_LAUNCH_CHECK();
       if (need_da) {
         // PA holds one dense [B][K] "split"; bwd_epilogue indexes splits with a 16-row stride
-        bwd_epilogue_kernel<<<ew_grid((size_t)B * K, h->sms), 256, 0, st>>>(h->PA, 1, B, K, gateH, K, gscale, dst, K);
+        launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, 1, B, K, gateH, K, gscale, dst, K);
         SN_LAUNCH_CHECK();
       }
     }
@@ -683,7 +716,7 @@ int sn_bob_backward_update(sn_bob* h, int slot, const float* act, const float* d
   const int C = h->dims[h->L];
   const size_t n = (size_t)B * C;
   if (h->relu_last) {
-    relu_gate_kernel<<<ew_grid(n, h->sms), 256, 0, st>>>(dout, h->H[h->L], n, h->dZ[h->L]);
+    launch_k(relu_gate_kernel, dim3(ew_grid(n, h->sms)), dim3(256), 0, st, dout, h->H[h->L], n, h->dZ[h->L]);
     SN_LAUNCH_CHECK();
   } else {
     SN_CUDA(cudaMemcpyAsync(h->dZ[h->L], dout, n * 4, cudaMemcpyDeviceToDevice, st));
@@ -796,7 +829,7 @@ int sn_alice_forward(sn_alice* h, const float* x, int B, float* act, void* strea
   SN_ALICE_ENTER(h);
   SN_REQUIRE(x && act && B > 0, "sn_alice_forward: bad arguments");
   dim3 grid(std::min(B, h->sms * 4), 4);
-  conv_pool_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, h->w, h->b, B, act);
+  launch_k(conv_pool_fwd_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, x, h->w, h->b, B, act);
   SN_LAUNCH_CHECK();
   return 0;
 }
@@ -809,11 +842,11 @@ static int alice_bwd(sn_alice* h, const float* x, const float* dact, int B, cuda
   SN_REQUIRE((int)grid.x <= h->gx, "internal: conv backward grid exceeds scratch");
   switch (h->hyper.type) {
     case SN_OPT_SGD_MOMENTUM:
-      conv_pool_bwd_kernel<1><<<grid, 256, 0, st>>>(x, h->w, h->b, dact, B, h->partial, h->ticket, nullptr, nullptr,
+      launch_k(conv_pool_bwd_kernel<1>, dim3(grid), dim3(256), 0, st, x, h->w, h->b, dact, B, h->partial, h->ticket, nullptr, nullptr,
                                                    h->s1, h->s2, op);
       break;
     case SN_OPT_ADAM:
-      conv_pool_bwd_kernel<2><<<grid, 256, 0, st>>>(x, h->w, h->b, dact, B, h->partial, h->ticket, nullptr, nullptr,
+      launch_k(conv_pool_bwd_kernel<2>, dim3(grid), dim3(256), 0, st, x, h->w, h->b, dact, B, h->partial, h->ticket, nullptr, nullptr,
                                                    h->s1, h->s2, op);
       break;
     default:
@@ -838,7 +871,7 @@ int sn_alice_local_step(sn_alice* h, const float* x, const int64_t* labels, int 
     SN_CUDA(cudaMalloc(&h->dact, (size_t)h->max_batch * kD0 * 4));
   }
   dim3 grid(std::min(B, h->sms * 4), 4);
-  conv_pool_fwd_kernel<<<grid, 256, 0, st>>>(x, h->w, h->b, B, h->act);
+  launch_k(conv_pool_fwd_kernel, dim3(grid), dim3(256), 0, st, x, h->w, h->b, B, h->act);
   SN_LAUNCH_CHECK();
   if (launch_ce(h->act, kD0, labels, B, kD0, h->dact, kD0, h->row_loss, h->ticket + 1, loss_out, nullptr, st)) return 1;
   return alice_bwd(h, x, h->dact, B, st);

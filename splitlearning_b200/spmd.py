@@ -136,6 +136,7 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
     local = int(os.environ.get("LOCAL_RANK", str(rank)))
     device = torch.device("cuda", local)
     torch.cuda.set_device(device)
+    os.environ.setdefault("TORCH_NCCL_SHOW_EAGER_INIT_P2P_SERIALIZATION_WARNING", "false")
     dist.init_process_group("nccl", device_id=device)
     from . import _lib
     lib = _lib.load()

@@ -35,6 +35,14 @@ enum { SN_OPT_NONE = 0, SN_OPT_SGD_MOMENTUM = 1, SN_OPT_ADAM = 2 };
 
 int sn_version(void);
 const char* sn_last_error(void);
+/* Arithmetic of the LARGE-batch (B > 64) matrix products; process-wide.  0 (default): fp32 FMA,
+ * the reference's precision (torch CPU fp32).  1: tcgen05 tensor cores in TF32 with fp32
+ * accumulation - about 5e-4 relative on this model's logits, i.e. outside the 1e-4 parity bound,
+ * for throughput runs (BASELINE.json config 5 sweep).  Batches <= 64 always use the fp32
+ * weight-streaming kernels, which are HBM-bound and gain nothing from tensor cores.
+ * (No counterpart in the reference, which has a single CPU fp32 path.) */
+int sn_set_matmul_precision(int mode);
+int sn_get_matmul_precision(void);
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 uint64_t sn_launch_count(void);
 

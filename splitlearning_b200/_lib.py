@@ -19,6 +19,8 @@ SIGNATURES = {
     "sn_version": (_i, []),
     "sn_last_error": (C.c_char_p, []),
     "sn_launch_count": (_u64, []),
+    "sn_set_matmul_precision": (_i, [_i]),
+    "sn_get_matmul_precision": (_i, []),
     "sn_conv_pool_forward": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "sn_conv_pool_backward_scratch_bytes": (_sz, [_i]),
     "sn_conv_pool_backward": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp]),

@@ -1,0 +1,265 @@
+// tcgen05 (5th-gen tensor core) GEMM for the tensor-bound regime of the split-NN step: large
+// batches (BASELINE.json config 5: B 64..65536, H 256..8192), where the MLP layers stop being a
+// weight stream and become real GEMMs.
+//
+//   C[M,N] = epilogue( A[M,K] . B[N,K]^T ),  A, B, C fp32 row-major, both operands K-major
+//   (forward: A = activations [batch, in], B = weights [out, in] exactly as nn.Linear stores them).
+//
+// One 128x128 output tile per CTA, warp-specialised:
+//   warp 0      TMA producer: cp.async.bulk.tensor 2-D loads of 128x32-float tiles (128-byte rows,
+//               SWIZZLE_128B) of A and B into a kStages-deep shared-memory ring, mbarrier complete_tx
+//   warp 1      TMEM allocation + single-thread tcgen05.mma.kind::tf32 issue (M=128,N=128,K=8 per
+//               instruction, fp32 accumulation in TMEM), tcgen05.commit releases ring slots
+//   warps 2..5  epilogue: tcgen05.ld the accumulator (32 lanes x 32 columns per instruction),
+//               + bias, ReLU, dropout keep-mask / Philox, vectorised stores
+// Out-of-range rows/columns/k are zero-filled by TMA and masked in the epilogue, so any M, N and
+// any K that is a multiple of 4 work.
+//
+// Precision: kind::tf32 reads the fp32 bit patterns and uses the top 19 bits (10-bit mantissa).
+// That is ~5e-4 relative on the logits of this model - outside the 1e-4 parity
+// bound - so this path is the PERF mode for large batches (sn_set_matmul_precision(1)); the fp32
+// path stays the default.
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace sn {
+namespace tc {
+
+constexpr int BM = 128, BN = 128, BK = 32;          // BK floats = 128 bytes = one swizzle row
+constexpr int kStages = 3;                          // 96 KB of operand tiles: two CTAs fit per SM
+constexpr int kTileBytes = BM * BK * 4;             // 16 KB per operand per stage
+constexpr int kThreads = 192;
+constexpr int kTmemCols = 128;                      // fp32 accumulator: 128 lanes x 128 columns
+
+struct __align__(1024) Smem {
+  float a[kStages][BM * BK];
+  float b[kStages][BN * BK];
+  unsigned long long full_bar[kStages];
+  unsigned long long empty_bar[kStages];
+  unsigned long long tmem_full_bar;
+  unsigned tmem_base;
+};
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, unsigned long long* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor):
+//   [0,14) start address >> 4 | [16,30) leading byte offset >> 4 (unused for swizzled K-major: 1)
+//   [32,46) stride byte offset >> 4 = 1024 B between 8-row groups | [46,48) version = 1 (sm_100)
+//   [61,64) layout type = 2 (SWIZZLE_128B)
+__device__ __forceinline__ unsigned long long make_desc_kmajor_sw128(const void* tile) {
+  unsigned long long d = 0;
+  d |= (unsigned long long)((smem_u32(tile) >> 4) & 0x3FFF);
+  d |= (unsigned long long)1 << 16;
+  d |= (unsigned long long)(1024 >> 4) << 32;
+  d |= (unsigned long long)1 << 46;
+  d |= (unsigned long long)2 << 61;
+  return d;
+}
+
+// Instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 [4,6)=1, a/b_format TF32
+// [7,10)=[10,13)=2, a/b K-major [15],[16]=0, N>>3 at [17,23), M>>4 at [24,29).
+__device__ __forceinline__ unsigned make_idesc_tf32(int m, int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(n >> 3) << 17) | ((unsigned)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void mma_tf32(unsigned tmem_d, unsigned long long adesc, unsigned long long bdesc,
+                                         unsigned idesc, unsigned accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void mma_commit(unsigned long long* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+
+struct Epilogue {
+  const float* bias;       // [N], nullable
+  int relu;
+  const uint8_t* mask;     // [M,N] keep bytes (row stride N), nullable
+  float keep_prob, scale;  // Philox dropout when mask == nullptr and keep_prob < 1
+  uint64_t seed, offset;
+  int layer;
+  float* out2;             // optional dense copy [M,N]
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
+                 int K, float* __restrict__ C, int ldc, Epilogue ep) {
+  extern __shared__ unsigned char smem_raw[];
+  Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int kblocks = (K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&sm.full_bar[s], 1);
+      mbar_init(&sm.empty_bar[s], 1);
+    }
+    mbar_init(&sm.tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {   // one warp allocates TMEM and later frees it
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)),
+                 "r"(kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const unsigned tmem_d = sm.tmem_base;
+
+  pdl_wait();          // A is the previous kernel's output
+  pdl_launch();
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < kblocks; ++kb) {
+        const int s = kb % kStages;
+        const unsigned ph = (kb / kStages) & 1;
+        mbar_wait(&sm.empty_bar[s], ph ^ 1);
+        mbar_expect_tx(&sm.full_bar[s], 2 * kTileBytes);
+        tma_load_2d(sm.a[s], &map_a, &sm.full_bar[s], kb * BK, m0);
+        tma_load_2d(sm.b[s], &map_b, &sm.full_bar[s], kb * BK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const unsigned idesc = make_idesc_tf32(BM, BN);
+      for (int kb = 0; kb < kblocks; ++kb) {
+        const int s = kb % kStages;
+        const unsigned ph = (kb / kStages) & 1;
+        mbar_wait(&sm.full_bar[s], ph);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const unsigned long long ad = make_desc_kmajor_sw128(sm.a[s]);
+        const unsigned long long bd = make_desc_kmajor_sw128(sm.b[s]);
+#pragma unroll
+        for (int k = 0; k < BK / 8; ++k)     // 8 tf32 = 32 bytes per instruction: +2 in 16-byte units
+          mma_tf32(tmem_d, ad + (unsigned long long)(2 * k), bd + (unsigned long long)(2 * k), idesc, (kb | k) != 0);
+        mma_commit(&sm.empty_bar[s]);          // slot free once these MMAs have read it
+      }
+      mma_commit(&sm.tmem_full_bar);           // accumulator complete
+    }
+  } else {
+    // epilogue warps 2..5: TMEM lane quarter = warp % 4
+    const int q = warp & 3;
+    mbar_wait(&sm.tmem_full_bar, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const int row = m0 + q * 32 + lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      unsigned r[32];
+      const unsigned taddr = tmem_d + ((unsigned)(q * 32) << 16) + (unsigned)c0;
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,"
+          "%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+            "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+            "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+            "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+          : "r"(taddr));
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      if (row < M) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int n = n0 + c0 + j;
+          if (n < N) {
+            float v = __uint_as_float(r[j]);
+            if (ep.bias) v += ep.bias[n];
+            if (ep.relu) v = fmaxf(v, 0.f);
+            const size_t idx = (size_t)row * N + n;
+            if (ep.mask) v = ep.mask[idx] ? v * ep.scale : 0.f;
+            else if (ep.keep_prob < 1.f) v = philox_keep(ep.seed, ep.offset, ep.layer, idx, ep.keep_prob) ? v * ep.scale : 0.f;
+            C[(size_t)row * ldc + n] = v;
+            if (ep.out2) ep.out2[idx] = v;
+          }
+        }
+      }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(kTmemCols) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// [rows, cols] fp32 row-major with leading dimension ld (floats); box = 32 floats x box_rows, 128B swizzle
+inline int make_map(CUtensorMap* map, const float* base, int rows, int cols, int ld, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return fail_msg("libsplitnn: cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail_msg("libsplitnn: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+  return 0;
+}
+
+inline bool usable(const float* A, int lda, const float* B, int ldb, int K) {
+  return (K % 4) == 0 && (lda % 4) == 0 && (ldb % 4) == 0 && ((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0;
+}
+
+constexpr size_t kSmemBytes = sizeof(Smem) + 1024;
+
+}  // namespace tc
+}  // namespace sn

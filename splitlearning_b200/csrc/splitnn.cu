@@ -12,11 +12,15 @@
 
 #include "alice_kernels.cuh"
 #include "common.cuh"
+#include "gemm_tc.cuh"
 #include "mlp_kernels.cuh"
 
 namespace sn {
 thread_local std::string g_last_error;
 std::atomic<uint64_t> g_launches{0};
+
+// 0 = fp32 everywhere (default, parity mode); 1 = TF32 tensor cores (tcgen05) for large batches
+std::atomic<int> g_matmul_precision{0};
 
 static int sm_count(int device) {
   static int cache[64] = {0};
@@ -169,6 +173,18 @@ static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t 
 }
 
 // ---------------------------------------------------------------- shared launch helpers
+static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int ldb, int N, int K, float* C, int ldc,
+                          const tc::Epilogue& ep, cudaStream_t st) {
+  CUtensorMap ma, mb;
+  if (tc::make_map(&ma, A, M, K, lda, tc::BM)) return 1;
+  if (tc::make_map(&mb, Bm, N, K, ldb, tc::BN)) return 1;
+  if (set_smem(tc::gemm_tf32_kernel, tc::kSmemBytes)) return 1;
+  dim3 grid(ceil_div(N, tc::BN), ceil_div(M, tc::BM));
+  launch_k(tc::gemm_tf32_kernel, grid, dim3(tc::kThreads), tc::kSmemBytes, st, ma, mb, M, N, K, C, ldc, ep);
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+
 static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, const float* bias, int K, int N,
                              int relu, const uint8_t* mask, float keep_prob, float scale, uint64_t seed,
                              uint64_t offset, int layer, float* H, int ldh, float* out2, float* P, int sms,
@@ -195,6 +211,13 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
     launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, P, kFwdSlots * p.ksplit, Bpad, B, N, bias, relu, mask,
                                                                     keep_prob, scale, seed, offset, layer, H, ldh, out2);
     SN_LAUNCH_CHECK();
+  } else if (g_matmul_precision.load() == 1 && tc::usable(X, ldx, W, K, K)) {
+    // tensor-bound regime: tcgen05 TF32 GEMM with the bias / ReLU / dropout epilogue fused
+    tc::Epilogue ep{bias, relu, mask, keep_prob, scale, seed, offset, layer, out2};
+    cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
+    int rc = launch_tc_gemm(X, ldx, B, W, K, N, K, H, ldh, ep, st);
+    Profiler::end(pe, st);
+    if (rc) return rc;
   } else {
     dim3 grid(ceil_div(N, 64), ceil_div(B, 64));
     launch_k(sgemm_strided_kernel, dim3(grid), dim3(256), 0, st, X, ldx, 1, W, 1, K, H, ldh, B, N, K);
@@ -263,6 +286,12 @@ static int conv_bwd_gx(int B, int sms) { return std::max(1, std::min(B, sms * 2)
 extern "C" {
 
 int sn_version(void) { return 1; }
+int sn_set_matmul_precision(int mode) {
+  SN_REQUIRE(mode == 0 || mode == 1, "sn_set_matmul_precision: mode must be 0 (fp32) or 1 (tf32 for large batches)");
+  g_matmul_precision.store(mode);
+  return 0;
+}
+int sn_get_matmul_precision(void) { return g_matmul_precision.load(); }
 const char* sn_last_error(void) { return g_last_error.c_str(); }
 uint64_t sn_launch_count(void) { return g_launches.load(); }
 

@@ -12,6 +12,11 @@ from ._lib import SN_OPT_ADAM, SN_OPT_NONE, SN_OPT_SGD_MOMENTUM, check, ptr, ptr
 D0 = 5408
 
 
+def set_matmul_precision(mode):
+    """0 = fp32 (default, parity); 1 = TF32 tcgen05 tensor cores for batches > 64 (perf mode)."""
+    check(_lib.load().sn_set_matmul_precision(int(mode)))
+
+
 def _stream(device=None):
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 

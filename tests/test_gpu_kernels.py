@@ -295,3 +295,35 @@ def test_philox_dropout_statistics_and_determinism(eng):
     drops = torch.stack([net.forward(act, train_mode=True, seed=3, offset=i).cpu() for i in range(8)])
     ratio = (drops.mean(0) / full).mean().item()          # E[keep*2] = 1
     assert 0.9 < ratio < 1.1, ratio
+
+
+# --------------------------------------------------------------------------- tcgen05 TF32 path
+def _tf32_trunc(a):
+    return (a.view(np.uint32) & np.uint32(0xFFFFE000)).view(np.float32)
+
+
+@pytest.mark.parametrize("B,K,N,relu", [(128, 32, 128, False), (256, 512, 256, True), (200, 1000, 100, True),
+                                        (65, 100, 12, False), (600, 5408, 1000, True)])
+def test_tcgen05_tf32_linear_forward(eng, B, K, N, relu):
+    """Large-batch perf mode: tcgen05.mma kind::tf32 reads the top 19 bits of each fp32 operand and
+    accumulates in fp32.  Checked tightly against an emulation of exactly that (truncated operands,
+    fp64 accumulate) and loosely (TF32's own error) against the fp32 result."""
+    rng = np.random.RandomState(B + K + N)
+    x = (rng.rand(B, K) * 4 - 1).astype(np.float32)
+    W = (rng.uniform(-1, 1, (N, K)) / np.sqrt(K)).astype(np.float32)
+    bias = rng.uniform(-1, 1, N).astype(np.float32)
+    mask = (rng.rand(B, N) < 0.5).astype(np.uint8)
+    eng.set_matmul_precision(1)
+    try:
+        got = eng.linear_forward(cu(x), cu(W), cu(bias), relu=relu, keep_mask=cu(mask), mask_scale=2.0).cpu().numpy()
+    finally:
+        eng.set_matmul_precision(0)
+    emu = _tf32_trunc(x).astype(np.float64) @ _tf32_trunc(W).astype(np.float64).T + bias
+    ref = x.astype(np.float64) @ W.astype(np.float64).T + bias
+    if relu:
+        emu, ref = np.maximum(emu, 0), np.maximum(ref, 0)
+    emu, ref = emu * mask * 2.0, ref * mask * 2.0
+    assert rel_err(got, emu) <= 5e-5          # the kernel computes what TF32 tensor cores define
+    assert rel_err(got, ref) <= 3e-3          # TF32 itself: ~6e-4 here, documented as perf mode only
+    exact = eng.linear_forward(cu(x), cu(W), cu(bias), relu=relu, keep_mask=cu(mask), mask_scale=2.0).cpu().numpy()
+    assert rel_err(exact, ref) <= 1e-5        # default precision is untouched

@@ -2,8 +2,14 @@
 // batches (BASELINE.json config 5: B 64..65536, H 256..8192), where the MLP layers stop being a
 // weight stream and become real GEMMs.
 //
-//   C[M,N] = epilogue( A[M,K] . B[N,K]^T ),  A, B, C fp32 row-major, both operands K-major
-//   (forward: A = activations [batch, in], B = weights [out, in] exactly as nn.Linear stores them).
+//   C[M,N] = epilogue( sum_r A(m,r) * B(n,r) ),  fp32 operands read as TF32, fp32 accumulate.
+//   Each operand is either K-major (reduction index contiguous in memory) or MN-major (its M/N
+//   index contiguous); the three products of a training step need all combinations:
+//     forward   Y[b,n]  = sum_k X[b,k]  W[n,k]    A = X  K-major,  B = W  K-major,  bias/ReLU/dropout epilogue
+//     dX        dA[b,k] = sum_n dZ[b,n] W[n,k]    A = dZ K-major,  B = W  MN-major, ReLU/dropout-gate epilogue
+//     dW+update g[n,k]  = sum_b dZ[b,n] A[b,k]    A = dZ MN-major, B = A  MN-major, optimizer epilogue (W, state
+//                                                 updated in place; dW is never written to memory)
+//   so no operand is ever transposed or copied: nn.Linear's [out,in] weights serve all three.
 //
 // One 128x128 output tile per CTA, warp-specialised:
 //   warp 0      TMA producer: cp.async.bulk.tensor 2-D loads of 128x32-float tiles (128-byte rows,
@@ -85,10 +91,28 @@ __device__ __forceinline__ unsigned long long make_desc_kmajor_sw128(const void*
   return d;
 }
 
+// MN-major TF32 operands have exactly one legal shared-memory layout (CUTLASS sm100_common.inl:
+// "for mn-major tf32 operands, SW128_32B is the only available smem layout"): layout type 1,
+// SWIZZLE_128B_BASE32B = Swizzle<2,5,2>, i.e. 128-byte rows along M/N whose 32-byte chunks are
+// XOR-ed with (reduction row mod 4); TMA writes it with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
+// The tile is stored as 32-float (128 B) wide column blocks, each block one TMA box of 32
+// reduction rows x 128 B.  Leading byte offset = distance between column blocks (4096 B), stride
+// byte offset = distance between groups of 4 reduction rows (512 B).
+__device__ __forceinline__ unsigned long long make_desc_mnmajor_sw128(const void* tile) {
+  unsigned long long d = 0;
+  d |= (unsigned long long)((smem_u32(tile) >> 4) & 0x3FFF);
+  d |= (unsigned long long)(4096 >> 4) << 16;
+  d |= (unsigned long long)(512 >> 4) << 32;
+  d |= (unsigned long long)1 << 46;
+  d |= (unsigned long long)1 << 61;
+  return d;
+}
+
 // Instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 [4,6)=1, a/b_format TF32
 // [7,10)=[10,13)=2, a/b K-major [15],[16]=0, N>>3 at [17,23), M>>4 at [24,29).
-__device__ __forceinline__ unsigned make_idesc_tf32(int m, int n) {
-  return (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(n >> 3) << 17) | ((unsigned)(m >> 4) << 24);
+__device__ __forceinline__ unsigned make_idesc_tf32(int m, int n, bool a_mn, bool b_mn) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) |
+         ((unsigned)(n >> 3) << 17) | ((unsigned)(m >> 4) << 24);
 }
 
 __device__ __forceinline__ void mma_tf32(unsigned tmem_d, unsigned long long adesc, unsigned long long bdesc,
@@ -107,7 +131,10 @@ __device__ __forceinline__ void mma_commit(unsigned long long* bar) {
                : "memory");
 }
 
+enum { EPI_FWD = 0, EPI_GATE = 1, EPI_UPDATE = 2 };
+
 struct Epilogue {
+  // EPI_FWD: C = act(acc + bias) * dropout
   const float* bias;       // [N], nullable
   int relu;
   const uint8_t* mask;     // [M,N] keep bytes (row stride N), nullable
@@ -115,8 +142,16 @@ struct Epilogue {
   uint64_t seed, offset;
   int layer;
   float* out2;             // optional dense copy [M,N]
+  // EPI_GATE: C = gate ? (gate[m,n] > 0 ? acc * scale : 0) : acc
+  const float* gate;
+  int ldgate;
+  // EPI_UPDATE: g = acc; optimizer step on C (= the weights), s1, s2 in place
+  float* s1;
+  float* s2;
+  OptParams op;
 };
 
+template <bool AMN, bool BMN, int EPI, int OPT>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
                  int K, float* __restrict__ C, int ldc, Epilogue ep) {
@@ -157,23 +192,32 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const unsigned ph = (kb / kStages) & 1;
         mbar_wait(&sm.empty_bar[s], ph ^ 1);
         mbar_expect_tx(&sm.full_bar[s], 2 * kTileBytes);
-        tma_load_2d(sm.a[s], &map_a, &sm.full_bar[s], kb * BK, m0);
-        tma_load_2d(sm.b[s], &map_b, &sm.full_bar[s], kb * BK, n0);
+        if (!AMN) tma_load_2d(sm.a[s], &map_a, &sm.full_bar[s], kb * BK, m0);
+        else
+#pragma unroll
+          for (int j = 0; j < BM / 32; ++j) tma_load_2d(sm.a[s] + j * 1024, &map_a, &sm.full_bar[s], m0 + 32 * j, kb * BK);
+        if (!BMN) tma_load_2d(sm.b[s], &map_b, &sm.full_bar[s], kb * BK, n0);
+        else
+#pragma unroll
+          for (int j = 0; j < BN / 32; ++j) tma_load_2d(sm.b[s] + j * 1024, &map_b, &sm.full_bar[s], n0 + 32 * j, kb * BK);
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      const unsigned idesc = make_idesc_tf32(BM, BN);
+      const unsigned idesc = make_idesc_tf32(BM, BN, AMN, BMN);
       for (int kb = 0; kb < kblocks; ++kb) {
         const int s = kb % kStages;
         const unsigned ph = (kb / kStages) & 1;
         mbar_wait(&sm.full_bar[s], ph);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const unsigned long long ad = make_desc_kmajor_sw128(sm.a[s]);
-        const unsigned long long bd = make_desc_kmajor_sw128(sm.b[s]);
+        const unsigned long long ad = AMN ? make_desc_mnmajor_sw128(sm.a[s]) : make_desc_kmajor_sw128(sm.a[s]);
+        const unsigned long long bd = BMN ? make_desc_mnmajor_sw128(sm.b[s]) : make_desc_kmajor_sw128(sm.b[s]);
+        // one instruction consumes 8 reduction steps: K-major +32 B (2 x 16 B), MN-major +8 rows of
+        // 128 B (64 x 16 B)
+        constexpr unsigned long long astep = AMN ? 64 : 2, bstep = BMN ? 64 : 2;
 #pragma unroll
-        for (int k = 0; k < BK / 8; ++k)     // 8 tf32 = 32 bytes per instruction: +2 in 16-byte units
-          mma_tf32(tmem_d, ad + (unsigned long long)(2 * k), bd + (unsigned long long)(2 * k), idesc, (kb | k) != 0);
+        for (int k = 0; k < BK / 8; ++k)
+          mma_tf32(tmem_d, ad + astep * k, bd + bstep * k, idesc, (kb | k) != 0);
         mma_commit(&sm.empty_bar[s]);          // slot free once these MMAs have read it
       }
       mma_commit(&sm.tmem_full_bar);           // accumulator complete
@@ -203,13 +247,25 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           const int n = n0 + c0 + j;
           if (n < N) {
             float v = __uint_as_float(r[j]);
-            if (ep.bias) v += ep.bias[n];
-            if (ep.relu) v = fmaxf(v, 0.f);
-            const size_t idx = (size_t)row * N + n;
-            if (ep.mask) v = ep.mask[idx] ? v * ep.scale : 0.f;
-            else if (ep.keep_prob < 1.f) v = philox_keep(ep.seed, ep.offset, ep.layer, idx, ep.keep_prob) ? v * ep.scale : 0.f;
-            C[(size_t)row * ldc + n] = v;
-            if (ep.out2) ep.out2[idx] = v;
+            if (EPI == EPI_FWD) {
+              if (ep.bias) v += ep.bias[n];
+              if (ep.relu) v = fmaxf(v, 0.f);
+              const size_t idx = (size_t)row * N + n;
+              if (ep.mask) v = ep.mask[idx] ? v * ep.scale : 0.f;
+              else if (ep.keep_prob < 1.f) v = philox_keep(ep.seed, ep.offset, ep.layer, idx, ep.keep_prob) ? v * ep.scale : 0.f;
+              C[(size_t)row * ldc + n] = v;
+              if (ep.out2) ep.out2[idx] = v;
+            } else if (EPI == EPI_GATE) {
+              if (ep.gate) v = ep.gate[(size_t)row * ep.ldgate + n] > 0.f ? v * ep.scale : 0.f;
+              C[(size_t)row * ldc + n] = v;
+            } else {
+              const size_t o = (size_t)row * ldc + n;
+              float p = C[o], a = ep.s1[o], b2 = (OPT == 2) ? ep.s2[o] : 0.f;
+              opt_update<OPT>(ep.op, p, v, a, b2);
+              C[o] = p;
+              ep.s1[o] = a;
+              if (OPT == 2) ep.s2[o] = b2;
+            }
           }
         }
       }
@@ -240,8 +296,10 @@ inline EncodeTiledFn encode_fn() {
   return fn;
 }
 
-// [rows, cols] fp32 row-major with leading dimension ld (floats); box = 32 floats x box_rows, 128B swizzle
-inline int make_map(CUtensorMap* map, const float* base, int rows, int cols, int ld, int box_rows) {
+// [rows, cols] fp32 row-major with leading dimension ld (floats); box = 32 floats x box_rows, 128B swizzle.
+// K-major operand: rows = its M/N extent, cols = reduction, box_rows = 128.
+// MN-major operand: rows = reduction, cols = its M/N extent, box_rows = 32 (four boxes per tile).
+inline int make_map(CUtensorMap* map, const float* base, int rows, int cols, int ld, int box_rows, bool mn_major = false) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return fail_msg("libsplitnn: cuTensorMapEncodeTiled is not available from this driver");
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -249,7 +307,8 @@ inline int make_map(CUtensorMap* map, const float* base, int rows, int cols, int
   cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail_msg("libsplitnn: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
   return 0;

@@ -173,14 +173,18 @@ static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t 
 }
 
 // ---------------------------------------------------------------- shared launch helpers
-static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int ldb, int N, int K, float* C, int ldc,
+// C[M,N] (+epilogue) = sum_r A(m,r) B(n,r).  Operand memory: K-major = [extent, R] row-major,
+// MN-major = [R, extent] row-major; lda/ldb are the row strides of those matrices.
+template <bool AMN, bool BMN, int EPI, int OPT>
+static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
                           const tc::Epilogue& ep, cudaStream_t st) {
   CUtensorMap ma, mb;
-  if (tc::make_map(&ma, A, M, K, lda, tc::BM)) return 1;
-  if (tc::make_map(&mb, Bm, N, K, ldb, tc::BN)) return 1;
-  if (set_smem(tc::gemm_tf32_kernel, tc::kSmemBytes)) return 1;
+  if (AMN ? tc::make_map(&ma, A, R, M, lda, 32, true) : tc::make_map(&ma, A, M, R, lda, tc::BM)) return 1;
+  if (BMN ? tc::make_map(&mb, Bm, R, N, ldb, 32, true) : tc::make_map(&mb, Bm, N, R, ldb, tc::BN)) return 1;
+  auto kern = tc::gemm_tf32_kernel<AMN, BMN, EPI, OPT>;
+  if (set_smem(kern, tc::kSmemBytes)) return 1;
   dim3 grid(ceil_div(N, tc::BN), ceil_div(M, tc::BM));
-  launch_k(tc::gemm_tf32_kernel, grid, dim3(tc::kThreads), tc::kSmemBytes, st, ma, mb, M, N, K, C, ldc, ep);
+  launch_k(kern, grid, dim3(tc::kThreads), tc::kSmemBytes, st, ma, mb, M, N, R, C, ldc, ep);
   SN_LAUNCH_CHECK();
   return 0;
 }
@@ -213,9 +217,11 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
     SN_LAUNCH_CHECK();
   } else if (g_matmul_precision.load() == 1 && tc::usable(X, ldx, W, K, K)) {
     // tensor-bound regime: tcgen05 TF32 GEMM with the bias / ReLU / dropout epilogue fused
-    tc::Epilogue ep{bias, relu, mask, keep_prob, scale, seed, offset, layer, out2};
+    tc::Epilogue ep{};
+    ep.bias = bias; ep.relu = relu; ep.mask = mask; ep.keep_prob = keep_prob; ep.scale = scale;
+    ep.seed = seed; ep.offset = offset; ep.layer = layer; ep.out2 = out2;
     cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
-    int rc = launch_tc_gemm(X, ldx, B, W, K, N, K, H, ldh, ep, st);
+    int rc = launch_tc_gemm<false, false, tc::EPI_FWD, 0>(X, ldx, B, W, K, N, K, H, ldh, ep, st);
     Profiler::end(pe, st);
     if (rc) return rc;
   } else {
@@ -664,6 +670,25 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
       }
+    } else if (g_matmul_precision.load() == 1 && (K % 4) == 0 && (N % 4) == 0) {
+      // tensor-bound regime (perf mode): dA, then dW fused with the optimizer, both on tcgen05
+      if (need_da) {
+        tc::Epilogue ep{};
+        ep.gate = gateH; ep.ldgate = K; ep.scale = gscale;
+        cudaEvent_t pe = h->prof.begin(st, 2, l);
+        int rc = launch_tc_gemm<false, true, tc::EPI_GATE, 0>(dZ, N, B, h->W[l], K, K, N, dst, K, ep, st);
+        Profiler::end(pe, st);
+        if (rc) return rc;
+      }
+      launch_k(bias_grad_update_kernel<OPT>, dim3(ceil_div(N, 256)), dim3(256), 0, st, dZ, N, B, N, h->b[l],
+               s.s1[2 * l + 1], s.s2[2 * l + 1], op);
+      SN_LAUNCH_CHECK();
+      tc::Epilogue eu{};
+      eu.s1 = s.s1[2 * l]; eu.s2 = s.s2[2 * l]; eu.op = op;
+      cudaEvent_t pe = h->prof.begin(st, 1, l);
+      int rc = launch_tc_gemm<true, true, tc::EPI_UPDATE, OPT>(dZ, N, N, A, K, K, B, h->W[l], K, eu, st);
+      Profiler::end(pe, st);
+      if (rc) return rc;
     } else {
       // general-batch path: dA from W_old first, then dW into a buffer, then the updates
       if (!h->dWbuf) {

@@ -327,3 +327,47 @@ def test_tcgen05_tf32_linear_forward(eng, B, K, N, relu):
     assert rel_err(got, ref) <= 3e-3          # TF32 itself: ~6e-4 here, documented as perf mode only
     exact = eng.linear_forward(cu(x), cu(W), cu(bias), relu=relu, keep_mask=cu(mask), mask_scale=2.0).cpu().numpy()
     assert rel_err(exact, ref) <= 1e-5        # default precision is untouched
+
+
+@pytest.mark.parametrize("opt", ["sgd", "adam"])
+def test_tcgen05_large_batch_train_step(eng, opt):
+    """Whole large-batch step on tensor cores (forward, dX with MN-major W, dW fused with the
+    optimizer with both operands MN-major) against the fp32 oracle, at TF32 accuracy."""
+    rng = np.random.RandomState(5)
+    dims = [5408, 512, 104, 100]
+    shapes = [(512, 5408), (512,), (104, 512), (104,), (100, 104), (100,)]
+    b = T(seeded_weights(shapes, 31))
+    spec = R.BobSpec(tuple(dims), False, 0.5)
+    gp = [cu(p.numpy()) for p in b]
+    kw = dict(optimizer=eng.SN_OPT_ADAM, lr=1e-3, weight_decay=1e-5) if opt == "adam" else \
+        dict(optimizer=eng.SN_OPT_SGD_MOMENTUM, lr=1e-3, momentum=0.9)
+    bob = eng.BobEngine(dims, gp[0::2], gp[1::2], max_batch=300, **kw)
+    B = 300
+    act = (rng.rand(B, 5408) * 4 * (rng.rand(B, 5408) < 0.6)).astype(np.float32)
+    y = rng.randint(0, 10, size=B).astype(np.int64)
+    masks = seeded_masks(B, (512, 104), 60)
+    bl = [p.detach().clone().requires_grad_(True) for p in b]
+    at = torch.from_numpy(act).requires_grad_(True)
+    logits_ref = R.bob_forward(at, bl, spec, T(masks))
+    loss_ref = R.cross_entropy(logits_ref, torch.from_numpy(y))
+    loss_ref.backward()
+    w_old = [p.clone() for p in b]
+    if opt == "adam":
+        R.adam_(b, [p.grad for p in bl], R.AdamState(), 1e-3, weight_decay=1e-5)
+    else:
+        R.sgd_momentum_(b, [p.grad for p in bl], R.SGDState(), 1e-3, 0.9)
+    eng.set_matmul_precision(1)
+    try:
+        loss, cut, logits = bob.train_step(cu(act), cu(y), masks=[cu(m) for m in masks], want_logits=True)
+        torch.cuda.synchronize()
+    finally:
+        eng.set_matmul_precision(0)
+    assert rel_err(logits.cpu(), logits_ref.detach()) <= 5e-3
+    assert abs(loss.item() - loss_ref.item()) <= 5e-3 * abs(loss_ref.item())
+    # TF32 truncates operands (10-bit mantissa, biased toward zero); six chained GEMMs and the
+    # softmax gradient compound it to a few percent on the cut gradient.  Perf mode only.
+    assert rel_err(cut.cpu(), at.grad) <= 5e-2
+    for p_ref, p, p0 in zip(b, gp, w_old):
+        assert rel_err(p.cpu(), p_ref) <= 2e-3
+        if opt == "sgd":        # the applied step itself (lr * grad) at TF32 accuracy
+            assert rel_err(p.cpu() - p0, p_ref - p0) <= 5e-2

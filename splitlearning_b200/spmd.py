@@ -88,6 +88,91 @@ def run_vanilla_schedule(rank, world, bob, alices, batch_fn, n_alices, turn, fir
             loss_sink(i, loss)
 
 
+# ------------------------------------------------------------------------------- SISA
+def run_sisa_schedule(rank, world, bob, alices, data, sizes, B, local_epochs, server_epochs, device,
+                      unlearn=None, timers=None):
+    """SISA over ranks (`split_nn.py:74-110` driving `data_entities_vanilla_sisa.py`).
+
+    This is the part of the reference that DOES shard: every Alice owns her model and her data.
+      phase 1  each rank trains its Alices locally, no communication (:55-70, :326-334);
+      phase 2  each Alice runs her frozen model over her whole shard in one launch and ships the
+               [n_k,5408] block + labels to rank 0 in one message each - the bulk transfer that
+               replaces a pickled list of per-batch tensors over RPC (:196-211,:279);
+      phase 3  rank 0 runs the server epochs over the cached blocks, client by client (:298-313);
+      phase 4  (unlearn=(k, omit_label)) Alice k drops the label, retrains with a fresh optimizer,
+               re-ships her block; rank 0 replaces that cache entry and trains again (:139-168).
+    alices: {k: engine with local_step/forward/reset_opt}; data: {k: (x[n,1,28,28], y[n])} for
+    the Alices this rank hosts; sizes[k] = n_k for every Alice (all ranks know the partition).
+    Returns rank 0's cache {k: (acts, labels)} (None elsewhere)."""
+    n_alices = len(sizes)
+    tick = timers if timers is not None else (lambda name: None)
+
+    def train_local(k, x, y):
+        for _ in range(local_epochs):
+            for s in range(0, x.shape[0], B):
+                alices[k].local_step(x[s:s + B], y[s:s + B])
+
+    def ship(k, x, y, cache):
+        own = owner_rank(k, world)
+        n = x.shape[0] if rank == own else None
+        if rank == own:
+            acts = alices[k].forward(x)
+            if own == 0:
+                cache[k] = (acts, y)
+            else:
+                dist.send(acts, dst=0)
+                dist.send(y, dst=0)
+        elif rank == 0:
+            acts = torch.empty(sizes[k], D0, dtype=torch.float32, device=device)
+            lab = torch.empty(sizes[k], dtype=torch.int64, device=device)
+            dist.recv(acts, src=own)
+            dist.recv(lab, src=own)
+            cache[k] = (acts, lab)
+        return n
+
+    def server(cache):
+        for _ in range(server_epochs):
+            for k in range(n_alices):
+                acts, lab = cache[k]
+                n = acts.shape[0]
+                if n:
+                    bob.server_epoch(acts, lab, list(range(0, n, B)) + [n])
+
+    tick("start")
+    for k in sorted(alices):
+        train_local(k, *data[k])
+    tick("local_training")
+    cache = {} if rank == 0 else None
+    for k in range(n_alices):
+        ship(k, *(data[k] if k in alices else (None, None)), cache)
+    tick("activation_gather")
+    if rank == 0:
+        server(cache)
+    tick("server_epochs")
+    if unlearn is not None:
+        k, omit = unlearn
+        if k in alices:
+            x, y = data[k]
+            keep = y != omit
+            xu, yu = x[keep].contiguous(), y[keep].contiguous()
+            alices[k].reset_opt()
+            train_local(k, xu, yu)
+            data = dict(data)
+            data[k] = (xu, yu)
+        # every rank must know the new shard size: it is a function of the (shared) partition
+        if world > 1:
+            n_new = torch.tensor([data[k][0].shape[0] if k in alices else 0], device=device, dtype=torch.int64)
+            dist.broadcast(n_new, src=owner_rank(k, world))
+            sizes = list(sizes)
+            sizes[k] = int(n_new.item())
+        tick("unlearn_retrain")
+        ship(k, *(data[k] if k in alices else (None, None)), cache)
+        if rank == 0:
+            server(cache)
+        tick("unlearn_server_epochs")
+    return cache
+
+
 # ------------------------------------------------------------------------------- CUDA engines
 class _CudaAlice:
     def __init__(self, device, lr):
@@ -111,6 +196,40 @@ class _CudaAlice:
         self.b.data.copy_(flat[288:320])
 
 
+class _CudaSisaAlice:
+    """SISA Alice: local Adam(wd 1e-5) steps (`data_entities_vanilla_sisa.py:48,62-70`)."""
+
+    def __init__(self, device, lr, B):
+        from . import engine as E
+        from . import models as M
+        self.model = M.model1_sisa(device)
+        self.kw = dict(optimizer=E.SN_OPT_ADAM, lr=lr, weight_decay=1e-5, max_batch=B)
+        self.eng = self.model.make_engine(**self.kw)
+        self.loss = torch.zeros((), device=device)
+
+    def local_step(self, x, y):
+        self.eng.local_step(x, y, loss_out=self.loss)
+
+    def forward(self, x):
+        return self.eng.forward(x)
+
+    def reset_opt(self):
+        self.eng.reset_opt()
+
+
+class _CudaSisaBob:
+    def __init__(self, device, lr, B):
+        from . import engine as E
+        from . import models as M
+        self.model = M.model2_sisa(device)
+        self.eng = self.model.make_engine(optimizer=E.SN_OPT_ADAM, lr=lr, weight_decay=1e-5, n_opt_slots=1, max_batch=B)
+        self.offset = 0
+
+    def server_epoch(self, acts, labels, offsets):
+        self.eng.server_epoch(acts, labels, offsets, slot=0, masks=None, seed=7, offset=self.offset)
+        self.offset += len(offsets)
+
+
 class _CudaBob:
     def __init__(self, device, lr, n_slots, B):
         from . import engine as E
@@ -125,6 +244,41 @@ class _CudaBob:
         self.offset += 1
         return self.eng.train_step(act, y, slot=slot, masks=None, seed=1, offset=self.offset, want_cut_grad=True,
                                    loss_out=self.loss)
+
+
+def bench_sisa(rank, world, device, B, n_alices):
+    """SISA on the same ranks (BASELINE.json configs[2]/[3] shape: 4 Alices, 55,999 train samples,
+    1 local epoch, 1 server epoch, then Alice 1 unlearns label 9 and Bob retrains).  Phase times are
+    max over ranks (CUDA events + barriers)."""
+    sizes = [16271 * 8 // 10, 21685 * 8 // 10, 15329 * 8 // 10, 16715 * 8 // 10][:n_alices]
+    g = torch.Generator().manual_seed(5)
+    data, mine = {}, {}
+    for k, n in enumerate(sizes):
+        x = torch.randint(0, 256, (n, 1, 28, 28), generator=g).float() * (torch.rand(n, 1, 28, 28, generator=g) < 0.4)
+        y = torch.randint(0, 10, (n,), generator=g)
+        if owner_rank(k, world) == rank:
+            data[k] = (x.to(device), y.to(device))
+            mine[k] = _CudaSisaAlice(device, 1e-3, B)
+    bob = _CudaSisaBob(device, 1e-3, B) if rank == 0 else None
+    marks = []
+
+    def tick(name):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        marks.append((name, ev))
+    run_sisa_schedule(rank, world, bob, mine, data, sizes, B, 1, 1, device, unlearn=(0, 9), timers=tick)
+    torch.cuda.synchronize()
+    out = {"samples": sum(sizes), "alices": n_alices, "placement": [owner_rank(k, world) for k in range(n_alices)]}
+    for (n0, e0), (n1, e1) in zip(marks[:-1], marks[1:]):
+        t = torch.tensor([e0.elapsed_time(e1)], device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out[n1 + "_ms"] = round(float(t.item()), 3)
+    out["gather_bytes"] = sum(sizes[k] * (D0 * 4 + 8) for k in range(n_alices) if owner_rank(k, world) != 0)
+    return out
 
 
 def bench_vanilla(args, B, n_alices, turn, config, peak):
@@ -185,6 +339,7 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
     def sink(i, loss):
         hloss[i - (W + K)].copy_(loss, non_blocking=True)
     e2e_ms = timed(host_batch, W + K, sink)
+    sisa = bench_sisa(rank, world, device, B, n_alices)
 
     if rank == 0:
         value = K * B / (ms * 1e-3)
@@ -201,6 +356,7 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
                          "frac": round(step_bytes / (ms * 1e-3 / K) / 1e9 / peak[0], 4), "traffic": None,
                          "peak_source": peak[1]},
             "nvlink_bytes_per_step": 2 * B * D0 * 4 + B * 8,
+            "sisa": sisa,
             "note": "vanilla split learning is a sequential chain (SURVEY.md 8e): extra GPUs host Alices and add "
                     "two NVLink messages per step; they cannot add throughput without changing results",
         }

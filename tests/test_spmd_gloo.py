@@ -123,3 +123,85 @@ def test_owner_placement():
     lab.copy_(torch.arange(16))
     act.fill_(1.5)
     assert lab.tolist() == list(range(16)) and float(msg[0]) == 1.5
+
+
+# ----------------------------------------------------------------------------- SISA over ranks
+class FakeSisaAlice(FakeAlice):
+    def __init__(self, seed):
+        super().__init__(seed)
+        self.adam = R.AdamState()
+
+    def local_step(self, x, y):
+        out = R.sisa_alice_step(self.p, x, y)
+        R.adam_(self.p, out["alice_grads"], self.adam, 1e-3, weight_decay=1e-5)
+
+    def reset_opt(self):
+        self.adam = R.AdamState()
+
+
+class FakeSisaBob:
+    def __init__(self):
+        g = torch.Generator().manual_seed(5)
+        self.p = [torch.randn(24, 5408, generator=g) * 0.01, torch.zeros(24), torch.randn(10, 24, generator=g) * 0.1,
+                  torch.zeros(10)]
+        self.adam = R.AdamState()
+        self.batches = []
+
+    def server_epoch(self, acts, labels, offsets):
+        for s, e in zip(offsets[:-1], offsets[1:]):
+            out = R.sisa_server_step(self.p, acts[s:e], labels[s:e], None, SPEC)
+            R.adam_(self.p, out["bob_grads"], self.adam, 1e-3, weight_decay=1e-5)
+            self.batches.append(e - s)
+
+
+SISA_SIZES = [10, 7, 9]
+
+
+def _sisa_data():
+    g = torch.Generator().manual_seed(77)
+    out = {}
+    for k, n in enumerate(SISA_SIZES):
+        out[k] = (torch.randint(0, 256, (n, 1, 28, 28), generator=g).float(), torch.randint(8, 10, (n,), generator=g))
+    return out
+
+
+def _run_sisa(rank, world, out_dir, port):
+    if world > 1:
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    full = _sisa_data()
+    mine = {k: FakeSisaAlice(300 + k) for k in range(len(SISA_SIZES)) if spmd.owner_rank(k, world) == rank}
+    data = {k: full[k] for k in mine}
+    bob = FakeSisaBob() if rank == 0 else None
+    cache = spmd.run_sisa_schedule(rank, world, bob, mine, data, SISA_SIZES, B, 1, 2, torch.device("cpu"), unlearn=(0, 9))
+    out = {f"alice{k}": a.get_weights().numpy() for k, a in mine.items()}
+    if rank == 0:
+        out.update({f"bob{i}": p.numpy() for i, p in enumerate(bob.p)})
+        out["batches"] = np.array(bob.batches)
+        out["cache0_n"] = np.array(cache[0][0].shape[0])
+        out["cache0_labels"] = cache[0][1].numpy()
+    np.savez(os.path.join(out_dir, f"s{world}_r{rank}.npz"), **out)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sisa_schedule_matches_single_process(world):
+    def collect(d, w):
+        merged = {}
+        for r in range(w):
+            with np.load(os.path.join(d, f"s{w}_r{r}.npz")) as f:
+                merged.update({k: f[k] for k in f.files})
+        return merged
+    with tempfile.TemporaryDirectory() as d:
+        _run_sisa(0, 1, d, 0)
+        ref = collect(d, 1)
+        mp.spawn(_run_sisa, args=(world, d, 29720 + world), nprocs=world, join=True)
+        got = collect(d, world)
+    assert set(got) == set(ref)
+    assert (ref["cache0_labels"] != 9).all() and int(ref["cache0_n"]) < SISA_SIZES[0]      # the unlearned shard was re-shipped
+    for k in ref:
+        assert np.array_equal(got[k], ref[k]), k

@@ -207,6 +207,12 @@ int sn_alice_backward_update(sn_alice* h, const float* x, const float* cut_grad,
 int sn_alice_local_step(sn_alice* h, const float* x, const int64_t* labels, int B,
                         float* loss_out, void* stream);
 
+/* One pass of sn_alice_local_step over n device-resident samples in batches of `batch` (the last
+ * one may be short): the whole inner loop of alice.train, data_entities_vanilla_sisa.py:59-70, in
+ * one call.  loss_per_step: device float[ceil(n/batch)], nullable. */
+int sn_alice_local_epoch(sn_alice* h, const float* x, const int64_t* labels, int64_t n, int batch,
+                         float* loss_per_step, void* stream);
+
 /* ------------------------------------------------------------------ NVLink plumbing */
 int sn_p2p_enable_all(int n_devices);
 int sn_p2p_copy(void* dst, int dst_device, const void* src, int src_device, size_t bytes,

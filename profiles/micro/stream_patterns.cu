@@ -68,6 +68,62 @@ void run(const char* name, const float* W, int N, int K, float* sink) {
   printf("%-44s smem/CTA %6zu KB  %8.2f us  %8.1f GB/s  (%s)\n", name, smem / 1024, us, (double)N * K * 4 / us / 1e3, cudaGetErrorString(cudaGetLastError()));
 }
 
+// read-modify-write of two arrays (weights + momentum), per-thread cp.async ring of D rows:
+// the memory pattern of bwd_update_kernel without its math.  grid (kgroups, nsplit), 8 warps:
+// kw warps along k (128 floats each), 8/kw along rows.
+template <int D>
+__global__ void __launch_bounds__(256, 1) rmw_kernel(float* W, float* S, int N, int K, int kw, int rows_per_cta) {
+  extern __shared__ float4 ring[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int wk = warp % kw, wr = warp / kw, rw = 8 / kw;
+  const int nb0 = blockIdx.y * rows_per_cta, nb1 = min(N, nb0 + rows_per_cta);
+  const int k0 = (blockIdx.x * kw + wk) * 128 + lane * 4;
+  const bool kok = k0 < K;
+  auto issue = [&](int slot, int row) {
+    if (kok && row < nb1) {
+      size_t o = (size_t)row * K + k0;
+      cp_async16(ring + (0 * D + slot) * 256 + tid, W + o);
+      cp_async16(ring + (1 * D + slot) * 256 + tid, S + o);
+    }
+    commit();
+  };
+  int n = nb0 + wr;
+  for (int d = 0; d < D - 1; ++d) issue(d, n + d * rw);
+  int slot = 0;
+  for (; n < nb1; n += rw) {
+    issue((slot + D - 1) % D, n + (D - 1) * rw);
+    wait<D - 1>();
+    if (kok) {
+      float4 w = ring[(0 * D + slot) * 256 + tid], m = ring[(1 * D + slot) * 256 + tid];
+      m.x = 0.9f * m.x + w.x; m.y = 0.9f * m.y + w.y; m.z = 0.9f * m.z + w.z; m.w = 0.9f * m.w + w.w;
+      w.x -= 1e-9f * m.x; w.y -= 1e-9f * m.y; w.z -= 1e-9f * m.z; w.w -= 1e-9f * m.w;
+      size_t o = (size_t)n * K + k0;
+      *reinterpret_cast<float4*>(W + o) = w;
+      __stcs(reinterpret_cast<float4*>(S + o), m);
+    }
+    slot = (slot + 1) % D;
+  }
+  wait<0>();
+}
+
+template <int D>
+void run_rmw(const char* name, float* W, float* S, int N, int K, int kw, int nsplit) {
+  int kgroups = (K / 128 + kw) / kw;  // ceil(43/kw)
+  kgroups = ((K + 127) / 128 + kw - 1) / kw;
+  int rows = (N + nsplit - 1) / nsplit;
+  size_t smem = (size_t)2 * D * 256 * 16;
+  cudaFuncSetAttribute(rmw_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+  for (int i = 0; i < 3; ++i) rmw_kernel<D><<<dim3(kgroups, nsplit), 256, smem>>>(W, S, N, K, kw, rows);
+  cudaEventRecord(a);
+  const int reps = 20;
+  for (int i = 0; i < reps; ++i) rmw_kernel<D><<<dim3(kgroups, nsplit), 256, smem>>>(W + (size_t)(i % 2) * N * K, S + (size_t)(i % 2) * N * K, N, K, kw, rows);
+  cudaEventRecord(b); cudaEventSynchronize(b);
+  float ms; cudaEventElapsedTime(&ms, a, b);
+  double us = 1e3 * ms / reps;
+  printf("%-52s grid %3dx%-3d  %8.2f us  %8.1f GB/s (r+w)  (%s)\n", name, kgroups, nsplit, us, (double)N * K * 16 / us / 1e3, cudaGetErrorString(cudaGetLastError()));
+}
+
 int main() {
   const int N = 5000, K = 5408;
   float *W, *sink;
@@ -83,5 +139,12 @@ int main() {
   run<8, 2, 3>("8 rows x 1 KB,  ring 3", W, N, K, sink);
   run<1, 1, 8>("1 row  x 512 B, ring 8 (bwd kernel today)", W, N, K, sink);
   run<1, 1, 16>("1 row  x 512 B, ring 16", W, N, K, sink);
+  float* S; cudaMalloc(&S, (size_t)2 * N * K * 4); cudaMemset(S, 0, (size_t)2 * N * K * 4);
+  run_rmw<8>("RMW W+momentum, kw=4 nsplit=13, ring 8 (bwd today)", W, S, N, K, 4, 13);
+  run_rmw<16>("RMW W+momentum, kw=4 nsplit=13, ring 16", W, S, N, K, 4, 13);
+  run_rmw<8>("RMW W+momentum, kw=8 nsplit=24, ring 8", W, S, N, K, 8, 24);
+  run_rmw<8>("RMW W+momentum, kw=2 nsplit=6,  ring 8", W, S, N, K, 2, 6);
+  run_rmw<8>("RMW W+momentum, kw=1 nsplit=3,  ring 8", W, S, N, K, 1, 3);
+  run_rmw<12>("RMW W+momentum, kw=8 nsplit=24, ring 12", W, S, N, K, 8, 24);
   return 0;
 }

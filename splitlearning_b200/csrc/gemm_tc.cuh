@@ -17,7 +17,8 @@
 //   warp 1      TMEM allocation + single-thread tcgen05.mma.kind::tf32 issue (M=128,N=128,K=8 per
 //               instruction, fp32 accumulation in TMEM), tcgen05.commit releases ring slots
 //   warps 2..5  epilogue: tcgen05.ld the accumulator (32 lanes x 32 columns per instruction),
-//               + bias, ReLU, dropout keep-mask / Philox, vectorised stores
+//               transpose through shared memory so every global access is a contiguous row
+//               segment, then bias/ReLU/dropout, the ReLU/dropout gate, or the optimizer update
 // Out-of-range rows/columns/k are zero-filled by TMA and masked in the epilogue, so any M, N and
 // any K that is a multiple of 4 work.
 //
@@ -227,7 +228,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     const int q = warp & 3;
     mbar_wait(&sm.tmem_full_bar, 0);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const int row = m0 + q * 32 + lane;
+    // The operand ring is idle once the accumulator is complete: reuse it as a per-warp 32x33
+    // transpose tile, so that global accesses are row-contiguous (lane = column) instead of one
+    // row per lane.
+    float* tile = reinterpret_cast<float*>(&sm.a[0][0]) + q * (32 * 33);
 #pragma unroll 1
     for (int c0 = 0; c0 < BN; c0 += 32) {
       unsigned r[32];
@@ -241,34 +245,39 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
           : "r"(taddr));
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      if (row < M) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int n = n0 + c0 + j;
-          if (n < N) {
-            float v = __uint_as_float(r[j]);
-            if (EPI == EPI_FWD) {
-              if (ep.bias) v += ep.bias[n];
-              if (ep.relu) v = fmaxf(v, 0.f);
-              const size_t idx = (size_t)row * N + n;
-              if (ep.mask) v = ep.mask[idx] ? v * ep.scale : 0.f;
-              else if (ep.keep_prob < 1.f) v = philox_keep(ep.seed, ep.offset, ep.layer, idx, ep.keep_prob) ? v * ep.scale : 0.f;
-              C[(size_t)row * ldc + n] = v;
-              if (ep.out2) ep.out2[idx] = v;
-            } else if (EPI == EPI_GATE) {
-              if (ep.gate) v = ep.gate[(size_t)row * ep.ldgate + n] > 0.f ? v * ep.scale : 0.f;
-              C[(size_t)row * ldc + n] = v;
-            } else {
-              const size_t o = (size_t)row * ldc + n;
-              float p = C[o], a = ep.s1[o], b2 = (OPT == 2) ? ep.s2[o] : 0.f;
-              opt_update<OPT>(ep.op, p, v, a, b2);
-              C[o] = p;
-              ep.s1[o] = a;
-              if (OPT == 2) ep.s2[o] = b2;
-            }
+      for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(r[j]);     // lane holds row q*32+lane
+      __syncwarp();
+      const int n = n0 + c0 + lane;                                                // now lane = column
+      if (n < N) {
+        const float bias_v = (EPI == EPI_FWD && ep.bias) ? ep.bias[n] : 0.f;
+#pragma unroll 4
+        for (int rr = 0; rr < 32; ++rr) {
+          const int row = m0 + q * 32 + rr;
+          if (row >= M) break;
+          float v = tile[rr * 33 + lane];
+          if (EPI == EPI_FWD) {
+            v += bias_v;
+            if (ep.relu) v = fmaxf(v, 0.f);
+            const size_t idx = (size_t)row * N + n;
+            if (ep.mask) v = ep.mask[idx] ? v * ep.scale : 0.f;
+            else if (ep.keep_prob < 1.f) v = philox_keep(ep.seed, ep.offset, ep.layer, idx, ep.keep_prob) ? v * ep.scale : 0.f;
+            C[(size_t)row * ldc + n] = v;
+            if (ep.out2) ep.out2[idx] = v;
+          } else if (EPI == EPI_GATE) {
+            if (ep.gate) v = ep.gate[(size_t)row * ep.ldgate + n] > 0.f ? v * ep.scale : 0.f;
+            C[(size_t)row * ldc + n] = v;
+          } else {
+            const size_t o = (size_t)row * ldc + n;
+            float p = C[o], a = ep.s1[o], b2 = (OPT == 2) ? ep.s2[o] : 0.f;
+            opt_update<OPT>(ep.op, p, v, a, b2);
+            C[o] = p;
+            ep.s1[o] = a;
+            if (OPT == 2) ep.s2[o] = b2;
           }
         }
       }
+      __syncwarp();
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }

@@ -931,6 +931,20 @@ int sn_alice_local_step(sn_alice* h, const float* x, const int64_t* labels, int 
   return alice_bwd(h, x, h->dact, B, st);
 }
 
+int sn_alice_local_epoch(sn_alice* h, const float* x, const int64_t* labels, int64_t n, int batch, float* loss_per_step,
+                         void* stream) {
+  SN_ALICE_ENTER(h);
+  SN_REQUIRE(x && labels && n >= 0 && batch > 0 && batch <= h->max_batch, "sn_alice_local_epoch: bad arguments");
+  int64_t step = 0;
+  for (int64_t s = 0; s < n; s += batch, ++step) {
+    const int b = (int)std::min<int64_t>(batch, n - s);
+    int rc = sn_alice_local_step(h, x + (size_t)s * 784, labels + s, b, loss_per_step ? loss_per_step + step : nullptr,
+                                 stream);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
 // ------------------------------------------------------------------ NVLink plumbing
 int sn_p2p_enable_all(int n_devices) {
   int ndev = 0;

@@ -75,11 +75,10 @@ class alice(object):
                                              max_batch=self.batch_size)
 
     def _local_epochs(self, dataset):
-        loss = torch.empty((), device=self.device)
         for epoch in range(self.local_epochs):
-            for inputs, labels in dataset.batches(self.rng):
-                self.engine.local_step(inputs, labels, loss_out=loss)
-        return loss
+            x, y = dataset.epoch(self.rng)          # this epoch's batch order, one gather
+            if x.shape[0]:
+                self.engine.local_epoch(x, y, dataset.batch_size)
 
     def train(self):
         self.logger.info("Local Training")

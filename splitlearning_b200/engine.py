@@ -183,6 +183,12 @@ class AliceEngine:
         check(self.lib.sn_alice_local_step(self.h, ptr(x), ptr(labels), x.shape[0], ptr(loss), _stream(x.device)))
         return loss
 
+    def local_epoch(self, x, labels, batch, loss_per_step=None):
+        """All batches of one pass over (x [n,1,28,28], labels [n]) in a single library call."""
+        _f32c(x)
+        check(self.lib.sn_alice_local_epoch(self.h, ptr(x), ptr(labels), int(x.shape[0]), int(batch),
+                                            ptr(loss_per_step), _stream(x.device)))
+
     def reset_opt(self):
         check(self.lib.sn_alice_reset_opt(self.h, _stream(self.device)))
 

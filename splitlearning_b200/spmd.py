@@ -109,8 +109,11 @@ def run_sisa_schedule(rank, world, bob, alices, data, sizes, B, local_epochs, se
 
     def train_local(k, x, y):
         for _ in range(local_epochs):
-            for s in range(0, x.shape[0], B):
-                alices[k].local_step(x[s:s + B], y[s:s + B])
+            if hasattr(alices[k], "local_epoch"):
+                alices[k].local_epoch(x, y, B)
+            else:
+                for s in range(0, x.shape[0], B):
+                    alices[k].local_step(x[s:s + B], y[s:s + B])
 
     def ship(k, x, y, cache):
         own = owner_rank(k, world)
@@ -209,6 +212,9 @@ class _CudaSisaAlice:
 
     def local_step(self, x, y):
         self.eng.local_step(x, y, loss_out=self.loss)
+
+    def local_epoch(self, x, y, B):
+        self.eng.local_epoch(x, y, B)
 
     def forward(self, x):
         return self.eng.forward(x)

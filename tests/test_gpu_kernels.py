@@ -368,6 +368,7 @@ def test_tcgen05_large_batch_train_step(eng, opt):
     # softmax gradient compound it to a few percent on the cut gradient.  Perf mode only.
     assert rel_err(cut.cpu(), at.grad) <= 5e-2
     for p_ref, p, p0 in zip(b, gp, w_old):
-        assert rel_err(p.cpu(), p_ref) <= 2e-3
+        # Adam's step is ~lr*sign(g): TF32 gradient error flips it wherever |g| is small
+        assert rel_err(p.cpu(), p_ref) <= (2e-2 if opt == "adam" else 2e-3)
         if opt == "sgd":        # the applied step itself (lr * grad) at TF32 accuracy
             assert rel_err(p.cpu() - p0, p_ref - p0) <= 5e-2

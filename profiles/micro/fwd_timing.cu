@@ -3,11 +3,13 @@
 #define SN_TIMING 1
 #include "../../splitlearning_b200/csrc/mlp_kernels.cuh"
 #include <cstdio>
+#include <cstdlib>
 #include <vector>
 namespace sn { thread_local std::string g_last_error; std::atomic<uint64_t> g_launches{0}; }
 using namespace sn;
-int main() {
-  const int N = 5000, K = 5408, B = 16, kc = 1408, ksplit = 4, nx = 37;
+int main(int argc, char** argv) {
+  int N = 5000, K = 5408, B = 16, kc = 1408, ksplit = 4, nx = 37;
+  if (argc > 5) { N = atoi(argv[1]); K = atoi(argv[2]); kc = atoi(argv[3]); ksplit = atoi(argv[4]); nx = atoi(argv[5]); }
   float *W, *X, *P;
   cudaMalloc(&W, (size_t)N * K * 4); cudaMalloc(&X, (size_t)B * K * 4); cudaMalloc(&P, (size_t)2 * ksplit * 16 * N * 4);
   cudaMemset(W, 0, (size_t)N * K * 4); cudaMemset(X, 0, (size_t)B * K * 4);

@@ -494,12 +494,19 @@ __global__ void __launch_bounds__(256) eval_counts_kernel(const float* __restric
 // ------------------------------------------------------------------------------------------
 constexpr int kRing = 8;   // rows in flight per thread (W + optimizer state): ~56-84 KB per SM
 
-template <int OPT, bool NEED_DA>
+// FUSE_FWD (SISA server epochs): the NEXT batch's activations are already known, so the same
+// traversal also produces the next step's forward through this layer with the freshly updated
+// weights: per row, each lane dots its 4 new weights with Xn[16][4], a 16-value butterfly sums
+// across the warp's 128-wide k slice, and the per-slice partials PF[slice][b][n] are summed by
+// fwd_epilogue_kernel at the start of the next step.  W is then read once per step instead of
+// twice (28*P -> 24*P bytes with Adam).
+template <int OPT, bool NEED_DA, bool FUSE_FWD = false>
 __global__ void __launch_bounds__(256, 1)
 bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict__ bias, float* __restrict__ s1,
                   float* __restrict__ s2, float* __restrict__ bs1, float* __restrict__ bs2,
                   const float* __restrict__ dZ, int ldz, const float* __restrict__ A, int lda, int B,
-                  float* __restrict__ PA, int kw, int rows_per_cta, OptParams op) {
+                  float* __restrict__ PA, int kw, int rows_per_cta, OptParams op,
+                  const float* __restrict__ Xn = nullptr, int Bn = 0, float* __restrict__ PF = nullptr) {
   extern __shared__ float4 smem4[];
   float* dzs = reinterpret_cast<float*>(smem4);                  // [rows_per_cta][16]
   // per-thread ring of the next kRing rows' float4s: [array][slot][thread]; a thread only ever
@@ -557,6 +564,14 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
 #pragma unroll
     for (int b = 0; b < kBT; ++b) acc[b] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
+  float4 xn[FUSE_FWD ? kBT : 1];
+  if (FUSE_FWD) {
+#pragma unroll
+    for (int b = 0; b < kBT; ++b)
+      xn[b] = (kok && b < Bn) ? __ldg(reinterpret_cast<const float4*>(Xn + (size_t)b * lda + k0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const int kslice = blockIdx.x * kw + wk;
+  const bool slice_ok = kslice * 128 < K;
   __syncthreads();
 
   int slot = 0;
@@ -600,6 +615,18 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
       *reinterpret_cast<float4*>(W + o) = w;
       __stcs(reinterpret_cast<float4*>(s1 + o), m1);
       if (OPT == 2) __stcs(reinterpret_cast<float4*>(s2 + o), m2);
+    }
+    if (FUSE_FWD) {                                   // next step's forward with the updated row
+      float y[kBT];
+#pragma unroll
+      for (int b = 0; b < kBT; ++b) {
+        float t = w.x * xn[b].x;
+        t = __fmaf_rn(w.y, xn[b].y, t);
+        t = __fmaf_rn(w.z, xn[b].z, t);
+        y[b] = __fmaf_rn(w.w, xn[b].w, t);
+      }
+      butterfly_reduce<kBT>(y, lane);               // lanes 2b, 2b+1 hold batch row b
+      if (slice_ok && !(lane & 1)) PF[((size_t)kslice * kBT + (lane >> 1)) * N + n] = y[0];
     }
   }
   cp_async_wait<0>();

@@ -271,6 +271,8 @@ struct sn_bob {
   int heads = 1;
   int row_loss_rows = 0;
   Profiler prof;
+  float* PF = nullptr;         // fused next-forward partials of layer 0 [k slices][16][dims[1]] (lazy)
+  bool pf_valid = false;       // PF holds layer 0's pre-activation partials for the coming step
 };
 
 struct sn_alice {
@@ -516,6 +518,7 @@ int sn_bob_destroy(sn_bob* h) {
   cudaFree(h->P);
   cudaFree(h->PA);
   cudaFree(h->dWbuf);
+  cudaFree(h->PF);
   cudaFree(h->row_loss);
   cudaFree(h->ticket);
   h->prof.clear();
@@ -622,8 +625,14 @@ static int bob_forward_impl(sn_bob* h, const float* act, int B, int train, const
     const bool drop = train && !last && h->dropout_p > 0.f;
     const uint8_t* mask = (drop && masks) ? masks[l] : nullptr;
     const float kp = (drop && !masks) ? keep : 1.f;
-    if (launch_linear_fwd(X, ldx, B, h->W[l], h->b[l], K, N, relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N,
-                          last ? out : nullptr, h->P, h->sms, st, &h->prof))
+    if (l == 0 && h->pf_valid) {
+      // layer 0 of this step was already multiplied out by the previous step's fused traversal
+      h->pf_valid = false;
+      launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, h->sms)), dim3(256), 0, st, h->PF, ceil_div(K, 128), kBT, B, N,
+               h->b[l], relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N, last ? out : nullptr);
+      SN_LAUNCH_CHECK();
+    } else if (launch_linear_fwd(X, ldx, B, h->W[l], h->b[l], K, N, relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N,
+                                 last ? out : nullptr, h->P, h->sms, st, &h->prof))
       return 1;
     X = h->H[l + 1];
     ldx = N;
@@ -633,7 +642,8 @@ static int bob_forward_impl(sn_bob* h, const float* act, int B, int train, const
 
 }  // extern "C" (templates need C++ linkage)
 template <int OPT>
-static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float* cut_grad, cudaStream_t st) {
+static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float* cut_grad, cudaStream_t st,
+                             const float* next_act = nullptr, int next_B = 0) {
   auto& s = h->slots[slot];
   s.step += 1;
   const OptParams op = make_opt(h->hyper, s.step);
@@ -655,18 +665,29 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         cudaEvent_t pe = h->prof.begin(st, 1, l);
         launch_k(bwd_update_kernel<OPT, true>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
                                                               s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, h->PA,
-                                                              p.kw, p.rows_per_cta, op);
+                                                              p.kw, p.rows_per_cta, op, (const float*)nullptr, 0, (float*)nullptr);
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
         launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, p.nsplit, B, K, gateH, K, gscale,
                                                                            dst, K);
         SN_LAUNCH_CHECK();
+      } else if (l == 0 && next_act && next_B > 0 && next_B <= kBT && (size_t)N * K > kSmallLayerElems) {
+        // SISA: fuse the next step's layer-0 forward into this traversal
+        if (!h->PF) SN_CUDA(cudaMalloc(&h->PF, (size_t)ceil_div(K, 128) * kBT * N * 4));
+        if (set_smem(bwd_update_kernel<OPT, false, true>, smem)) return 1;
+        cudaEvent_t pe = h->prof.begin(st, 1, l);
+        launch_k(bwd_update_kernel<OPT, false, true>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, h->b[l],
+                 s.s1[2 * l], s.s2[2 * l], s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, h->PA, p.kw, p.rows_per_cta, op,
+                 next_act, next_B, h->PF);
+        Profiler::end(pe, st);
+        SN_LAUNCH_CHECK();
+        h->pf_valid = true;
       } else {
         if (set_smem(bwd_update_kernel<OPT, false>, smem)) return 1;
         cudaEvent_t pe = h->prof.begin(st, 1, l);
         launch_k(bwd_update_kernel<OPT, false>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
                                                                s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B,
-                                                               h->PA, p.kw, p.rows_per_cta, op);
+                                                               h->PA, p.kw, p.rows_per_cta, op, (const float*)nullptr, 0, (float*)nullptr);
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
       }
@@ -722,22 +743,21 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
 }
 
 extern "C" {
-static int bob_backward_dispatch(sn_bob* h, int slot, const float* act, int B, float* cut_grad, cudaStream_t st) {
+static int bob_backward_dispatch(sn_bob* h, int slot, const float* act, int B, float* cut_grad, cudaStream_t st,
+                                 const float* next_act = nullptr, int next_B = 0) {
   switch (h->hyper.type) {
-    case SN_OPT_SGD_MOMENTUM: return bob_backward_impl<1>(h, slot, act, B, cut_grad, st);
-    case SN_OPT_ADAM: return bob_backward_impl<2>(h, slot, act, B, cut_grad, st);
+    case SN_OPT_SGD_MOMENTUM: return bob_backward_impl<1>(h, slot, act, B, cut_grad, st, next_act, next_B);
+    case SN_OPT_ADAM: return bob_backward_impl<2>(h, slot, act, B, cut_grad, st, next_act, next_B);
     default: return fail_msg("libsplitnn: this sn_bob was created without an optimizer");
   }
 }
 
-int sn_bob_train_step(sn_bob* h, int slot, const float* act, const int64_t* labels, int B,
-                      const uint8_t* const* drop_masks, uint64_t seed, uint64_t offset, float* cut_grad,
-                      float* logits_out, float* loss_out, void* stream) {
-  SN_BOB_ENTER(h);
+static int bob_train_step_impl(sn_bob* h, int slot, const float* act, const int64_t* labels, int B,
+                               const uint8_t* const* drop_masks, uint64_t seed, uint64_t offset, float* cut_grad,
+                               float* logits_out, float* loss_out, cudaStream_t st, const float* next_act, int next_B) {
   SN_REQUIRE(act && labels && B > 0, "sn_bob_train_step: bad arguments");
   SN_REQUIRE(B <= h->max_batch, "sn_bob_train_step: batch larger than max_batch given to sn_bob_create");
   SN_REQUIRE(slot >= 0 && slot < h->n_slots, "sn_bob_train_step: optimizer slot out of range");
-  cudaStream_t st = (cudaStream_t)stream;
   h->stashed = true;
   h->stashed_B = B;
   if (bob_forward_impl(h, act, B, 1, drop_masks, seed, offset, logits_out, st)) return 1;
@@ -747,7 +767,16 @@ int sn_bob_train_step(sn_bob* h, int slot, const float* act, const int64_t* labe
   // [B][heads*Ch] row-major is [B*heads][Ch]: multi-head CE is the same kernel over more rows
   const int Ch = C / h->heads;
   if (launch_ce(z, Ch, labels, B * h->heads, Ch, h->dZ[h->L], Ch, h->row_loss, h->ticket, loss_out, nullptr, st)) return 1;
-  return bob_backward_dispatch(h, slot, act, B, cut_grad, st);
+  return bob_backward_dispatch(h, slot, act, B, cut_grad, st, next_act, next_B);
+}
+
+int sn_bob_train_step(sn_bob* h, int slot, const float* act, const int64_t* labels, int B,
+                      const uint8_t* const* drop_masks, uint64_t seed, uint64_t offset, float* cut_grad,
+                      float* logits_out, float* loss_out, void* stream) {
+  SN_BOB_ENTER(h);
+  h->pf_valid = false;
+  return bob_train_step_impl(h, slot, act, labels, B, drop_masks, seed, offset, cut_grad, logits_out, loss_out,
+                             (cudaStream_t)stream, nullptr, 0);
 }
 
 int sn_bob_forward(sn_bob* h, const float* act, int B, int train_mode, const uint8_t* const* drop_masks, uint64_t seed,
@@ -755,6 +784,7 @@ int sn_bob_forward(sn_bob* h, const float* act, int B, int train_mode, const uin
   SN_BOB_ENTER(h);
   SN_REQUIRE(act && out && B > 0, "sn_bob_forward: bad arguments");
   SN_REQUIRE(B <= h->max_batch, "sn_bob_forward: batch larger than max_batch given to sn_bob_create");
+  h->pf_valid = false;
   h->stashed = train_mode != 0;
   h->stashed_B = B;
   return bob_forward_impl(h, act, B, train_mode, drop_masks, seed, offset, out, (cudaStream_t)stream);
@@ -785,16 +815,29 @@ int sn_bob_server_epoch(sn_bob* h, int slot, const float* cache, const int64_t* 
   SN_REQUIRE(cache && labels && batch_offsets && n_batches >= 0, "sn_bob_server_epoch: bad arguments");
   const int d0 = h->dims[0], nm = h->L - 1;
   std::vector<const uint8_t*> m(std::max(nm, 1), nullptr);
+  h->pf_valid = false;
+  // SN_NO_FUSE_FWD=1 keeps the two-traversal form (A/B timing and parity tests of the fusion)
+  static const bool fuse = getenv("SN_NO_FUSE_FWD") == nullptr;
   for (int i = 0; i < n_batches; ++i) {
     const int64_t r0 = batch_offsets[i], r1 = batch_offsets[i + 1];
     SN_REQUIRE(r1 > r0 && r1 - r0 <= h->max_batch, "sn_bob_server_epoch: bad batch_offsets");
     if (drop_masks)
       for (int l = 0; l < nm; ++l) m[l] = drop_masks[l] + (size_t)r0 * h->dims[l + 1];
-    int rc = sn_bob_train_step(h, slot, cache + (size_t)r0 * d0, labels + r0, (int)(r1 - r0),
-                               drop_masks ? m.data() : nullptr, seed, offset + (uint64_t)i, nullptr, nullptr,
-                               loss_per_step ? loss_per_step + i : nullptr, stream);
-    if (rc) return rc;
+    // the next batch is already resident in the cache: let this step's layer-0 traversal also
+    // produce the next step's layer-0 forward (one read of W per step instead of two)
+    const float* next_act = nullptr;
+    int next_B = 0;
+    if (fuse && i + 1 < n_batches) {
+      next_act = cache + (size_t)batch_offsets[i + 1] * d0;
+      next_B = (int)(batch_offsets[i + 2] - batch_offsets[i + 1]);
+      if (next_B <= 0 || next_B > h->max_batch) { next_act = nullptr; next_B = 0; }
+    }
+    int rc = bob_train_step_impl(h, slot, cache + (size_t)r0 * d0, labels + r0 * h->heads, (int)(r1 - r0),
+                                 drop_masks ? m.data() : nullptr, seed, offset + (uint64_t)i, nullptr, nullptr,
+                                 loss_per_step ? loss_per_step + i : nullptr, (cudaStream_t)stream, next_act, next_B);
+    if (rc) { h->pf_valid = false; return rc; }
   }
+  h->pf_valid = false;
   return 0;
 }
 

@@ -372,3 +372,42 @@ def test_tcgen05_large_batch_train_step(eng, opt):
         assert rel_err(p.cpu(), p_ref) <= (2e-2 if opt == "adam" else 2e-3)
         if opt == "sgd":        # the applied step itself (lr * grad) at TF32 accuracy
             assert rel_err(p.cpu() - p0, p_ref - p0) <= 5e-2
+
+
+def test_server_epoch_fused_forward_matches_stepwise_and_oracle(eng):
+    """sn_bob_server_epoch fuses step t+1's first-layer forward into step t's weight traversal.
+    Same batches through (a) the fused epoch call, (b) one sn_bob_train_step per batch (never
+    fused), (c) the oracle: per-step losses and final weights must agree."""
+    rng = np.random.RandomState(11)
+    b = T(seeded_weights(B_SHAPES, 12))
+    sizes = [16, 16, 16, 16, 9]                          # ragged last batch
+    offs = np.concatenate([[0], np.cumsum(sizes)]).tolist()
+    n = offs[-1]
+    acts = (rng.rand(n, 5408) * 30 * (rng.rand(n, 5408) < 0.6)).astype(np.float32)
+    y = rng.randint(0, 10, size=n).astype(np.int64)
+    m1 = (rng.rand(n, 5000) < 0.5).astype(np.uint8)
+    m2 = (rng.rand(n, 1000) < 0.5).astype(np.uint8)
+    kw = dict(optimizer=eng.SN_OPT_ADAM, lr=1e-3, weight_decay=1e-5)
+    bob_f, gp_f = _bob(eng, b, **kw)
+    bob_s, gp_s = _bob(eng, b, **kw)
+    acts_g, y_g, m1_g, m2_g = cu(acts), cu(y), cu(m1), cu(m2)
+    loss_f = torch.zeros(len(sizes), device="cuda")
+    bob_f.server_epoch(acts_g, y_g, offs, masks=[m1_g, m2_g], loss_per_step=loss_f)
+    loss_s, loss_o = [], []
+    opt = R.AdamState()
+    for i, (s0, s1) in enumerate(zip(offs[:-1], offs[1:])):
+        l, _, _ = bob_s.train_step(acts_g[s0:s1], y_g[s0:s1], masks=[m1_g[s0:s1], m2_g[s0:s1]], want_cut_grad=False)
+        loss_s.append(l.item())
+        ref = R.sisa_server_step(b, torch.from_numpy(acts[s0:s1]), torch.from_numpy(y[s0:s1]),
+                                 [torch.from_numpy(m1[s0:s1]), torch.from_numpy(m2[s0:s1])])
+        R.adam_(b, ref["bob_grads"], opt, 1e-3, weight_decay=1e-5)
+        loss_o.append(ref["loss"].item())
+    torch.cuda.synchronize()
+    lf = loss_f.cpu().numpy()
+    np.testing.assert_allclose(lf, np.array(loss_s), rtol=2e-4)     # fused vs unfused: summation order only
+    np.testing.assert_allclose(lf[:1], np.array(loss_o[:1]), rtol=1e-4)
+    np.testing.assert_allclose(lf, np.array(loss_o), rtol=5e-3)     # free-running Adam, 5 steps
+    assert bob_f.get_opt_step(0) == len(sizes) == bob_s.get_opt_step(0)
+    for n_, pf, ps, po in zip(B_NAMES, gp_f, gp_s, b):
+        check_adam_weights(pf.cpu(), ps.cpu(), n_ + " fused vs stepwise")
+        assert rel_err(pf.cpu(), po) <= 2e-3, n_

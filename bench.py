@@ -311,6 +311,19 @@ def run_sisa_epoch(torch, dev, peak):
         caches.append((acts, y, list(range(0, n, B)) + [n]))
     t1.record()
     torch.cuda.synchronize()
+    # activation cache fill in isolation: one frozen-Alice launch writes a whole shard into HBM
+    xs_big = (torch.randint(0, 256, (sizes[1], 1, 28, 28), generator=g).float()).to(dev)
+    dst = torch.empty(sizes[1], D0, device=dev)
+    alice.forward(xs_big, out=dst)
+    torch.cuda.synchronize()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
+    alice.forward(xs_big, out=dst)
+    c1.record()
+    torch.cuda.synchronize()
+    fill_ms = c0.elapsed_time(c1)
+    fill_bytes = sizes[1] * (D0 * 4 + 784 * 4)
+    del xs_big, dst
     n_steps = sum(len(c[2]) - 1 for c in caches)
     n_samples = sum(sizes)
 
@@ -341,7 +354,10 @@ def run_sisa_epoch(torch, dev, peak):
     bob.profile(False)
     step_bytes = 24.0 * P_BOB + 4.0 * B * D0
     adam_fc1 = 24.0 * P_FC1 + 4.0 * B * (DIMS[1] + DIMS[0])
-    return {"kernel_us": kern,
+    return {"cache_fill": {"kernel": "conv_pool_fwd_kernel over one Alice's whole shard", "samples": sizes[1],
+                           "ms": round(fill_ms, 3), "bytes": fill_bytes, "achieved": round(fill_bytes / (fill_ms * 1e-3) / 1e9, 1),
+                           "unit": "GB/s", "frac": round(fill_bytes / (fill_ms * 1e-3) / 1e9 / peak, 4)},
+            "kernel_us": kern,
             "dominant": {"kernel": "bwd_update_kernel<Adam,no dA> fc1", "bytes_per_launch": adam_fc1,
                          "achieved": round(adam_fc1 / (kern.get("bwd_update_fc1_us", 1e9) * 1e-6) / 1e9, 1),
                          "frac": round(adam_fc1 / (kern.get("bwd_update_fc1_us", 1e9) * 1e-6) / 1e9 / peak, 4)},

@@ -40,10 +40,17 @@ constexpr int kTileBytes = BM * BK * 4;             // 16 KB per operand per sta
 constexpr int kThreads = 192;
 constexpr int kTmemCols = 128;                      // fp32 accumulator: 128 lanes x 128 columns
 
-struct __align__(1024) Smem {
+// X3 = 3xTF32: every operand tile also has a "lo" twin holding x - trunc_tf32(x), written by the
+// epilogue warps while they wait for the accumulator; D = hi.hi + lo.hi + hi.lo recovers fp32
+// accuracy (~1e-5 relative: the tensor core's own fp32 accumulation is the floor) at 3x the MMAs.
+template <bool X3>
+struct __align__(1024) SmemT {
   float a[kStages][BM * BK];
   float b[kStages][BN * BK];
+  float a_lo[X3 ? kStages : 1][X3 ? BM * BK : 4];
+  float b_lo[X3 ? kStages : 1][X3 ? BN * BK : 4];
   unsigned long long full_bar[kStages];
+  unsigned long long split_bar[kStages];
   unsigned long long empty_bar[kStages];
   unsigned long long tmem_full_bar;
   unsigned tmem_base;
@@ -56,6 +63,9 @@ __device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned coun
 }
 __device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
   asm volatile(
@@ -152,11 +162,14 @@ struct Epilogue {
   OptParams op;
 };
 
-template <bool AMN, bool BMN, int EPI, int OPT>
+__device__ __forceinline__ float tf32_lo(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+
+template <bool AMN, bool BMN, int EPI, int OPT, bool X3>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
                  int K, float* __restrict__ C, int ldc, Epilogue ep) {
   extern __shared__ unsigned char smem_raw[];
+  using Smem = SmemT<X3>;
   Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
@@ -167,6 +180,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&sm.full_bar[s], 1);
+      mbar_init(&sm.split_bar[s], 128);
       mbar_init(&sm.empty_bar[s], 1);
     }
     mbar_init(&sm.tmem_full_bar, 1);
@@ -209,16 +223,27 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       for (int kb = 0; kb < kblocks; ++kb) {
         const int s = kb % kStages;
         const unsigned ph = (kb / kStages) & 1;
-        mbar_wait(&sm.full_bar[s], ph);
+        mbar_wait(X3 ? &sm.split_bar[s] : &sm.full_bar[s], ph);     // X3: the lo tiles are written too
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const unsigned long long ad = AMN ? make_desc_mnmajor_sw128(sm.a[s]) : make_desc_kmajor_sw128(sm.a[s]);
         const unsigned long long bd = BMN ? make_desc_mnmajor_sw128(sm.b[s]) : make_desc_kmajor_sw128(sm.b[s]);
         // one instruction consumes 8 reduction steps: K-major +32 B (2 x 16 B), MN-major +8 rows of
         // 128 B (64 x 16 B)
         constexpr unsigned long long astep = AMN ? 64 : 2, bstep = BMN ? 64 : 2;
+        if (!X3) {
 #pragma unroll
-        for (int k = 0; k < BK / 8; ++k)
-          mma_tf32(tmem_d, ad + astep * k, bd + bstep * k, idesc, (kb | k) != 0);
+          for (int k = 0; k < BK / 8; ++k)
+            mma_tf32(tmem_d, ad + astep * k, bd + bstep * k, idesc, (kb | k) != 0);
+        } else {
+          const unsigned long long al = AMN ? make_desc_mnmajor_sw128(sm.a_lo[s]) : make_desc_kmajor_sw128(sm.a_lo[s]);
+          const unsigned long long bl = BMN ? make_desc_mnmajor_sw128(sm.b_lo[s]) : make_desc_kmajor_sw128(sm.b_lo[s]);
+#pragma unroll
+          for (int k = 0; k < BK / 8; ++k) {
+            mma_tf32(tmem_d, al + astep * k, bd + bstep * k, idesc, (kb | k) != 0);   // small terms first
+            mma_tf32(tmem_d, ad + astep * k, bl + bstep * k, idesc, 1);
+            mma_tf32(tmem_d, ad + astep * k, bd + bstep * k, idesc, 1);
+          }
+        }
         mma_commit(&sm.empty_bar[s]);          // slot free once these MMAs have read it
       }
       mma_commit(&sm.tmem_full_bar);           // accumulator complete
@@ -226,6 +251,28 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   } else {
     // epilogue warps 2..5: TMEM lane quarter = warp % 4
     const int q = warp & 3;
+    if (X3) {
+      // while the main loop runs these 128 threads write the lo twins of every stage: same
+      // (swizzled) offsets as the hi tile, so the layout needs no decoding
+      const int t = threadIdx.x - 64;
+      for (int kb = 0; kb < kblocks; ++kb) {
+        const int s = kb % kStages;
+        const unsigned ph = (kb / kStages) & 1;
+        mbar_wait(&sm.full_bar[s], ph);
+        const float4* ah = reinterpret_cast<const float4*>(sm.a[s]);
+        const float4* bh = reinterpret_cast<const float4*>(sm.b[s]);
+        float4* alo = reinterpret_cast<float4*>(sm.a_lo[s]);
+        float4* blo = reinterpret_cast<float4*>(sm.b_lo[s]);
+#pragma unroll 4
+        for (int i = t; i < BM * BK / 4; i += 128) {
+          const float4 v = ah[i], w = bh[i];
+          alo[i] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
+          blo[i] = make_float4(tf32_lo(w.x), tf32_lo(w.y), tf32_lo(w.z), tf32_lo(w.w));
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic-proxy writes -> tensor core reads
+        mbar_arrive(&sm.split_bar[s]);
+      }
+    }
     mbar_wait(&sm.tmem_full_bar, 0);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     // The operand ring is idle once the accumulator is complete: reuse it as a per-warp 32x33
@@ -327,7 +374,8 @@ inline bool usable(const float* A, int lda, const float* B, int ldb, int K) {
   return (K % 4) == 0 && (lda % 4) == 0 && (ldb % 4) == 0 && ((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0;
 }
 
-constexpr size_t kSmemBytes = sizeof(Smem) + 1024;
+template <bool X3>
+constexpr size_t smem_bytes() { return sizeof(SmemT<X3>) + 1024; }
 
 }  // namespace tc
 }  // namespace sn

@@ -19,7 +19,8 @@ namespace sn {
 thread_local std::string g_last_error;
 std::atomic<uint64_t> g_launches{0};
 
-// 0 = fp32 everywhere (default, parity mode); 1 = TF32 tensor cores (tcgen05) for large batches
+// large-batch matrix products: 0 = 3xTF32 on tcgen05 (default, fp32-accurate, parity mode);
+// 1 = TF32 on tcgen05 (perf mode); 2 = fp32 SIMT fallback everywhere
 std::atomic<int> g_matmul_precision{0};
 
 static int sm_count(int device) {
@@ -175,18 +176,26 @@ static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t 
 // ---------------------------------------------------------------- shared launch helpers
 // C[M,N] (+epilogue) = sum_r A(m,r) B(n,r).  Operand memory: K-major = [extent, R] row-major,
 // MN-major = [R, extent] row-major; lda/ldb are the row strides of those matrices.
-template <bool AMN, bool BMN, int EPI, int OPT>
-static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
-                          const tc::Epilogue& ep, cudaStream_t st) {
+template <bool AMN, bool BMN, int EPI, int OPT, bool X3>
+static int launch_tc_gemm_p(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
+                            const tc::Epilogue& ep, cudaStream_t st) {
   CUtensorMap ma, mb;
   if (AMN ? tc::make_map(&ma, A, R, M, lda, 32, true) : tc::make_map(&ma, A, M, R, lda, tc::BM)) return 1;
   if (BMN ? tc::make_map(&mb, Bm, R, N, ldb, 32, true) : tc::make_map(&mb, Bm, N, R, ldb, tc::BN)) return 1;
-  auto kern = tc::gemm_tf32_kernel<AMN, BMN, EPI, OPT>;
-  if (set_smem(kern, tc::kSmemBytes)) return 1;
+  auto kern = tc::gemm_tf32_kernel<AMN, BMN, EPI, OPT, X3>;
+  if (set_smem(kern, tc::smem_bytes<X3>())) return 1;
   dim3 grid(ceil_div(N, tc::BN), ceil_div(M, tc::BM));
-  launch_k(kern, grid, dim3(tc::kThreads), tc::kSmemBytes, st, ma, mb, M, N, R, C, ldc, ep);
+  launch_k(kern, grid, dim3(tc::kThreads), tc::smem_bytes<X3>(), st, ma, mb, M, N, R, C, ldc, ep);
   SN_LAUNCH_CHECK();
   return 0;
+}
+// precision 1 = TF32 (one pass), anything else that reaches here = 3xTF32 (fp32-accurate)
+template <bool AMN, bool BMN, int EPI, int OPT>
+static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
+                          const tc::Epilogue& ep, cudaStream_t st) {
+  if (g_matmul_precision.load() == 1)
+    return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
+  return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
 }
 
 static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, const float* bias, int K, int N,
@@ -215,7 +224,7 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
     launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, P, kFwdSlots * p.ksplit, Bpad, B, N, bias, relu, mask,
                                                                     keep_prob, scale, seed, offset, layer, H, ldh, out2);
     SN_LAUNCH_CHECK();
-  } else if (g_matmul_precision.load() == 1 && tc::usable(X, ldx, W, K, K)) {
+  } else if (g_matmul_precision.load() != 2 && tc::usable(X, ldx, W, K, K)) {
     // tensor-bound regime: tcgen05 TF32 GEMM with the bias / ReLU / dropout epilogue fused
     tc::Epilogue ep{};
     ep.bias = bias; ep.relu = relu; ep.mask = mask; ep.keep_prob = keep_prob; ep.scale = scale;
@@ -295,7 +304,7 @@ extern "C" {
 
 int sn_version(void) { return 1; }
 int sn_set_matmul_precision(int mode) {
-  SN_REQUIRE(mode == 0 || mode == 1, "sn_set_matmul_precision: mode must be 0 (fp32) or 1 (tf32 for large batches)");
+  SN_REQUIRE(mode >= 0 && mode <= 2, "sn_set_matmul_precision: mode must be 0 (3xTF32), 1 (TF32) or 2 (fp32 SIMT)");
   g_matmul_precision.store(mode);
   return 0;
 }
@@ -691,7 +700,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
       }
-    } else if (g_matmul_precision.load() == 1 && (K % 4) == 0 && (N % 4) == 0) {
+    } else if (g_matmul_precision.load() != 2 && (K % 4) == 0 && (N % 4) == 0) {
       // tensor-bound regime (perf mode): dA, then dW fused with the optimizer, both on tcgen05
       if (need_da) {
         tc::Epilogue ep{};
@@ -812,7 +821,8 @@ int sn_bob_server_epoch(sn_bob* h, int slot, const float* cache, const int64_t* 
                         int n_batches, const uint8_t* const* drop_masks, uint64_t seed, uint64_t offset,
                         float* loss_per_step, void* stream) {
   SN_BOB_ENTER(h);
-  SN_REQUIRE(cache && labels && batch_offsets && n_batches >= 0, "sn_bob_server_epoch: bad arguments");
+  if (n_batches == 0) return 0;       // an empty shard (an Alice whose data was all unlearned) is a no-op
+  SN_REQUIRE(cache && labels && batch_offsets && n_batches > 0, "sn_bob_server_epoch: bad arguments");
   const int d0 = h->dims[0], nm = h->L - 1;
   std::vector<const uint8_t*> m(std::max(nm, 1), nullptr);
   h->pf_valid = false;

@@ -13,7 +13,8 @@ D0 = 5408
 
 
 def set_matmul_precision(mode):
-    """0 = fp32 (default, parity); 1 = TF32 tcgen05 tensor cores for batches > 64 (perf mode)."""
+    """Large-batch (B > 64) products: 0 = 3xTF32 tcgen05 (default, fp32-accurate), 1 = TF32 tcgen05
+    (perf mode), 2 = fp32 SIMT fallback."""
     check(_lib.load().sn_set_matmul_precision(int(mode)))
 
 

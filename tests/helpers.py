@@ -37,7 +37,7 @@ def check_summary(g, name, tensor, tol, what=""):
     return e
 
 
-def check_adam_weights(got, ref, name=""):
+def check_adam_weights(got, ref, name="", frob=1e-3, frac_tol=1e-4):
     """Adam-updated weights.  One Adam step moves every weight by ~lr*g/(|g|+eps): where a gradient
     entry is within rounding of zero the step's sign depends on fp32 summation order, so a handful
     of entries legitimately differ by up to 2*lr between ANY two fp32 implementations (torch-CPU
@@ -48,6 +48,17 @@ def check_adam_weights(got, ref, name=""):
     a = np.asarray(got, np.float64).reshape(-1)
     b = np.asarray(ref, np.float64).reshape(-1)
     e = rel_err(a, b)
-    assert e <= 1e-3, f"{name}: rel err {e:.3e}"
+    assert e <= frob, f"{name}: rel err {e:.3e}"
     frac = float((np.abs(a - b) > 1e-5).mean())
-    assert frac <= 1e-4, f"{name}: {frac:.2e} of entries differ by more than 1e-5"
+    assert frac <= frac_tol, f"{name}: {frac:.2e} of entries differ by more than 1e-5"
+
+
+def check_grad_through_relu(got, ref, fwd_eps, name=""):
+    """Gradients that passed through ReLU gates computed by a forward with relative error
+    `fwd_eps`: a pre-activation within fwd_eps of zero can land on the other side of the kink, which
+    changes that gradient entry by O(1).  The flipped fraction is ~fwd_eps, so the norm-wise error is
+    ~sqrt(fwd_eps) (measured: 3xTF32 forward 3.9e-5 at K=5408 -> 5e-3 on the cut gradient, while
+    every single GEMM of the backward is exact to 1e-6; one flipped hidden unit changes a whole
+    row of the layer below, so no per-entry criterion applies).  Require the norm-wise bound."""
+    e = rel_err(got, ref)
+    assert e <= 4.0 * np.sqrt(fwd_eps), f"{name}: rel err {e:.3e}"

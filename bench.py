@@ -173,16 +173,18 @@ def run_ours_single(args):
     def hand_off(src, dst):      # give_weights / load_state_dict between consecutive Alices
         dst[0].load_state_dict(src[0].state_dict())
 
+    from splitlearning_b200 import engine as E
+    act_buf = torch.empty(B, D0, device=dev)
+    cut_buf = torch.empty(B, D0, device=dev)
+
     def step(i, x, y, loss_out):
         k = (i // TURN) % N_ALICES
         if i % TURN == 0 and i > 0:
             hand_off(alices[(k - 1) % N_ALICES], alices[k])
-        eng = alices[k][1]
-        act = eng.forward(x)
         seed_ctr[0] += 1
-        _, cut, _ = bob.train_step(act, y, slot=k, masks=None, seed=1, offset=seed_ctr[0], want_cut_grad=True,
-                                   loss_out=loss_out)
-        eng.backward_update(x, cut)
+        # the three calls of alice.train's batch body (forward, Bob's train step, backward+update)
+        # through the library's single-call form
+        E.vanilla_step(alices[k][1], bob, x, y, k, 1, seed_ctr[0], act_buf, cut_buf, loss_out)
 
     loss_dev = torch.zeros((), device=dev)
     K, W = args.steps, args.warmup
@@ -205,26 +207,25 @@ def run_ours_single(args):
     final_loss = float(loss_dev.item())
 
     # ---- end-to-end through the same calls with HOST buffers ("e2e")
+    # Inputs start in pinned host memory; splitlearning_b200.io copies step t+1's batch on a side stream
+    # while step t computes (every step still does its own H2D copy and its own D2H loss read).
+    from splitlearning_b200.io import iterate_host_batches
     hx, hy = synthetic_batches(torch, nb, pin=True)
-    dx = torch.empty(B, 1, 28, 28, device=dev)
-    dy = torch.empty(B, dtype=torch.int64, device=dev)
     hloss = torch.zeros(K + W, dtype=torch.float32).pin_memory()
     dl = torch.zeros((), device=dev)
 
-    def e2e_step(i):
-        dx.copy_(hx[i % nb], non_blocking=True)
-        dy.copy_(hy[i % nb], non_blocking=True)
-        step(i, dx, dy, dl)
-        hloss[i].copy_(dl, non_blocking=True)
+    def e2e_run(first, count):
+        host = ((hx[i % nb], hy[i % nb]) for i in range(first, first + count))
+        for j, (dx, dy) in enumerate(iterate_host_batches(host, dev, B)):
+            step(first + j, dx, dy, dl)
+            hloss[first + j].copy_(dl, non_blocking=True)
 
-    for i in range(W):
-        e2e_step(i)
+    e2e_run(0, W)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
-    for i in range(K):
-        e2e_step(W + i)
+    e2e_run(W, K)
     f1.record()
     torch.cuda.synchronize()
     e2e_wall = time.perf_counter() - t0

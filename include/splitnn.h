@@ -217,6 +217,13 @@ int sn_alice_local_step(sn_alice* h, const float* x, const int64_t* labels, int 
 int sn_alice_local_epoch(sn_alice* h, const float* x, const int64_t* labels, int64_t n, int batch,
                          float* loss_per_step, void* stream);
 
+/* One whole vanilla split step on one device in one call: sn_alice_forward -> sn_bob_train_step
+ * (Philox dropout) -> sn_alice_backward_update, i.e. the body of alice.train's batch loop,
+ * data_entities_vanilla.py:70-76.  act and cut_grad are caller scratch [B,5408]. */
+int sn_vanilla_step(sn_alice* alice, sn_bob* bob, int slot, const float* x, const int64_t* labels,
+                    int B, uint64_t seed, uint64_t offset, float* act, float* cut_grad,
+                    float* loss_out, void* stream);
+
 /* ------------------------------------------------------------------ NVLink plumbing */
 int sn_p2p_enable_all(int n_devices);
 int sn_p2p_copy(void* dst, int dst_device, const void* src, int src_device, size_t bytes,

@@ -54,6 +54,7 @@ SIGNATURES = {
     "sn_alice_backward_update": (_i, [_vp, _vp, _vp, _i, _vp]),
     "sn_alice_local_step": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "sn_alice_local_epoch": (_i, [_vp, _vp, _vp, _i64, _i, _vp, _vp]),
+    "sn_vanilla_step": (_i, [_vp, _vp, _i, _vp, _vp, _i, _u64, _u64, _vp, _vp, _vp, _vp]),
     "sn_p2p_enable_all": (_i, [_i]),
     "sn_p2p_copy": (_i, [_vp, _i, _vp, _i, _sz, _vp]),
 }

@@ -998,6 +998,17 @@ int sn_alice_local_epoch(sn_alice* h, const float* x, const int64_t* labels, int
   return 0;
 }
 
+int sn_vanilla_step(sn_alice* alice, sn_bob* bob, int slot, const float* x, const int64_t* labels, int B, uint64_t seed,
+                    uint64_t offset, float* act, float* cut_grad, float* loss_out, void* stream) {
+  SN_REQUIRE(alice && bob && x && labels && act && cut_grad && B > 0, "sn_vanilla_step: bad arguments");
+  SN_REQUIRE(alice->device == bob->device, "sn_vanilla_step: Alice and Bob must share a device (use the separate calls across GPUs)");
+  int rc = sn_alice_forward(alice, x, B, act, stream);
+  if (rc) return rc;
+  rc = sn_bob_train_step(bob, slot, act, labels, B, nullptr, seed, offset, cut_grad, nullptr, loss_out, stream);
+  if (rc) return rc;
+  return sn_alice_backward_update(alice, x, cut_grad, B, stream);
+}
+
 // ------------------------------------------------------------------ NVLink plumbing
 int sn_p2p_enable_all(int n_devices) {
   int ndev = 0;

@@ -207,6 +207,13 @@ class AliceEngine:
         check(self.lib.sn_alice_set_opt_step(self.h, int(step)))
 
 
+def vanilla_step(alice, bob, x, labels, slot, seed, offset, act, cut, loss):
+    """`sn_vanilla_step`: Alice forward, Bob train step, Alice backward+update in one library call
+    (all on one device; `act`/`cut` are preallocated [B,5408] buffers)."""
+    check(bob.lib.sn_vanilla_step(alice.h, bob.h, int(slot), ptr(x), ptr(labels), int(x.shape[0]), int(seed), int(offset),
+                                  ptr(act), ptr(cut), ptr(loss), _stream(x.device)))
+
+
 class _RawCuda:
     """Minimal __cuda_array_interface__ carrier so torch can view library-owned memory."""
 

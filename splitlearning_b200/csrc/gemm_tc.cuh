@@ -34,17 +34,19 @@
 namespace sn {
 namespace tc {
 
-constexpr int BM = 128, BN = 128, BK = 32;          // BK floats = 128 bytes = one swizzle row
-constexpr int kStages = 3;                          // 96 KB of operand tiles: two CTAs fit per SM
-constexpr int kTileBytes = BM * BK * 4;             // 16 KB per operand per stage
+constexpr int BM = 128, BK = 32;                    // BK floats = 128 bytes = one swizzle row
+// tile width BN is a template parameter: 128 (3 stages, two CTAs per SM: one's epilogue overlaps the
+// other's main loop) or 256 (4 stages, one CTA per SM, half the A traffic per flop)
+constexpr int stages_for(int bn, bool x3) { return (bn == 256 && !x3) ? 4 : 3; }
+constexpr int kTileBytes = BM * BK * 4;             // 16 KB per A tile per stage
 constexpr int kThreads = 192;
-constexpr int kTmemCols = 128;                      // fp32 accumulator: 128 lanes x 128 columns
 
 // X3 = 3xTF32: every operand tile also has a "lo" twin holding x - trunc_tf32(x), written by the
 // epilogue warps while they wait for the accumulator; D = hi.hi + lo.hi + hi.lo recovers fp32
 // accuracy (~1e-5 relative: the tensor core's own fp32 accumulation is the floor) at 3x the MMAs.
-template <bool X3>
+template <bool X3, int BN>
 struct __align__(1024) SmemT {
+  static constexpr int kStages = stages_for(BN, X3);
   float a[kStages][BM * BK];
   float b[kStages][BN * BK];
   float a_lo[X3 ? kStages : 1][X3 ? BM * BK : 4];
@@ -164,12 +166,14 @@ struct Epilogue {
 
 __device__ __forceinline__ float tf32_lo(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 
-template <bool AMN, bool BMN, int EPI, int OPT, bool X3>
+template <bool AMN, bool BMN, int EPI, int OPT, bool X3, int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
                  int K, float* __restrict__ C, int ldc, Epilogue ep) {
   extern __shared__ unsigned char smem_raw[];
-  using Smem = SmemT<X3>;
+  using Smem = SmemT<X3, BN>;
+  constexpr int kStages = Smem::kStages;
+  constexpr int kTmemCols = BN;                     // fp32 accumulator: 128 lanes x BN columns
   Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
@@ -206,7 +210,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const int s = kb % kStages;
         const unsigned ph = (kb / kStages) & 1;
         mbar_wait(&sm.empty_bar[s], ph ^ 1);
-        mbar_expect_tx(&sm.full_bar[s], 2 * kTileBytes);
+        mbar_expect_tx(&sm.full_bar[s], kTileBytes + BN * BK * 4);
         if (!AMN) tma_load_2d(sm.a[s], &map_a, &sm.full_bar[s], kb * BK, m0);
         else
 #pragma unroll
@@ -265,8 +269,12 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         float4* blo = reinterpret_cast<float4*>(sm.b_lo[s]);
 #pragma unroll 4
         for (int i = t; i < BM * BK / 4; i += 128) {
-          const float4 v = ah[i], w = bh[i];
+          const float4 v = ah[i];
           alo[i] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
+        }
+#pragma unroll 4
+        for (int i = t; i < BN * BK / 4; i += 128) {
+          const float4 w = bh[i];
           blo[i] = make_float4(tf32_lo(w.x), tf32_lo(w.y), tf32_lo(w.z), tf32_lo(w.w));
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic-proxy writes -> tensor core reads
@@ -374,8 +382,8 @@ inline bool usable(const float* A, int lda, const float* B, int ldb, int K) {
   return (K % 4) == 0 && (lda % 4) == 0 && (ldb % 4) == 0 && ((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0;
 }
 
-template <bool X3>
-constexpr size_t smem_bytes() { return sizeof(SmemT<X3>) + 1024; }
+template <bool X3, int BN>
+constexpr size_t smem_bytes() { return sizeof(SmemT<X3, BN>) + 1024; }
 
 }  // namespace tc
 }  // namespace sn

@@ -176,16 +176,16 @@ static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t 
 // ---------------------------------------------------------------- shared launch helpers
 // C[M,N] (+epilogue) = sum_r A(m,r) B(n,r).  Operand memory: K-major = [extent, R] row-major,
 // MN-major = [R, extent] row-major; lda/ldb are the row strides of those matrices.
-template <bool AMN, bool BMN, int EPI, int OPT, bool X3>
+template <bool AMN, bool BMN, int EPI, int OPT, bool X3, int BN>
 static int launch_tc_gemm_p(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
                             const tc::Epilogue& ep, cudaStream_t st) {
   CUtensorMap ma, mb;
   if (AMN ? tc::make_map(&ma, A, R, M, lda, 32, true) : tc::make_map(&ma, A, M, R, lda, tc::BM)) return 1;
-  if (BMN ? tc::make_map(&mb, Bm, R, N, ldb, 32, true) : tc::make_map(&mb, Bm, N, R, ldb, tc::BN)) return 1;
-  auto kern = tc::gemm_tf32_kernel<AMN, BMN, EPI, OPT, X3>;
-  if (set_smem(kern, tc::smem_bytes<X3>())) return 1;
-  dim3 grid(ceil_div(N, tc::BN), ceil_div(M, tc::BM));
-  launch_k(kern, grid, dim3(tc::kThreads), tc::smem_bytes<X3>(), st, ma, mb, M, N, R, C, ldc, ep);
+  if (BMN ? tc::make_map(&mb, Bm, R, N, ldb, 32, true) : tc::make_map(&mb, Bm, N, R, ldb, BN)) return 1;
+  auto kern = tc::gemm_tf32_kernel<AMN, BMN, EPI, OPT, X3, BN>;
+  if (set_smem(kern, tc::smem_bytes<X3, BN>())) return 1;
+  dim3 grid(ceil_div(N, BN), ceil_div(M, tc::BM));
+  launch_k(kern, grid, dim3(tc::kThreads), tc::smem_bytes<X3, BN>(), st, ma, mb, M, N, R, C, ldc, ep);
   SN_LAUNCH_CHECK();
   return 0;
 }
@@ -193,9 +193,14 @@ static int launch_tc_gemm_p(const float* A, int lda, int M, const float* Bm, int
 template <bool AMN, bool BMN, int EPI, int OPT>
 static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
                           const tc::Epilogue& ep, cudaStream_t st) {
-  if (g_matmul_precision.load() == 1)
-    return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
-  return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
+  if (g_matmul_precision.load() == 1) {
+    // wide tiles once there is enough work to fill the SMs with them (SN_TC_BN=128 forces narrow)
+    static const bool wide_ok = !(getenv("SN_TC_BN") && atoi(getenv("SN_TC_BN")) == 128);
+    if (wide_ok && (long long)ceil_div(N, 256) * ceil_div(M, tc::BM) >= 148 && R >= 256)
+      return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false, 256>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
+    return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
+  }
+  return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
 }
 
 static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, const float* bias, int K, int N,

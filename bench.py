@@ -209,16 +209,17 @@ def run_ours_single(args):
     # ---- end-to-end through the same calls with HOST buffers ("e2e")
     # Inputs start in pinned host memory; splitlearning_b200.io copies step t+1's batch on a side stream
     # while step t computes (every step still does its own H2D copy and its own D2H loss read).
+    # The loss read: ce_kernel stores each step's loss straight into pinned host memory (UVA-mapped,
+    # 4 B over PCIe per step); a cudaMemcpyAsync D2H on the compute stream instead costs 7 us/step
+    # (profiles/micro/e2e_variants.py: 193.6 -> 186.6 us/step).
     from splitlearning_b200.io import iterate_host_batches
     hx, hy = synthetic_batches(torch, nb, pin=True)
     hloss = torch.zeros(K + W, dtype=torch.float32).pin_memory()
-    dl = torch.zeros((), device=dev)
 
     def e2e_run(first, count):
         host = ((hx[i % nb], hy[i % nb]) for i in range(first, first + count))
         for j, (dx, dy) in enumerate(iterate_host_batches(host, dev, B)):
-            step(first + j, dx, dy, dl)
-            hloss[first + j].copy_(dl, non_blocking=True)
+            step(first + j, dx, dy, hloss[first + j])
 
     e2e_run(0, W)
     torch.cuda.synchronize()

@@ -319,7 +319,8 @@ def _tf32_trunc(a):
 
 
 @pytest.mark.parametrize("B,K,N,relu", [(128, 32, 128, False), (256, 512, 256, True), (200, 1000, 100, True),
-                                        (65, 100, 12, False), (600, 5408, 1000, True)])
+                                        (65, 100, 12, False), (600, 5408, 1000, True),
+                                        (2500, 300, 2100, True)])      # 20 x 9 tiles of 128x256: the wide-tile kernel
 def test_tcgen05_tf32_linear_forward(eng, B, K, N, relu):
     """Large-batch perf mode: tcgen05.mma kind::tf32 reads the top 19 bits of each fp32 operand and
     accumulates in fp32.  Checked tightly against an emulation of exactly that (truncated operands,

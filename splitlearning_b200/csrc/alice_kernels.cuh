@@ -40,14 +40,22 @@ __global__ void __launch_bounds__(256) conv_pool_fwd_kernel(const float* __restr
   __shared__ float ws[kConvCG * 9];
   __shared__ float bs[kConvCG];
   const int cg = blockIdx.y;
+  // x is an input (never written by a kernel of the chain): the first image is staged before the
+  // dependency wait.  The conv weights are NOT safe to touch early - the previous step's
+  // conv_pool_bwd_kernel, which updates them, can be the launch right before this one.
+  if (blockIdx.x < B)
+    for (int t = threadIdx.x; t < 196; t += 256)
+      reinterpret_cast<float4*>(img)[t] = reinterpret_cast<const float4*>(x + (size_t)blockIdx.x * 784)[t];
   pdl_wait();
   pdl_launch();
   if (threadIdx.x < kConvCG * 9) ws[threadIdx.x] = w[cg * kConvCG * 9 + threadIdx.x];
   if (threadIdx.x < kConvCG) bs[threadIdx.x] = bias[cg * kConvCG + threadIdx.x];
   for (int b = blockIdx.x; b < B; b += gridDim.x) {
-    __syncthreads();
-    for (int t = threadIdx.x; t < 196; t += 256)
-      reinterpret_cast<float4*>(img)[t] = reinterpret_cast<const float4*>(x + (size_t)b * 784)[t];
+    if (b != blockIdx.x) {
+      __syncthreads();
+      for (int t = threadIdx.x; t < 196; t += 256)
+        reinterpret_cast<float4*>(img)[t] = reinterpret_cast<const float4*>(x + (size_t)b * 784)[t];
+    }
     __syncthreads();
     for (int o = threadIdx.x; o < kConvCG * kPooled; o += 256) {
       const int c = o / kPooled, p = o - c * kPooled;
@@ -72,46 +80,71 @@ __global__ void __launch_bounds__(256) conv_pool_bwd_kernel(const float* __restr
                                                             float* __restrict__ partial, unsigned* __restrict__ ticket,
                                                             float* __restrict__ dw_out, float* __restrict__ db_out,
                                                             float* __restrict__ s1, float* __restrict__ s2,
-                                                            OptParams op) {
+                                                            OptParams op, int prefetch_early) {
   __shared__ float img[28 * 28];
   __shared__ unsigned is_last;
   const int cg = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int c = cg * kConvCG + warp;
-  pdl_wait();
-  pdl_launch();
+  SN_TP_DECL;
+  SN_TP(0);
+  // Before the dependency wait (prefetch_early: the host knows the launch right before this one
+  // is not another weight update of the same Alice): the conv weights, last written at least two
+  // launches back, and the first image (an input, never written by the chain).
+  if (!prefetch_early) { pdl_wait(); pdl_launch(); }
   float wr[9];
 #pragma unroll
   for (int t = 0; t < 9; ++t) wr[t] = w[c * 9 + t];
   const float bc = bias[c];
+  if (blockIdx.x < B)
+    for (int t = threadIdx.x; t < 196; t += 256)
+      reinterpret_cast<float4*>(img)[t] = reinterpret_cast<const float4*>(x + (size_t)blockIdx.x * 784)[t];
+  if (prefetch_early) { pdl_wait(); pdl_launch(); }
+  SN_TP(1);
   float g[10];
 #pragma unroll
   for (int t = 0; t < 10; ++t) g[t] = 0.f;
 
   for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    // this lane's (up to 6) cut-gradient values, all requested before anything waits: inside the
+    // position loop each load sat behind the ReLU test and cost a full L2 round trip per position
+    // (clock64 phase timing: 5.4k of the kernel's 8.5k compute cycles)
+    float dv[6];
+#pragma unroll
+    for (int q = 0; q < 6; ++q) {
+      const int p = lane + 32 * q;
+      dv[q] = p < kPooled ? __ldg(dact + (size_t)b * kD0 + (size_t)c * kPooled + p) : 0.f;
+    }
+    if (b != blockIdx.x) {
+      __syncthreads();
+      for (int t = threadIdx.x; t < 196; t += 256)
+        reinterpret_cast<float4*>(img)[t] = reinterpret_cast<const float4*>(x + (size_t)b * 784)[t];
+    }
     __syncthreads();
-    for (int t = threadIdx.x; t < 196; t += 256)
-      reinterpret_cast<float4*>(img)[t] = reinterpret_cast<const float4*>(x + (size_t)b * 784)[t];
-    __syncthreads();
-    for (int p = lane; p < kPooled; p += 32) {
-      const int i = p / 13, j = p - i * 13;
-      float v[4];
-      conv4(img, wr, bc, i, j, v);
-      int best = 0;                       // first maximum wins (torch CPU max_pool2d)
-      float m = v[0];
 #pragma unroll
-      for (int d = 1; d < 4; ++d)
-        if (v[d] > m) { m = v[d]; best = d; }
-      if (m > 0.f) {                      // ReLU gate
-        const float d = dact[(size_t)b * kD0 + (size_t)c * kPooled + p];
-        const int r0 = 2 * i + (best >> 1), c0 = 2 * j + (best & 1);
+    for (int q = 0; q < 6; ++q) {
+      const int p = lane + 32 * q;
+      if (p < kPooled) {
+        const int i = p / 13, j = p - i * 13;
+        float v[4];
+        conv4(img, wr, bc, i, j, v);
+        int best = 0;                       // first maximum wins (torch CPU max_pool2d)
+        float m = v[0];
 #pragma unroll
-        for (int u = 0; u < 3; ++u)
+        for (int d = 1; d < 4; ++d)
+          if (v[d] > m) { m = v[d]; best = d; }
+        if (m > 0.f) {                      // ReLU gate
+          const float d = dv[q];
+          const int r0 = 2 * i + (best >> 1), c0 = 2 * j + (best & 1);
 #pragma unroll
-          for (int q = 0; q < 3; ++q) g[u * 3 + q] = __fmaf_rn(d, img[(r0 + u) * 28 + c0 + q], g[u * 3 + q]);
-        g[9] += d;
+          for (int u = 0; u < 3; ++u)
+#pragma unroll
+            for (int x2 = 0; x2 < 3; ++x2) g[u * 3 + x2] = __fmaf_rn(d, img[(r0 + u) * 28 + c0 + x2], g[u * 3 + x2]);
+          g[9] += d;
+        }
       }
     }
   }
+  SN_TP(2);
 #pragma unroll
   for (int t = 0; t < 10; ++t) g[t] = warp_sum(g[t]);
   if (lane == 0) {
@@ -120,29 +153,49 @@ __global__ void __launch_bounds__(256) conv_pool_bwd_kernel(const float* __restr
     for (int t = 0; t < 9; ++t) dst[c * 9 + t] = g[t];
     dst[288 + c] = g[9];
   }
+  SN_TP(3);
   __threadfence();
   __syncthreads();
+  SN_TP(4);
   if (threadIdx.x == 0) {
     unsigned t = atomicAdd(ticket, 1u);
     is_last = (t == gridDim.x * gridDim.y - 1);
   }
   __syncthreads();
+  SN_TP(5);
   if (!is_last) return;
   __threadfence();
+  SN_TP(6);
   for (int idx = threadIdx.x; idx < kConvParams; idx += 256) {
+    // parameter and optimizer state requested first, then the partials eight at a time (all in
+    // flight together), added in CTA order
+    float* p = idx < 288 ? (w + idx) : (bias + idx - 288);
+    float pv = 0.f, a = 0.f, bq = 0.f;
+    if (OPT != 0) {
+      pv = *p;
+      a = s1[idx];
+      if (OPT == 2) bq = s2[idx];
+    }
     float s = 0.f;
-    for (unsigned r = 0; r < gridDim.x; ++r) s += __ldcg(partial + (size_t)r * kConvParams + idx);
+    for (unsigned r0 = 0; r0 < gridDim.x; r0 += 8) {
+      float t[8];
+#pragma unroll
+      for (unsigned q = 0; q < 8; ++q) t[q] = r0 + q < gridDim.x ? __ldcg(partial + (size_t)(r0 + q) * kConvParams + idx) : 0.f;
+#pragma unroll
+      for (unsigned q = 0; q < 8; ++q)
+        if (r0 + q < gridDim.x) s += t[q];
+    }
     if (OPT == 0) {
       if (idx < 288) dw_out[idx] = s; else db_out[idx - 288] = s;
     } else {
-      float* p = idx < 288 ? (w + idx) : (bias + idx - 288);
-      float pv = *p, a = s1[idx], bq = (OPT == 2) ? s2[idx] : 0.f;
       opt_update<OPT>(op, pv, s, a, bq);
       *p = pv;
       s1[idx] = a;
       if (OPT == 2) s2[idx] = bq;
     }
   }
+  SN_TP(7);
+  SN_TP_FLUSH();
   if (threadIdx.x == 0) *ticket = 0u;     // re-arm for the next launch
 }
 

@@ -88,7 +88,31 @@ __device__ __forceinline__ void opt_update(const OptParams& op, float& p, float 
 // and calls pdl_launch() right AFTER its own wait (so a dependent can never overtake the
 // predecessor's predecessor: whatever a kernel does before its wait may only touch data produced
 // two or more kernels back).  Without the launch attribute both are no-ops.
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#ifdef SN_TRACE
+// Debug build only (profiles/micro/step_trace.py): CTA 0 of every kernel stamps %globaltimer right
+// after its dependency wait, i.e. at the moment its predecessor has fully completed; consecutive
+// differences are each kernel's cost inside the PDL chain, which a profiler cannot see.
+__device__ unsigned long long g_trace[8192];
+__device__ unsigned g_trace_n;
+__device__ long long g_trace_phase[16];        // clock64 phase stamps of one CTA of the kernel under study
+#define SN_TP(i) do { if (threadIdx.x == 0) tp_[i] = clock64(); } while (0)
+#define SN_TP_DECL long long tp_[16] = {0}
+#define SN_TP_FLUSH() do { if (threadIdx.x == 0) for (int q_ = 0; q_ < 16; ++q_) g_trace_phase[q_] = tp_[q_]; } while (0)
+#else
+#define SN_TP(i) do {} while (0)
+#define SN_TP_DECL do {} while (0)
+#define SN_TP_FLUSH() do {} while (0)
+#endif
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+#ifdef SN_TRACE
+  if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_trace[atomicAdd(&g_trace_n, 1u) & 8191u] = t;
+  }
+#endif
+}
 __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -27,6 +27,25 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 
+// L2 eviction-priority policies (createpolicy) and the hinted forms of the copies/stores that use
+// them.  The first layer's weights (108 MB) are touched twice per step and fit in the 126 MB L2
+// if nothing pushes them out: their lines are tagged evict_last, the optimizer state (touched once
+// per step, never re-read before its lines would have been evicted anyway) evict_first.
+__device__ __forceinline__ uint64_t l2_policy(int kind) {   // 0 normal, 1 evict_last, 2 evict_first
+  uint64_t p;
+  if (kind == 1) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  else if (kind == 2) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void cp_async16_hint(void* smem, const void* gmem, uint64_t policy) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void st_hint(float4* p, const float4& v, uint64_t policy) {
+  asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;\n" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(policy) : "memory");
+}
+
 template <int V>
 __device__ __forceinline__ void butterfly_reduce(float* v, int lane) {
   int cnt = V;
@@ -83,8 +102,10 @@ __device__ __forceinline__ void cp_async16_zfill(void* smem, const void* gmem, b
 // (row>>1)&3, which makes every LDS.128 of a quarter-warp hit 8 distinct bank groups.
 __global__ void __launch_bounds__(256, 1)
 fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N,
-                  int K, int kc, float* __restrict__ P, int Bpad, int ksplit, int prefetch_early) {
+                  int K, int kc, float* __restrict__ P, int Bpad, int ksplit, int prefetch_early, int l2_keep_w) {
   extern __shared__ float4 smem4[];
+  // rows below l2_keep_w are tagged evict_last (see l2_policy), the others stream
+  const uint64_t pol_keep = l2_policy(1);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ks = blockIdx.y, k0 = ks * kc;
   const int klen = min(kc, K - k0);
@@ -115,7 +136,13 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
         const float* src = W + (size_t)(gi * 8) * ldw + k0 + k;
         if (gi * 8 + 8 <= N) {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) cp_async16(wring + (slot * 8 + i) * 32 + lane, src + (size_t)i * ldw);
+          if (gi * 8 < l2_keep_w) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) cp_async16_hint(wring + (slot * 8 + i) * 32 + lane, src + (size_t)i * ldw, pol_keep);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) cp_async16(wring + (slot * 8 + i) * 32 + lane, src + (size_t)i * ldw);
+          }
         } else {
 #pragma unroll
           for (int i = 0; i < 8; ++i)
@@ -271,6 +298,7 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
   const size_t total = (size_t)B * N;
   for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
     const int b = (int)(idx / N), n = (int)(idx - (size_t)b * N);
+    const float bn = bias[n];                    // requested before the partials, not after them
     float s = 0.f;
     const float* pp = P + (size_t)b * N + n;
     const size_t pstride = (size_t)Bpad * N;
@@ -281,7 +309,7 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
       s += p0; s += p1; s += p2; s += p3;
     }
     for (; ks < ksplit; ++ks) s += pp[(size_t)ks * pstride];
-    s += bias[n];
+    s += bn;
     if (relu) s = fmaxf(s, 0.f);
     if (mask) {
       s = mask[idx] ? s * scale : 0.f;
@@ -293,97 +321,243 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Cross-entropy of one row by one warp: loss = lse - z[y]; dlogits = (softmax - onehot)/B.
+// Returns the row loss (same value in every lane).  CG reads the logits with ld.global.cg (L2):
+// needed when other CTAs of the same launch wrote them.  NC > 0: the row has at most 32*NC classes
+// and `zc` already holds this lane's logits (class lane+32i, -inf beyond C), so the three passes run
+// from registers - one L2 round trip per row instead of twelve dependent ones (clock64 phase
+// timing: 15.8k cycles for two rows per warp before, at ~500 cycles per dependent load).
+// ------------------------------------------------------------------------------------------
+template <bool CG, int NC>
+__device__ __forceinline__ float ce_row(const float* __restrict__ zr, const float* zc, int64_t lab, int C, float invB,
+                                        float* __restrict__ dzr, int lane) {
+  auto ld = [&](int c, int i) { return NC > 0 ? zc[i] : (CG ? __ldcg(zr + c) : zr[c]); };
+  const int iters = NC > 0 ? NC : (C + 31) >> 5;
+  float m = -INFINITY;
+  int arg = 0x7fffffff;
+#pragma unroll
+  for (int i = 0; i < iters; ++i) {
+    const int c = lane + 32 * i;
+    if (c < C) {
+      const float v = ld(c, i);
+      if (v > m) { m = v; arg = c; }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, m, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
+  }
+  // sum of exp(z-m) WITHOUT the max term (which is exactly 1): log1p keeps full precision when
+  // one class dominates, where log(1+eps) computed from a rounded sum would lose it
+  float s1 = 0.f;
+  float zl = 0.f;                            // z[label], picked up on the way
+  float ex[NC > 0 ? NC : 1];                 // exp(z-m) of this lane's classes (register form only)
+#pragma unroll
+  for (int i = 0; i < iters; ++i) {
+    const int c = lane + 32 * i;
+    if (c < C) {
+      const float v = ld(c, i);
+      const float e = c != arg ? expf(v - m) : 1.f;
+      if (NC > 0) ex[i] = e;
+      if (c != arg) s1 += e;
+      if (c == lab) zl = v;
+    }
+  }
+  s1 = warp_sum(s1);
+  zl = warp_sum(zl);                         // exactly one lane holds it, the others add zeros
+  const float s = 1.f + s1;
+  const bool ok = lab >= 0 && lab < C;
+  // -log_softmax(z)[y] = log(sum exp(z-m)) - (z[y]-m): no cancellation against the row max
+  const float loss = ok ? (log1pf(s1) - (zl - m)) : NAN;   // torch raises on a bad target
+  if (dzr) {
+    const float invs = 1.f / s;
+#pragma unroll
+    for (int i = 0; i < iters; ++i) {
+      const int c = lane + 32 * i;
+      if (c < C) {
+        float p = (NC > 0 ? ex[i] : expf(ld(c, i) - m)) * invs;
+        if (c == lab) p -= 1.f;
+        dzr[c] = p * invB;
+      }
+    }
+  }
+  return loss;
+}
+
+constexpr int kCeRegClasses = 4;     // rows of up to 128 classes are held in registers (4 per lane)
+
+// one warp, one row; picks the register-resident form when the row is short enough
+template <bool CG>
+__device__ __forceinline__ float ce_row_auto(const float* __restrict__ zr, int64_t lab, int C, float invB,
+                                             float* __restrict__ dzr, int lane) {
+  if (C <= 32 * kCeRegClasses) {
+    float zc[kCeRegClasses];
+#pragma unroll
+    for (int i = 0; i < kCeRegClasses; ++i) {
+      const int c = lane + 32 * i;
+      zc[i] = c < C ? (CG ? __ldcg(zr + c) : zr[c]) : -INFINITY;
+    }
+    return ce_row<CG, kCeRegClasses>(zr, zc, lab, C, invB, dzr, lane);
+  }
+  return ce_row<CG, 0>(zr, nullptr, lab, C, invB, dzr, lane);
+}
+
+// Cross-entropy fused behind the last layer (fwd_small_kernel): labels == nullptr turns it off.
+// The logits H[B][N] are read as rows = B*heads rows of C = N/heads classes (multi-head CE).
+struct CeTail {
+  const int64_t* labels;
+  float* dz;            // [rows][C]
+  float* row_loss;      // [rows] scratch
+  unsigned* ticket;     // zero before the launch; re-armed by the kernel
+  float* loss;          // mean over rows
+  int rows, C;
+};
+
 // Tiny layers (fc3 100x1000, the U-shape tail 10x100): the weight matrix is L2-resident and the
-// launch is pure latency, so the split-K machinery above costs more than it saves.  One warp per
-// output row, lanes stride k, 16 batch accumulators per lane, one 16-value butterfly, and the
-// bias / ReLU / dropout epilogue fused: one launch instead of two, no partial sums.
+// launch is pure latency, so the split-K machinery above costs more than it saves.  One launch,
+// bias / ReLU / dropout fused, no global partial sums.
+//   grid (ceil(N/2), batch tiles), 256 threads.  The CTA owns kHeadRows = 2 output rows.  Thread
+//   (warp w, lane l) owns the 4 k-columns of float4 w*32+l (+256 per pass): it holds X[16][4] and
+//   W[2 rows][4] in registers - loaded straight from global, one round trip, no staging - and
+//   does 128 FMAs per pass; a 32-value butterfly sums across the lanes, the 8 warps' sums meet in
+//   shared memory and 32 threads finish (fixed order: deterministic).
+//   (The first version gave each WARP a row and read the whole X tile from shared memory in
+//   every warp: 8 x 64 KB of LDS per CTA, 3.4 us of shared-memory bandwidth for 0.2 us of math.)
+// In a training step this is the last layer and the loss follows: the last CTA to finish (ticket)
+// computes the cross-entropy of all rows and the logit gradient in the same launch.
+constexpr int kHeadRows = 2;
+
 __global__ void __launch_bounds__(256)
 fwd_small_kernel(const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N, int K,
                  const float* __restrict__ bias, int relu, const uint8_t* __restrict__ mask, float keep_prob,
                  float scale, uint64_t seed, uint64_t offset, int layer, float* __restrict__ H, int ldh,
-                 float* __restrict__ out2, int prefetch_early) {
-  extern __shared__ float4 smem4[];                 // X tile [16][K4] float4 (K padded to 4)
+                 float* __restrict__ out2, int prefetch_early, CeTail ce) {
+  __shared__ float part[8][kHeadRows * kBT];
+  __shared__ float rl[256];                          // row losses of the tail (rows beyond 256: global scratch)
+  __shared__ unsigned is_last;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int n = blockIdx.x * 8 + warp;
+  const int n0 = blockIdx.x * kHeadRows;
   const int b0 = blockIdx.y * kBT, nb = min(kBT, B - b0);
   const int K4 = (K + 3) >> 2;
-  const bool vec = (K & 3) == 0;
-  // when the host says the previous kernel cannot be writing W (prefetch_early), this warp's W
-  // row is fetched before the PDL wait; otherwise right after it
-  constexpr int WPF = 8;                            // float4 per lane held in registers (K <= 1024)
-  float4 wreg[WPF];
-  const bool row_ok = n < N;
-  const float* wr = W + (size_t)(row_ok ? n : 0) * ldw;
+  const bool wvec = (K & 3) == 0 && (ldw & 3) == 0 && (reinterpret_cast<uintptr_t>(W) & 15) == 0;
+  const bool xvec = (K & 3) == 0 && (ldx & 3) == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0;
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  SN_TP_DECL;
+  SN_TP(0);
+
+  auto load4 = [&](const float* row, int k4, bool vec) {
+    if (vec) return __ldg(reinterpret_cast<const float4*>(row) + k4);
+    const int k = k4 * 4;
+    float4 v;
+    v.x = k < K ? __ldg(row + k) : 0.f;
+    v.y = k + 1 < K ? __ldg(row + k + 1) : 0.f;
+    v.z = k + 2 < K ? __ldg(row + k + 2) : 0.f;
+    v.w = k + 3 < K ? __ldg(row + k + 3) : 0.f;
+    return v;
+  };
+  auto load_w = [&](int k4, float4* w) {
+#pragma unroll
+    for (int r = 0; r < kHeadRows; ++r)
+      w[r] = (k4 < K4 && n0 + r < N) ? load4(W + (size_t)(n0 + r) * ldw, k4, wvec) : zero4;
+  };
+
+  // when the host says the previous kernel cannot be writing W or the bias (prefetch_early), the
+  // first pass's W values are fetched before the PDL wait; otherwise right after it
+  float4 w[kHeadRows];
   if (!prefetch_early) { pdl_wait(); pdl_launch(); }
-  if (vec) {
-#pragma unroll
-    for (int q = 0; q < WPF; ++q) {
-      const int k4 = q * 32 + lane;
-      wreg[q] = (row_ok && k4 < K4) ? __ldg(reinterpret_cast<const float4*>(wr) + k4) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-  }
+  load_w(warp * 32 + lane, w);
+  float bv = 0.f;
+  if (tid < kHeadRows * kBT && n0 + (tid >> 4) < N) bv = __ldg(bias + n0 + (tid >> 4));
   if (prefetch_early) { pdl_wait(); pdl_launch(); }
-  // X -> smem, all loads of a thread in flight together (one round trip)
-  for (int idx = tid; idx < kBT * K4; idx += 256) {
-    const int b = idx / K4, k4 = idx - b * K4;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (b < nb) {
-      const float* xr = X + (size_t)(b0 + b) * ldx;
-      if (vec) v = __ldg(reinterpret_cast<const float4*>(xr) + k4);
-      else {
-        const int k = k4 * 4;
-        v.x = k < K ? __ldg(xr + k) : 0.f;
-        v.y = k + 1 < K ? __ldg(xr + k + 1) : 0.f;
-        v.z = k + 2 < K ? __ldg(xr + k + 2) : 0.f;
-        v.w = k + 3 < K ? __ldg(xr + k + 3) : 0.f;
-      }
-    }
-    smem4[idx] = v;
-  }
-  __syncthreads();
-  if (!row_ok) return;
-  float acc[kBT];
+  SN_TP(1);
+
+  float acc[kHeadRows * kBT];
 #pragma unroll
-  for (int b = 0; b < kBT; ++b) acc[b] = 0.f;
-  for (int q = 0; q * 32 < K4; ++q) {
-    const int k4 = q * 32 + lane;
-    float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (k4 < K4) {
-      if (vec) w = q < WPF ? wreg[q < WPF ? q : 0] : __ldg(reinterpret_cast<const float4*>(wr) + k4);
-      else {
-        const int k = k4 * 4;
-        w.x = k < K ? __ldg(wr + k) : 0.f;
-        w.y = k + 1 < K ? __ldg(wr + k + 1) : 0.f;
-        w.z = k + 2 < K ? __ldg(wr + k + 2) : 0.f;
-        w.w = k + 3 < K ? __ldg(wr + k + 3) : 0.f;
-      }
+  for (int i = 0; i < kHeadRows * kBT; ++i) acc[i] = 0.f;
+  for (int kb = 0; kb < K4; kb += 256) {
+    const int k4 = kb + warp * 32 + lane;
+    if (kb > 0) load_w(k4, w);
+    float4 x[kBT];
+#pragma unroll
+    for (int b = 0; b < kBT; ++b) x[b] = (k4 < K4 && b < nb) ? load4(X + (size_t)(b0 + b) * ldx, k4, xvec) : zero4;
+#pragma unroll
+    for (int r = 0; r < kHeadRows; ++r)
 #pragma unroll
       for (int b = 0; b < kBT; ++b) {
-        const float4 x = smem4[b * K4 + k4];
-        acc[b] = __fmaf_rn(w.x, x.x, acc[b]);
-        acc[b] = __fmaf_rn(w.y, x.y, acc[b]);
-        acc[b] = __fmaf_rn(w.z, x.z, acc[b]);
-        acc[b] = __fmaf_rn(w.w, x.w, acc[b]);
+        float a = acc[r * kBT + b];
+        a = __fmaf_rn(w[r].x, x[b].x, a);
+        a = __fmaf_rn(w[r].y, x[b].y, a);
+        a = __fmaf_rn(w[r].z, x[b].z, a);
+        acc[r * kBT + b] = __fmaf_rn(w[r].w, x[b].w, a);
       }
+  }
+  SN_TP(2);
+  // after the butterfly lane l holds the flat indices (row*16 + b) l*V/32 .. l*V/32 + V/32 - 1
+  butterfly_reduce<kHeadRows * kBT>(acc, lane);
+  constexpr int kPerLane = kHeadRows * kBT / 32;
+#pragma unroll
+  for (int j = 0; j < kPerLane; ++j) part[warp][kPerLane * lane + j] = acc[j];
+  __syncthreads();
+  if (tid < kHeadRows * kBT) {
+    const int r = tid >> 4, b = tid & 15, n = n0 + r;
+    if (n < N && b < nb) {
+      float s = part[0][tid];
+#pragma unroll
+      for (int q = 1; q < 8; ++q) s += part[q][tid];
+      s += bv;
+      if (relu) s = fmaxf(s, 0.f);
+      const size_t idx = (size_t)(b0 + b) * N + n;
+      if (mask) {
+        s = mask[idx] ? s * scale : 0.f;
+      } else if (keep_prob < 1.f) {
+        s = philox_keep(seed, offset, layer, idx, keep_prob) ? s * scale : 0.f;
+      }
+      H[(size_t)(b0 + b) * ldh + n] = s;
+      if (out2) out2[idx] = s;
     }
   }
-  butterfly_reduce<kBT>(acc, lane);             // lanes 2b and 2b+1 both end with the sum for batch row b
-  const int b = lane >> 1;
-  if ((lane & 1) || b >= nb) return;
-  float s = acc[0] + bias[n];
-  if (relu) s = fmaxf(s, 0.f);
-  const size_t idx = (size_t)(b0 + b) * N + n;
-  if (mask) {
-    s = mask[idx] ? s * scale : 0.f;
-  } else if (keep_prob < 1.f) {
-    s = philox_keep(seed, offset, layer, idx, keep_prob) ? s * scale : 0.f;
+  if (!ce.labels) return;
+  // ---- loss tail: the last CTA of the grid sees every logit
+  // labels of this warp's first two rows, fetched while the ticket round trip is in flight
+  const int r_a = warp, r_b = warp + 8;
+  const int64_t lab_a = r_a < ce.rows ? ce.labels[r_a] : 0, lab_b = r_b < ce.rows ? ce.labels[r_b] : 0;
+  SN_TP(3);
+  __threadfence();
+  __syncthreads();
+  SN_TP(4);
+  if (tid == 0) is_last = (atomicAdd(ce.ticket, 1u) == gridDim.x * gridDim.y - 1);
+  __syncthreads();
+  SN_TP(5);
+  if (!is_last) return;
+  __threadfence();
+  const float invB = 1.f / (float)ce.rows;
+  for (int r = warp; r < ce.rows; r += 8) {
+    const int64_t lab = r == r_a ? lab_a : r == r_b ? lab_b : ce.labels[r];
+    const float l = ce_row_auto<true>(H + (size_t)r * ce.C, lab, ce.C, invB, ce.dz ? ce.dz + (size_t)r * ce.C : nullptr, lane);
+    if (lane == 0) {
+      if (r < 256) rl[r] = l; else ce.row_loss[r] = l;
+    }
   }
-  H[(size_t)(b0 + b) * ldh + n] = s;
-  if (out2) out2[idx] = s;
+  __syncthreads();
+  SN_TP(6);
+  SN_TP_FLUSH();
+  if (warp == 0) {
+    // fixed-order sum: lanes take rows lane, lane+32, ...; then a shuffle tree (same as ce_kernel)
+    float s = 0.f;
+    for (int r = lane; r < ce.rows; r += 32) s += r < 256 ? rl[r] : ce.row_loss[r];
+    s = warp_sum(s);
+    if (lane == 0) {
+      if (ce.loss) *ce.loss = s / (float)ce.rows;
+      *ce.ticket = 0u;
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------
-// Cross-entropy: one warp per row; loss = mean_b(lse - z[y]); dlogits = (softmax - onehot)/B.
+// Cross-entropy as its own launch: one warp per row; loss = mean_b(lse - z[y]).
 // Row losses go to row_loss[B]; the last CTA (ticket) sums them in row order.
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ z, int ldz, const int64_t* __restrict__ y,
@@ -396,38 +570,8 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ z, in
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * 8 + warp;
   if (b < B) {
-    const float* zr = z + (size_t)b * ldz;
-    float m = -INFINITY;
-    int arg = 0x7fffffff;
-    for (int c = lane; c < C; c += 32) {
-      const float v = zr[c];
-      if (v > m) { m = v; arg = c; }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float om = __shfl_xor_sync(0xffffffffu, m, o);
-      const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
-      if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
-    }
-    // sum of exp(z-m) WITHOUT the max term (which is exactly 1): log1p keeps full precision when
-    // one class dominates, where log(1+eps) computed from a rounded sum would lose it
-    float s1 = 0.f;
-    for (int c = lane; c < C; c += 32)
-      if (c != arg) s1 += expf(zr[c] - m);
-    s1 = warp_sum(s1);
-    const float s = 1.f + s1;
-    const int64_t lab = y[b];
-    const bool ok = lab >= 0 && lab < C;
-    // -log_softmax(z)[y] = log(sum exp(z-m)) - (z[y]-m): no cancellation against the row max
-    if (lane == 0) row_loss[b] = ok ? (log1pf(s1) - (zr[lab] - m)) : NAN;   // torch raises on a bad target
-    if (dz) {
-      const float invB = 1.f / (float)B, invs = 1.f / s;
-      for (int c = lane; c < C; c += 32) {
-        float p = expf(zr[c] - m) * invs;
-        if (c == lab) p -= 1.f;
-        dz[(size_t)b * lddz + c] = p * invB;
-      }
-    }
+    const float l = ce_row_auto<false>(z + (size_t)b * ldz, y[b], C, 1.f / (float)B, dz ? dz + (size_t)b * lddz : nullptr, lane);
+    if (lane == 0) row_loss[b] = l;
   }
   __threadfence();
   __syncthreads();
@@ -506,8 +650,10 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
                   float* __restrict__ s2, float* __restrict__ bs1, float* __restrict__ bs2,
                   const float* __restrict__ dZ, int ldz, const float* __restrict__ A, int lda, int B,
                   float* __restrict__ PA, int kw, int rows_per_cta, OptParams op,
-                  const float* __restrict__ Xn = nullptr, int Bn = 0, float* __restrict__ PF = nullptr) {
+                  const float* __restrict__ Xn, int Bn, float* __restrict__ PF, int l2_keep_w) {
   extern __shared__ float4 smem4[];
+  // rows below l2_keep_w: weights tagged evict_last, their optimizer state evict_first
+  const uint64_t pol_keep = l2_policy(1), pol_norm = l2_policy(0), pol_s = l2_policy(l2_keep_w ? 2 : 0);
   float* dzs = reinterpret_cast<float*>(smem4);                  // [rows_per_cta][16]
   // per-thread ring of the next kRing rows' float4s: [array][slot][thread]; a thread only ever
   // reads what it copied itself, so cp.async.wait_group is the only synchronisation needed
@@ -522,9 +668,9 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
   auto issue = [&](int slot, int row) {
     if (kok && row < nb1) {
       const size_t o = (size_t)row * ldw + k0;
-      cp_async16(ring + (0 * kRing + slot) * 256 + tid, W + o);
-      cp_async16(ring + (1 * kRing + slot) * 256 + tid, s1 + o);
-      if (OPT == 2) cp_async16(ring + (2 * kRing + slot) * 256 + tid, s2 + o);
+      cp_async16_hint(ring + (0 * kRing + slot) * 256 + tid, W + o, row < l2_keep_w ? pol_keep : pol_norm);
+      cp_async16_hint(ring + (1 * kRing + slot) * 256 + tid, s1 + o, pol_s);
+      if (OPT == 2) cp_async16_hint(ring + (2 * kRing + slot) * 256 + tid, s2 + o, pol_s);
     }
     cp_async_commit();
   };
@@ -612,9 +758,15 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
       opt_update<OPT>(op, w.z, g.z, m1.z, m2.z);
       opt_update<OPT>(op, w.w, g.w, m1.w, m2.w);
       const size_t o = (size_t)n * ldw + k0;
-      *reinterpret_cast<float4*>(W + o) = w;
-      __stcs(reinterpret_cast<float4*>(s1 + o), m1);
-      if (OPT == 2) __stcs(reinterpret_cast<float4*>(s2 + o), m2);
+      if (l2_keep_w) {
+        st_hint(reinterpret_cast<float4*>(W + o), w, n < l2_keep_w ? pol_keep : pol_norm);
+        st_hint(reinterpret_cast<float4*>(s1 + o), m1, pol_s);
+        if (OPT == 2) st_hint(reinterpret_cast<float4*>(s2 + o), m2, pol_s);
+      } else {
+        *reinterpret_cast<float4*>(W + o) = w;
+        __stcs(reinterpret_cast<float4*>(s1 + o), m1);
+        if (OPT == 2) __stcs(reinterpret_cast<float4*>(s2 + o), m2);
+      }
     }
     if (FUSE_FWD) {                                   // next step's forward with the updated row
       float y[kBT];
@@ -668,6 +820,111 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
   }
 }
 
+// Backward + optimizer for tiny layers (fc3 100x1000: 400 KB, L2-resident, pure latency).  The
+// streaming kernel above needs an n split to fill the GPU and then a second launch to add the
+// splits; here a CTA sees EVERY row, so its input-gradient sum is final and the gate is applied
+// in place: one launch.  To still spread the 3.2 MFMA over enough SMs the k slices are narrow:
+//   grid ceil(K/32), 256 threads.  Lane l owns the single column k = 32*blockIdx.x + l; warp w
+//   owns rows w, w+8, ... (N <= 128: at most 16 per warp, their W / optimizer-state values
+//   prefetched into registers BEFORE the dependency wait).  Per row: dW = sum_b dZ[b][n]*A[b][k]
+//   (b order, as everywhere), dA[b] += dZ[b][n]*W_old, optimizer update in place.  The 8 warps' dA
+//   sums meet in shared memory (fixed order), are gated with A itself (A is the gate activation of
+//   a hidden layer) and written to dst[b][k].
+constexpr int kSmallBwdRows = 16;   // rows per warp held in registers => N <= 128
+
+template <int OPT, bool NEED_DA>
+__global__ void __launch_bounds__(256)
+bwd_small_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict__ bias, float* __restrict__ s1,
+                 float* __restrict__ s2, float* __restrict__ bs1, float* __restrict__ bs2,
+                 const float* __restrict__ dZ, int ldz, const float* __restrict__ A, int lda, int B, OptParams op,
+                 int gate, float gscale, float* __restrict__ dst, int ldd) {
+  __shared__ float dzs[128 * kBT];                 // [row][16]
+  __shared__ float red[8][kBT][32];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int k = blockIdx.x * 32 + lane;
+  const bool kok = k < K;
+  float w[kSmallBwdRows], m1[kSmallBwdRows], m2[OPT == 2 ? kSmallBwdRows : 1];
+#pragma unroll
+  for (int i = 0; i < kSmallBwdRows; ++i) {
+    const int n = warp + 8 * i;
+    const bool ok = kok && n < N;
+    const size_t o = (size_t)(ok ? n : 0) * ldw + (ok ? k : 0);
+    w[i] = ok ? W[o] : 0.f;
+    m1[i] = ok ? s1[o] : 0.f;
+    if (OPT == 2) m2[i] = ok ? s2[o] : 0.f;
+  }
+  pdl_wait();        // W / optimizer state are never written by the kernel just before this one;
+  pdl_launch();      // dZ (and A) are
+  for (int idx = tid; idx < N * kBT; idx += 256) {
+    const int b = idx / N, j = idx - b * N;
+    dzs[j * kBT + b] = b < B ? __ldg(dZ + (size_t)b * ldz + j) : 0.f;
+  }
+  float a[kBT];
+#pragma unroll
+  for (int b = 0; b < kBT; ++b) a[b] = (kok && b < B) ? __ldg(A + (size_t)b * lda + k) : 0.f;
+  float acc[NEED_DA ? kBT : 1];
+  if (NEED_DA) {
+#pragma unroll
+    for (int b = 0; b < kBT; ++b) acc[b] = 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < kSmallBwdRows; ++i) {
+    const int n = warp + 8 * i;
+    if (n < N) {
+      const float4* dzr = reinterpret_cast<const float4*>(dzs + n * kBT);
+      float dz[kBT];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 t = dzr[q];
+        dz[q * 4 + 0] = t.x; dz[q * 4 + 1] = t.y; dz[q * 4 + 2] = t.z; dz[q * 4 + 3] = t.w;
+      }
+      float g = 0.f;
+#pragma unroll
+      for (int b = 0; b < kBT; ++b) {
+        g = __fmaf_rn(dz[b], a[b], g);
+        if (NEED_DA) acc[b] = __fmaf_rn(dz[b], w[i], acc[b]);
+      }
+      if (kok) {
+        float pw = w[i], q1 = m1[i], q2 = OPT == 2 ? m2[OPT == 2 ? i : 0] : 0.f;
+        opt_update<OPT>(op, pw, g, q1, q2);
+        const size_t o = (size_t)n * ldw + k;
+        W[o] = pw;
+        s1[o] = q1;
+        if (OPT == 2) s2[o] = q2;
+      }
+    }
+  }
+  if (blockIdx.x == 0) {                            // bias: db[n] = sum_b dZ[b][n]
+    for (int j = tid; j < N; j += 256) {
+      float db = 0.f;
+#pragma unroll
+      for (int b = 0; b < kBT; ++b) db += dzs[j * kBT + b];
+      float p = bias[j], q1 = bs1[j], q2 = (OPT == 2) ? bs2[j] : 0.f;
+      opt_update<OPT>(op, p, db, q1, q2);
+      bias[j] = p;
+      bs1[j] = q1;
+      if (OPT == 2) bs2[j] = q2;
+    }
+  }
+  if (NEED_DA) {
+#pragma unroll
+    for (int b = 0; b < kBT; ++b) red[warp][b][lane] = acc[b];
+    __syncthreads();
+    for (int o = tid; o < kBT * 32; o += 256) {
+      const int l = o & 31, b = o >> 5;
+      float t = 0.f;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) t += red[r][b][l];
+      const int kk = blockIdx.x * 32 + l;
+      if (kk < K && b < B) {
+        if (gate) t = __ldg(A + (size_t)b * lda + kk) > 0.f ? t * gscale : 0.f;
+        dst[(size_t)b * ldd + kk] = t;
+      }
+    }
+  }
+}
+
 // dst[b][k] = (sum_s PA[s][b][k]) * gate, gate = (H[b][k] > 0 ? scale : 0) for hidden layers
 // (H is the post-ReLU, post-dropout activation so H>0 <=> ReLU active and kept), 1 at the cut.
 __global__ void bwd_epilogue_kernel(const float* __restrict__ PA, int nsplit, int B, int K,
@@ -678,17 +935,18 @@ __global__ void bwd_epilogue_kernel(const float* __restrict__ PA, int nsplit, in
   const size_t total = (size_t)B * K;
   for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
     const int b = (int)(idx / K), k = (int)(idx - (size_t)b * K);
+    const float hv = H ? H[(size_t)b * ldh + k] : 1.f;   // requested before the partials
     float s = 0.f;
     const float* pp = PA + (size_t)b * K + k;
     const size_t pstride = (size_t)kBT * K;
     int p = 0;
-    for (; p + 4 <= nsplit; p += 4) {
+    for (; p + 4 <= nsplit; p += 4) {            // four independent loads in flight, fixed add order
       const float p0 = pp[(size_t)p * pstride], p1 = pp[(size_t)(p + 1) * pstride];
       const float p2 = pp[(size_t)(p + 2) * pstride], p3 = pp[(size_t)(p + 3) * pstride];
       s += p0; s += p1; s += p2; s += p3;
     }
     for (; p < nsplit; ++p) s += pp[(size_t)p * pstride];
-    if (H) s = H[(size_t)b * ldh + k] > 0.f ? s * scale : 0.f;
+    if (H) s = hv > 0.f ? s * scale : 0.f;
     dst[(size_t)b * ldd + k] = s;
   }
 }

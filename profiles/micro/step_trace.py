@@ -64,7 +64,9 @@ read_trace()
 run(140)
 t = read_trace()
 L = len(t) // 140                               # launches per step
-KNOWN = {12: ["conv_fwd", "fwd_fc1", "epi_fc1", "fwd_fc2", "epi_fc2", "fc3+ce", "bwd_fc3", "bwd_fc2", "bepi_fc2",
+KNOWN = {10: ["conv_fwd", "fwd_fc1+epi", "fwd_fc2+epi", "fc3+ce", "bwd_fc3", "bwd_fc2", "bepi_fc2", "bwd_fc1", "bepi_fc1",
+              "conv_bwd"],
+         12: ["conv_fwd", "fwd_fc1", "epi_fc1", "fwd_fc2", "epi_fc2", "fc3+ce", "bwd_fc3", "bwd_fc2", "bepi_fc2",
               "bwd_fc1", "bepi_fc1", "conv_bwd"],
          14: ["conv_fwd", "fwd_fc1", "epi_fc1", "fwd_fc2", "epi_fc2", "fwd_fc3", "ce", "bwd_fc3", "bepi_fc3", "bwd_fc2",
               "bepi_fc2", "bwd_fc1", "bepi_fc1", "conv_bwd"]}

@@ -135,7 +135,6 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
       if (k < klen) {
         const float* src = W + (size_t)(gi * 8) * ldw + k0 + k;
         if (gi * 8 + 8 <= N) {
-#pragma unroll
           if (gi * 8 < l2_keep_w) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) cp_async16_hint(wring + (slot * 8 + i) * 32 + lane, src + (size_t)i * ldw, pol_keep);

@@ -47,6 +47,14 @@ const char* sn_last_error(void);
  * nothing from tensor cores.  (No counterpart in the reference: one CPU fp32 path.) */
 int sn_set_matmul_precision(int mode);
 int sn_get_matmul_precision(void);
+/* Route the weight stream of big layers at batch <= 16 through the tensor cores (1) or the CUDA
+ * cores (0, default).  The tensor-core form (3xTF32 with the weight operand in tensor memory,
+ * gemm_tc.cuh: skinny_fwd_x3_kernel) is fp32-accurate and passes the same parity tests, but an
+ * M=128 N=16 K=8 MMA costs ~120 cycles whatever N is, so at batch 16 it is slower than the FMA
+ * kernel (36 vs 28 us on fc1); kept selectable for measurement.  Ignored in precision mode 2.
+ * (No counterpart in the reference.) */
+int sn_set_skinny_tensor_forward(int on);
+int sn_get_skinny_tensor_forward(void);
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 uint64_t sn_launch_count(void);
 

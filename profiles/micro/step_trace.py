@@ -88,3 +88,4 @@ if hasattr(lib, "sn_trace_phase_read"):
     if lib.sn_trace_phase_read(ph.ctypes.data) == 0 and ph[0]:
         nz = ph[ph > 0]
         print("  phase stamps of the instrumented kernel (clock64 cycles from entry):", (nz - nz[0]).tolist())
+        print("  raw phase slots:", ph.tolist())

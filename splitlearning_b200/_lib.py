@@ -21,6 +21,8 @@ SIGNATURES = {
     "sn_launch_count": (_u64, []),
     "sn_set_matmul_precision": (_i, [_i]),
     "sn_get_matmul_precision": (_i, []),
+    "sn_set_skinny_tensor_forward": (_i, [_i]),
+    "sn_get_skinny_tensor_forward": (_i, []),
     "sn_conv_pool_forward": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "sn_conv_pool_backward_scratch_bytes": (_sz, [_i]),
     "sn_conv_pool_backward": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp]),

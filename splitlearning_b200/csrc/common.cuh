@@ -97,7 +97,11 @@ __device__ unsigned g_trace_n;
 __device__ long long g_trace_phase[16];        // clock64 phase stamps of one CTA of the kernel under study
 #define SN_TP(i) do { if (threadIdx.x == 0) tp_[i] = clock64(); } while (0)
 #define SN_TP_DECL long long tp_[16] = {0}
+#ifdef SN_TRACE_TC   // the tcgen05 skinny kernel owns g_trace_phase in this build
+#define SN_TP_FLUSH() do {} while (0)
+#else
 #define SN_TP_FLUSH() do { if (threadIdx.x == 0) for (int q_ = 0; q_ < 16; ++q_) g_trace_phase[q_] = tp_[q_]; } while (0)
+#endif
 #else
 #define SN_TP(i) do {} while (0)
 #define SN_TP_DECL do {} while (0)

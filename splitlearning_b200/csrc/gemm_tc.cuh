@@ -343,6 +343,291 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   }
 }
 
+// =====================================================================================
+// Skinny forward on tensor cores: P[q][b][n] = partial sums of X[b][:] . W[n][:] for B <= 16.
+//
+// At batch 16 the first layer is a 108 MB weight stream with 16 FMAs per weight: on the CUDA
+// cores that is FP32-pipe-bound (27 us against a 17 us HBM floor).  Here the weights are
+// the M operand: D[128 weight rows x 16 batch] += W_tile[128 x 8] * X^T[8 x 16], kind::tf32,
+// M=128 N=16 K=8 per instruction, as 3xTF32 (lo.hi + hi.lo + hi.hi) so the result keeps fp32
+// accuracy.  The SIMT work per weight drops from 16 FMAs to one AND and one SUB (the lo twin),
+// and the kernel becomes the HBM stream it should be.
+//
+// Work unit = (row tile of 128 weight rows, k block of 32); units are ordered row-tile-major and cut
+// into equal contiguous ranges, one per CTA (grid = #SMs, whatever N and K are).  A range touches
+// at most two row tiles: two sets of accumulators in TMEM.  A row tile's CTAs are consecutive;
+// CTA c writes its partial into slot c - c_first(tile), and the last CTA of a tile zero-fills the
+// slots nobody wrote, so fwd_epilogue_kernel adds a fixed `qmax` slots per element.
+//   warp 0      TMA producer (8-stage ring of 16 KB weight tiles + 2 KB activation blocks; the
+//               weight loads of the first stages are issued BEFORE the dependency wait when the
+//               host allows, and rows below l2_keep_w carry the evict_last L2 policy)
+//   warp 1      TMEM alloc + MMA issue (M operand from tensor memory, N operand from shared memory)
+//   warps 2..5  per stage: weight rows -> hi and lo operands in tensor memory (tcgen05.st), lo twin
+//               of the activation block; at the end accumulators -> partial stores (lane = weight
+//               row, so each of the 16 stores of a warp is one contiguous 128-byte segment)
+// =====================================================================================
+constexpr int kSkStages = 8;
+constexpr int kSkNB = 16;                           // batch columns of one accumulator
+constexpr int kSkAccs = 12;                         // independent accumulators per segment
+constexpr int kSkAccCols = 2 * kSkAccs * kSkNB;     // 384 TMEM columns of accumulators (two segments)
+constexpr int kSkTmemCols = 512;                    // + 2 x (32 hi + 32 lo) columns of weight operand
+
+struct __align__(1024) SkSmem {
+  float a[kSkStages][BM * BK];                      // weight tiles as TMA delivers them (SWIZZLE_128B)
+  float b[kSkStages][kSkNB * BK];                   // activation blocks, hi (as loaded) ...
+  float b_lo[kSkStages][kSkNB * BK];                // ... and lo twins
+  unsigned long long full_bar[kSkStages];           // TMA landed
+  unsigned long long split_bar[kSkStages];          // operands of the stage are ready for the MMAs
+  unsigned long long empty_bar[kSkStages];          // MMAs of the stage are done (smem slot free)
+  unsigned long long a_empty_bar[2];                // MMAs reading TMEM operand buffer j are done
+  unsigned long long tmem_full_bar[2];
+  unsigned tmem_base;
+};
+constexpr size_t sk_smem_bytes() { return sizeof(SkSmem) + 1024; }
+
+__device__ __forceinline__ void tma_load_2d_hint(void* dst, const CUtensorMap* map, unsigned long long* bar, int c0, int c1,
+                                                 unsigned long long policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+
+// D[tmem] (+)= A[tmem] * B[smem descriptor]: the M operand comes from tensor memory (lane = row,
+// one 32-bit column per k), so the MMA reads no shared memory for it
+__device__ __forceinline__ void mma_tf32_ts(unsigned tmem_d, unsigned tmem_a, unsigned long long bdesc, unsigned idesc,
+                                            unsigned accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+__device__ __forceinline__ void tmem_st32(unsigned taddr, const unsigned (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,"
+      "%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+      "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]),
+      "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]),
+      "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(unsigned taddr, unsigned (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+        "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+
+// first / last CTA whose unit range [floor(c*U/G), floor((c+1)*U/G)) contains unit x
+__host__ __device__ inline int sk_cta_of_unit(long long x, long long U, long long G) { return (int)(((x + 1) * G - 1) / U); }
+
+__global__ void __launch_bounds__(kThreads, 1)
+skinny_fwd_x3_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x, int N, int K,
+                     int B, float* __restrict__ P, int Bpad, int qmax, int prefetch_early, int l2_keep_w) {
+  extern __shared__ unsigned char smem_raw[];
+  SkSmem& sm = *reinterpret_cast<SkSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long KB = (K + BK - 1) / BK, RT = (N + BM - 1) / BM, U = KB * RT, G = gridDim.x;
+  const long long u0 = (long long)blockIdx.x * U / G, u1 = (long long)(blockIdx.x + 1) * U / G;
+  const int nunits = (int)(u1 - u0);
+  const int rt_first = (int)(u0 / KB);
+  constexpr unsigned kStageBytes = (BM * BK + kSkNB * BK) * 4;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
+    for (int s = 0; s < kSkStages; ++s) {
+      mbar_init(&sm.full_bar[s], 1);
+      mbar_init(&sm.split_bar[s], 4);              // one arrival per splitter warp
+      mbar_init(&sm.empty_bar[s], 1);
+    }
+    for (int j = 0; j < 2; ++j) {
+      mbar_init(&sm.a_empty_bar[j], 1);
+      mbar_init(&sm.tmem_full_bar[j], 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)),
+                 "r"(kSkTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const unsigned tmem_d = sm.tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      unsigned long long pol_keep, pol_norm;
+      asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+      asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol_norm));
+      auto load_w = [&](int i) {
+        const long long u = u0 + i;
+        const int rt = (int)(u / KB), kb = (int)(u - (long long)rt * KB), s = i % kSkStages;
+        tma_load_2d_hint(sm.a[s], &map_w, &sm.full_bar[s], kb * BK, rt * BM, rt * BM < l2_keep_w ? pol_keep : pol_norm);
+      };
+      auto load_x = [&](int i) {
+        const long long u = u0 + i;
+        const int kb = (int)(u % KB), s = i % kSkStages;
+        tma_load_2d(sm.b[s], &map_x, &sm.full_bar[s], kb * BK, 0);
+      };
+      // the weights were last written at least two launches back (the host says so): start
+      // their stream before the dependency wait; the activations are the predecessor's output
+      const int npre = prefetch_early ? min(kSkStages, nunits) : 0;
+      for (int i = 0; i < npre; ++i) {
+        mbar_expect_tx(&sm.full_bar[i % kSkStages], kStageBytes);
+        load_w(i);
+      }
+      pdl_wait();
+      pdl_launch();
+      for (int i = 0; i < npre; ++i) load_x(i);
+      for (int i = npre; i < nunits; ++i) {
+        const int s = i % kSkStages;
+        const unsigned ph = (i / kSkStages) & 1;
+        mbar_wait(&sm.empty_bar[s], ph ^ 1);
+        mbar_expect_tx(&sm.full_bar[s], kStageBytes);
+        load_w(i);
+        load_x(i);
+      }
+    } else {
+      pdl_wait();
+      pdl_launch();
+    }
+  } else if (warp == 1) {
+    pdl_wait();
+    pdl_launch();
+    if (lane == 0) {
+      const unsigned idesc = make_idesc_tf32(BM, kSkNB, false, false);
+      for (int i = 0; i < nunits; ++i) {
+        const int s = i % kSkStages, j = i & 1;
+        const unsigned ph = (i / kSkStages) & 1;
+        const long long u = u0 + i;
+        const int rt = (int)(u / KB), kb = (int)(u - (long long)rt * KB);
+        const int seg = rt != rt_first;
+        const bool seg_start = (i == 0) || (kb == 0);
+        const bool seg_end = (i == nunits - 1) || (kb == KB - 1);
+        mbar_wait(&sm.split_bar[s], ph);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        // Twelve independent accumulators per segment (3 products x 4 k-steps of the block), 16
+        // TMEM columns each: an N=16 MMA is far shorter than the pipeline's accumulate latency, so
+        // one accumulator would serialise the issue stream; and each chain adds once per k block
+        // instead of twelve times, which cuts the accumulator's truncation bias by an order of
+        // magnitude.  The epilogue adds the twelve in fp32.
+        const unsigned d = tmem_d + (unsigned)(seg * kSkAccs * kSkNB);
+        const unsigned a_hi = tmem_d + (unsigned)(kSkAccCols + j * 64), a_lo = a_hi + 32;
+        const unsigned long long bd = make_desc_kmajor_sw128(sm.b[s]), bl = make_desc_kmajor_sw128(sm.b_lo[s]);
+        const unsigned acc = seg_start ? 0u : 1u;
+#pragma unroll
+        for (int k = 0; k < BK / 8; ++k) {
+          mma_tf32_ts(d + (unsigned)((0 * 4 + k) * kSkNB), a_lo + 8 * k, bd + 2 * k, idesc, acc);
+          mma_tf32_ts(d + (unsigned)((1 * 4 + k) * kSkNB), a_hi + 8 * k, bl + 2 * k, idesc, acc);
+          mma_tf32_ts(d + (unsigned)((2 * 4 + k) * kSkNB), a_hi + 8 * k, bd + 2 * k, idesc, acc);
+        }
+        mma_commit(&sm.empty_bar[s]);
+        mma_commit(&sm.a_empty_bar[j]);
+        if (seg_end) mma_commit(&sm.tmem_full_bar[seg]);
+      }
+    }
+  } else {
+    // Operand warps 2..5.  Thread = weight row (TMEM lane quarter = warp % 4): it reads its row's
+    // 32 floats of the stage from the swizzled tile (8 conflict-free LDS.128), and writes them and
+    // their lo twins straight into tensor memory, from where the MMAs take the M operand.  The
+    // first version kept hi and lo tiles in shared memory: 6.5 bytes of shared-memory traffic per
+    // weight byte (TMA write, twin read + write, three MMA reads) - more than the SMs have at HBM
+    // rate - and ran slower than the CUDA-core kernel.  Now: TMA write + one read.
+    pdl_wait();
+    pdl_launch();
+    const int q = warp & 3;
+    const int t = threadIdx.x - 64;
+    const int r = q * 32 + lane;
+    const unsigned lane_addr = (unsigned)(q * 32) << 16;
+    for (int i = 0; i < nunits; ++i) {
+      const int s = i % kSkStages, j = i & 1;
+      const unsigned ph = (i / kSkStages) & 1;
+      mbar_wait(&sm.full_bar[s], ph);
+      const float4* rowp = reinterpret_cast<const float4*>(sm.a[s]) + r * 8;
+      unsigned hi[32], lo[32];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const float4 v = rowp[c ^ (r & 7)];
+        hi[4 * c + 0] = __float_as_uint(v.x); hi[4 * c + 1] = __float_as_uint(v.y);
+        hi[4 * c + 2] = __float_as_uint(v.z); hi[4 * c + 3] = __float_as_uint(v.w);
+      }
+      const float4 xb = reinterpret_cast<const float4*>(sm.b[s])[t];
+#pragma unroll
+      for (int e = 0; e < 32; ++e) lo[e] = __float_as_uint(tf32_lo(__uint_as_float(hi[e])));
+      reinterpret_cast<float4*>(sm.b_lo[s])[t] = make_float4(tf32_lo(xb.x), tf32_lo(xb.y), tf32_lo(xb.z), tf32_lo(xb.w));
+      // operand buffer j was last read by the MMAs of unit i-2
+      if (i >= 2) mbar_wait(&sm.a_empty_bar[j], (unsigned)(((i >> 1) - 1) & 1));
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const unsigned a_hi = tmem_d + lane_addr + (unsigned)(kSkAccCols + j * 64);
+      tmem_st32(a_hi, hi);
+      tmem_st32(a_hi + 32, lo);
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // b_lo: generic-proxy write -> tensor core read
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.split_bar[s]);
+    }
+    // accumulators -> partial slots: sum of the twelve, small products first (lo.hi, hi.lo, then
+    // hi.hi), fixed order
+    const int nseg = nunits == 0 ? 0 : ((int)((u1 - 1) / KB) != rt_first ? 2 : 1);
+    for (int seg = 0; seg < nseg; ++seg) {
+      const int rt = rt_first + seg;
+      mbar_wait(&sm.tmem_full_bar[seg], 0);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      float acc[kSkNB];
+#pragma unroll
+      for (int b = 0; b < kSkNB; ++b) acc[b] = 0.f;
+#pragma unroll
+      for (int a0 = 0; a0 < kSkAccs; a0 += 4) {
+        unsigned v[4][kSkNB];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) tmem_ld16(tmem_d + lane_addr + (unsigned)((seg * kSkAccs + a0 + a) * kSkNB), v[a]);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < kSkNB; ++b) acc[b] += __uint_as_float(v[a][b]);
+      }
+      const int c_first = sk_cta_of_unit((long long)rt * KB, U, G);
+      const int c_last = sk_cta_of_unit((long long)(rt + 1) * KB - 1, U, G);
+      const int slot = (int)blockIdx.x - c_first;
+      const int n = rt * BM + r;
+      if (n < N) {
+        float* dst = P + (size_t)slot * Bpad * N + n;
+#pragma unroll
+        for (int b = 0; b < kSkNB; ++b)
+          if (b < B) dst[(size_t)b * N] = acc[b];
+        if ((int)blockIdx.x == c_last) {
+          for (int z = slot + 1; z < qmax; ++z) {
+            float* zd = P + (size_t)z * Bpad * N + n;
+#pragma unroll
+            for (int b = 0; b < kSkNB; ++b)
+              if (b < B) zd[(size_t)b * N] = 0.f;
+          }
+        }
+      }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(kSkTmemCols) : "memory");
+  }
+}
+
 // ------------------------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,

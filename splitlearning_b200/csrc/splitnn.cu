@@ -203,11 +203,36 @@ static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int l
   return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
 }
 
+// tcgen05 skinny forward (gemm_tc.cuh): grid and partial-slot count for a [N x K] layer
+struct SkPlan { int grid, qmax; };
+constexpr size_t kSkinnyTcMinElems = 16u << 20;     // below this the launch is latency, not bandwidth
+std::atomic<int> g_skinny_tensor{-1};               // -1: not set yet (SN_TC_SKINNY=1 in the environment turns it on)
+static bool sk_enabled() {
+  int v = g_skinny_tensor.load();
+  if (v < 0) {
+    v = (getenv("SN_TC_SKINNY") && atoi(getenv("SN_TC_SKINNY")) != 0) ? 1 : 0;
+    g_skinny_tensor.store(v);
+  }
+  return v == 1 && g_matmul_precision.load() != 2;
+}
+static SkPlan plan_sk(int K, int N, int sms) {
+  const long long KB = ceil_div(K, tc::BK), RT = ceil_div(N, tc::BM), U = KB * RT;
+  long long G = std::min<long long>(sms, U);
+  G = std::max(G, RT);                              // a range may touch two row tiles at most
+  int qmax = 1;
+  for (long long rt = 0; rt < RT; ++rt)
+    qmax = std::max(qmax, tc::sk_cta_of_unit((rt + 1) * KB - 1, U, G) - tc::sk_cta_of_unit(rt * KB, U, G) + 1);
+  return SkPlan{(int)G, qmax};
+}
+static bool sk_applies(int B, int K, int N, const float* X, int ldx, const float* W) {
+  return sk_enabled() && B <= tc::kSkNB && (size_t)N * K >= kSkinnyTcMinElems && tc::usable(X, ldx, W, K, K);
+}
+
 static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, const float* bias, int K, int N,
                              int relu, const uint8_t* mask, float keep_prob, float scale, uint64_t seed,
                              uint64_t offset, int layer, float* H, int ldh, float* out2, float* P, int sms,
                              cudaStream_t st, Profiler* prof = nullptr, const CeTail* ce = nullptr,
-                             bool* ce_fused = nullptr, int l2_keep_w = 0) {
+                             bool* ce_fused = nullptr, int l2_keep_w = 0, bool prefetch_w = false) {
   if (ce_fused) *ce_fused = false;
   if (B <= kSkinnyFwdMaxB && (size_t)N * K <= kSmallLayerElems && K <= kSmallLayerMaxK) {
     dim3 grid(ceil_div(N, kHeadRows), ceil_div(B, kBT));
@@ -219,6 +244,20 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
                                           layer, H, ldh, out2, layer > 0 ? 1 : 0, tail ? *ce : CeTail{});
     if (ce_fused) *ce_fused = tail;
     Profiler::end(pe, st);
+    SN_LAUNCH_CHECK();
+  } else if (sk_applies(B, K, N, X, ldx, W)) {
+    // big layer, B <= 16: the weight stream goes through the tensor cores (3xTF32, fp32-accurate)
+    const SkPlan p = plan_sk(K, N, sms);
+    CUtensorMap mw, mx;
+    if (tc::make_map(&mw, W, N, K, K, tc::BM) || tc::make_map(&mx, X, B, K, ldx, tc::kSkNB)) return 1;
+    if (set_smem(tc::skinny_fwd_x3_kernel, tc::sk_smem_bytes())) return 1;
+    cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
+    launch_k(tc::skinny_fwd_x3_kernel, dim3(p.grid), dim3(tc::kThreads), tc::sk_smem_bytes(), st, mw, mx, N, K, B, P, kBT, p.qmax,
+             prefetch_w ? 1 : 0, l2_keep_w);
+    Profiler::end(pe, st);
+    SN_LAUNCH_CHECK();
+    launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, P, p.qmax, kBT, B, N, bias, relu, mask, keep_prob,
+             scale, seed, offset, layer, H, ldh, out2);
     SN_LAUNCH_CHECK();
   } else if (B <= kSkinnyFwdMaxB && (K % 4) == 0) {
     FwdPlan p = plan_fwd(K, N, sms);
@@ -258,7 +297,9 @@ static size_t fwd_partial_floats(int B, int K, int N, int sms) {
   if (B > kSkinnyFwdMaxB || ((size_t)N * K <= kSmallLayerElems && K <= kSmallLayerMaxK)) return 0;
   if ((K % 4) != 0) return 0;
   FwdPlan p = plan_fwd(K, N, sms);
-  return (size_t)kFwdSlots * p.ksplit * round_up(B, kBT) * N;
+  size_t need = (size_t)kFwdSlots * p.ksplit * round_up(B, kBT) * N;
+  if ((size_t)N * K >= kSkinnyTcMinElems) need = std::max(need, (size_t)plan_sk(K, N, sms).qmax * kBT * N);
+  return need;
 }
 
 }  // namespace sn
@@ -284,6 +325,7 @@ struct sn_bob {
   float* dWbuf = nullptr;      // general-batch path only (lazy)
   float* row_loss = nullptr;
   unsigned* ticket = nullptr;
+  int last_writer = -1;        // layer whose weights the most recent launch on this handle updated (-1: none)
   bool stashed = false;
   int stashed_B = 0;
   int heads = 1;
@@ -320,6 +362,11 @@ int sn_set_matmul_precision(int mode) {
   return 0;
 }
 int sn_get_matmul_precision(void) { return g_matmul_precision.load(); }
+int sn_set_skinny_tensor_forward(int on) {
+  g_skinny_tensor.store(on ? 1 : 0);
+  return 0;
+}
+int sn_get_skinny_tensor_forward(void) { return sk_enabled() ? 1 : 0; }
 const char* sn_last_error(void) { return g_last_error.c_str(); }
 uint64_t sn_launch_count(void) { return g_launches.load(); }
 
@@ -673,10 +720,12 @@ static int bob_forward_impl(sn_bob* h, const float* act, int B, int train, const
       launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, h->sms)), dim3(256), 0, st, h->PF, ceil_div(K, 128), kBT, B, N,
                h->b[l], relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N, last ? out : nullptr);
       SN_LAUNCH_CHECK();
+      h->last_writer = -1;
     } else if (launch_linear_fwd(X, ldx, B, h->W[l], h->b[l], K, N, relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N,
                                  last ? out : nullptr, h->P, h->sms, st, &h->prof, last ? ce : nullptr,
-                                 last ? ce_fused : nullptr, h->l2_keep[l]))
+                                 last ? ce_fused : nullptr, h->l2_keep[l], h->last_writer != l))
       return 1;
+    h->last_writer = -1;
     X = h->H[l + 1];
     ldx = N;
   }
@@ -699,6 +748,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
     float* dst = l > 0 ? h->dZ[l] : cut_grad;
     const float* gateH = l > 0 ? h->H[l] : nullptr;
     const float gscale = (l > 0 && h->dropout_p > 0.f) ? scale : 1.f;
+    h->last_writer = l;        // reset below where a non-updating launch (the dA reduction) comes last
     if (B <= kBT && (size_t)N * K <= kSmallLayerElems && N <= 8 * kSmallBwdRows) {
       // tiny layer: one launch, no n split, gate applied in place (bwd_small_kernel)
       cudaEvent_t pe = h->prof.begin(st, 1, l);
@@ -726,6 +776,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, p.nsplit, B, K, gateH, K,
                  gscale, dst, K);
         SN_LAUNCH_CHECK();
+        h->last_writer = -1;
       } else if (l == 0 && next_act && next_B > 0 && next_B <= kBT && (size_t)N * K > kSmallLayerElems) {
         // SISA: fuse the next step's layer-0 forward into this traversal
         if (!h->PF) SN_CUDA(cudaMalloc(&h->PF, (size_t)ceil_div(K, 128) * kBT * N * 4));
@@ -792,6 +843,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         // PA holds one dense [B][K] "split"; bwd_epilogue indexes splits with a 16-row stride
         launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, 1, B, K, gateH, K, gscale, dst, K);
         SN_LAUNCH_CHECK();
+        h->last_writer = -1;
       }
     }
   }

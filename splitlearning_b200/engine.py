@@ -18,6 +18,12 @@ def set_matmul_precision(mode):
     check(_lib.load().sn_set_matmul_precision(int(mode)))
 
 
+def set_skinny_tensor_forward(on):
+    """Batch <= 16 forward of big layers on tensor cores (3xTF32, weights in tensor memory) instead of
+    the FMA kernel.  fp32-accurate but slower at this batch size (see include/splitnn.h); off by default."""
+    check(_lib.load().sn_set_skinny_tensor_forward(1 if on else 0))
+
+
 def _stream(device=None):
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 

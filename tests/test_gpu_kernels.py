@@ -483,3 +483,25 @@ def test_error_paths_and_edge_shapes(eng):
     # a zero-length SISA epoch is a no-op
     bob.server_epoch(torch.zeros(0, 52, device="cuda"), torch.zeros(0, dtype=torch.int64, device="cuda"), [0])
     torch.cuda.synchronize()
+
+
+def test_skinny_forward_on_tensor_cores_matches_fma_kernel(eng):
+    """The selectable tcgen05 form of the batch<=16 weight stream (3xTF32, weight operand in tensor
+    memory, 12 independent TMEM accumulators): same inputs through both kernels and fp64."""
+    rng = np.random.RandomState(77)
+    for B, K, N in ((16, 5408, 5000), (9, 5408, 5000), (16, 4100, 4200)):
+        x = (rng.rand(B, K) * 30 * (rng.rand(B, K) < 0.6)).astype(np.float32)
+        W = (rng.uniform(-1, 1, (N, K)) / np.sqrt(K)).astype(np.float32)
+        bias = rng.uniform(-1, 1, N).astype(np.float32)
+        mask = (rng.rand(B, N) < 0.5).astype(np.uint8)
+        ref = np.maximum(x.astype(np.float64) @ W.astype(np.float64).T + bias, 0) * mask * 2.0
+        fma = eng.linear_forward(cu(x), cu(W), cu(bias), relu=True, keep_mask=cu(mask), mask_scale=2.0).cpu().numpy()
+        eng.set_skinny_tensor_forward(True)
+        try:
+            tc = eng.linear_forward(cu(x), cu(W), cu(bias), relu=True, keep_mask=cu(mask), mask_scale=2.0).cpu().numpy()
+            tc2 = eng.linear_forward(cu(x), cu(W), cu(bias), relu=True, keep_mask=cu(mask), mask_scale=2.0).cpu().numpy()
+        finally:
+            eng.set_skinny_tensor_forward(False)
+        assert np.array_equal(tc, tc2)                  # deterministic
+        assert rel_err(fma, ref) <= 2e-6
+        assert rel_err(tc, ref) <= 1e-5                 # 3xTF32 + fp32 tensor-core accumulation

@@ -3,7 +3,7 @@
 in which CTA 0 of each kernel stamps %globaltimer right after its PDL dependency wait (= when the
 previous kernel has completed).  Differences of consecutive stamps are what each kernel costs the
 step with launch overlap as it really is - ncu serialises launches and cannot show that.
-usage: python profiles/micro/step_trace.py [vanilla|sisa]"""
+usage: python profiles/micro/step_trace.py [vanilla|sisa|local]"""
 import ctypes as C
 import os
 import sys
@@ -45,6 +45,18 @@ if mode == "vanilla":
     def run(n):
         for i in range(n):
             E.vanilla_step(alices[0][1], bob, xs[i % 64], ys[i % 64], 0, 1, i + 1, act, cut, loss)
+elif mode == "local":
+    # SISA phase 1: an Alice's local epoch (conv fwd -> CE over the 5408 activations -> conv bwd + Adam)
+    from splitlearning_b200 import models as M
+    torch.manual_seed(0)
+    am = M.model1_sisa(dev)
+    alice = am.make_engine(optimizer=E.SN_OPT_ADAM, lr=1e-3, weight_decay=1e-5, max_batch=B)
+    xl = (torch.randint(0, 256, (140 * B, 1, 28, 28)).float() * (torch.rand(140 * B, 1, 28, 28) < 0.4)).to(dev)
+    yl = torch.randint(0, 10, (140 * B,)).to(dev)
+    names = None
+
+    def run(n):
+        alice.local_epoch(xl, yl, B)
 else:
     from splitlearning_b200 import models as M
     torch.manual_seed(1)

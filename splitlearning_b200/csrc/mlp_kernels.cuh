@@ -322,26 +322,22 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
 
 // ------------------------------------------------------------------------------------------
 // Cross-entropy of one row by one warp: loss = lse - z[y]; dlogits = (softmax - onehot)/B.
-// Returns the row loss (same value in every lane).  CG reads the logits with ld.global.cg (L2):
-// needed when other CTAs of the same launch wrote them.  NC > 0: the row has at most 32*NC classes
-// and `zc` already holds this lane's logits (class lane+32i, -inf beyond C), so the three passes run
+// Returns the row loss (same value in every lane).  Register form: the row has at most 32*NC
+// classes and `zc` holds this lane's logits (class lane+32i, -inf beyond C), so the three passes run
 // from registers - one L2 round trip per row instead of twelve dependent ones (clock64 phase
-// timing: 15.8k cycles for two rows per warp before, at ~500 cycles per dependent load).
+// timing: 15.8k cycles for two rows per warp before, at ~500 cycles per dependent load).  Memory
+// form: CG reads the logits with ld.global.cg (L2), needed when other CTAs of the same launch wrote
+// them.
 // ------------------------------------------------------------------------------------------
-template <bool CG, int NC>
-__device__ __forceinline__ float ce_row(const float* __restrict__ zr, const float* zc, int64_t lab, int C, float invB,
-                                        float* __restrict__ dzr, int lane) {
-  auto ld = [&](int c, int i) { return NC > 0 ? zc[i] : (CG ? __ldcg(zr + c) : zr[c]); };
-  const int iters = NC > 0 ? NC : (C + 31) >> 5;
+template <int NC>
+__device__ __forceinline__ float ce_row_reg(const float (&zc)[NC], int64_t lab, int C, float invB,
+                                            float* __restrict__ dzr, int lane) {
   float m = -INFINITY;
   int arg = 0x7fffffff;
 #pragma unroll
-  for (int i = 0; i < iters; ++i) {
+  for (int i = 0; i < NC; ++i) {
     const int c = lane + 32 * i;
-    if (c < C) {
-      const float v = ld(c, i);
-      if (v > m) { m = v; arg = c; }
-    }
+    if (c < C && zc[i] > m) { m = zc[i]; arg = c; }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -351,36 +347,66 @@ __device__ __forceinline__ float ce_row(const float* __restrict__ zr, const floa
   }
   // sum of exp(z-m) WITHOUT the max term (which is exactly 1): log1p keeps full precision when
   // one class dominates, where log(1+eps) computed from a rounded sum would lose it
-  float s1 = 0.f;
-  float zl = 0.f;                            // z[label], picked up on the way
-  float ex[NC > 0 ? NC : 1];                 // exp(z-m) of this lane's classes (register form only)
+  float s1 = 0.f, zl = 0.f, ex[NC];
 #pragma unroll
-  for (int i = 0; i < iters; ++i) {
+  for (int i = 0; i < NC; ++i) {
     const int c = lane + 32 * i;
+    ex[i] = 1.f;
     if (c < C) {
-      const float v = ld(c, i);
-      const float e = c != arg ? expf(v - m) : 1.f;
-      if (NC > 0) ex[i] = e;
-      if (c != arg) s1 += e;
-      if (c == lab) zl = v;
+      if (c != arg) { ex[i] = expf(zc[i] - m); s1 += ex[i]; }
+      if (c == lab) zl = zc[i];
     }
   }
   s1 = warp_sum(s1);
-  zl = warp_sum(zl);                         // exactly one lane holds it, the others add zeros
-  const float s = 1.f + s1;
+  zl = warp_sum(zl);                         // exactly one lane holds z[label], the others add zeros
   const bool ok = lab >= 0 && lab < C;
   // -log_softmax(z)[y] = log(sum exp(z-m)) - (z[y]-m): no cancellation against the row max
   const float loss = ok ? (log1pf(s1) - (zl - m)) : NAN;   // torch raises on a bad target
   if (dzr) {
-    const float invs = 1.f / s;
+    const float invs = 1.f / (1.f + s1);
 #pragma unroll
-    for (int i = 0; i < iters; ++i) {
+    for (int i = 0; i < NC; ++i) {
       const int c = lane + 32 * i;
       if (c < C) {
-        float p = (NC > 0 ? ex[i] : expf(ld(c, i) - m)) * invs;
+        float p = ex[i] * invs;
         if (c == lab) p -= 1.f;
         dzr[c] = p * invB;
       }
+    }
+  }
+  return loss;
+}
+
+// the same from memory, for rows of any length (three streaming passes)
+template <bool CG>
+__device__ __forceinline__ float ce_row_mem(const float* __restrict__ zr, int64_t lab, int C, float invB,
+                                            float* __restrict__ dzr, int lane) {
+  auto ld = [&](int c) { return CG ? __ldcg(zr + c) : zr[c]; };
+  float m = -INFINITY;
+  int arg = 0x7fffffff;
+  for (int c = lane; c < C; c += 32) {
+    const float v = ld(c);
+    if (v > m) { m = v; arg = c; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, m, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
+  }
+  float s1 = 0.f;
+  for (int c = lane; c < C; c += 32)
+    if (c != arg) s1 += expf(ld(c) - m);
+  s1 = warp_sum(s1);
+  const float s = 1.f + s1;
+  const bool ok = lab >= 0 && lab < C;
+  const float loss = ok ? (log1pf(s1) - (ld(ok ? (int)lab : 0) - m)) : NAN;
+  if (dzr) {
+    const float invs = 1.f / s;
+    for (int c = lane; c < C; c += 32) {
+      float p = expf(ld(c) - m) * invs;
+      if (c == lab) p -= 1.f;
+      dzr[c] = p * invB;
     }
   }
   return loss;
@@ -399,9 +425,9 @@ __device__ __forceinline__ float ce_row_auto(const float* __restrict__ zr, int64
       const int c = lane + 32 * i;
       zc[i] = c < C ? (CG ? __ldcg(zr + c) : zr[c]) : -INFINITY;
     }
-    return ce_row<CG, kCeRegClasses>(zr, zc, lab, C, invB, dzr, lane);
+    return ce_row_reg<kCeRegClasses>(zc, lab, C, invB, dzr, lane);
   }
-  return ce_row<CG, 0>(zr, nullptr, lab, C, invB, dzr, lane);
+  return ce_row_mem<CG>(zr, lab, C, invB, dzr, lane);
 }
 
 // Cross-entropy fused behind the last layer (fwd_small_kernel): labels == nullptr turns it off.
@@ -587,6 +613,103 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ z, in
       const float L = s / (float)B;
       if (loss_out) *loss_out = L;
       if (loss_out2) *loss_out2 = L;
+      *ticket = 0u;
+    }
+  }
+}
+
+// Cross-entropy over LONG rows (an Alice's local loss treats her 5408 activations as logits): one
+// CTA per row, the whole row in registers (NV values per thread, one coalesced read), CTA-wide
+// argmax / sum through shared memory.  The warp-per-row kernel streams such a row three times from
+// one warp: 21.5 us of the 31 us local step (profiles/micro/step_trace.py local); this form reads it once.
+// Same first-argmax, log1p and gradient formulas; fixed reduction order (deterministic).
+template <int NV>
+__global__ void __launch_bounds__(256) ce_wide_kernel(const float* __restrict__ z, int ldz, const int64_t* __restrict__ y,
+                                                      int B, int C, float* __restrict__ dz, int lddz,
+                                                      float* __restrict__ row_loss, unsigned* __restrict__ ticket,
+                                                      float* __restrict__ loss_out) {
+  __shared__ float sm_m[8], sm_s[8], sm_zl;
+  __shared__ int sm_a[8];
+  __shared__ unsigned is_last;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.x;
+  const float* zr = z + (size_t)b * ldz;
+  pdl_wait();
+  pdl_launch();
+  const int64_t lab = y[b];
+  float v[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = tid + 256 * i;
+    v[i] = c < C ? zr[c] : -INFINITY;
+  }
+  float m = -INFINITY;
+  int arg = 0x7fffffff;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = tid + 256 * i;
+    if (c < C && v[i] > m) { m = v[i]; arg = c; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, m, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
+  }
+  if (lane == 0) { sm_m[warp] = m; sm_a[warp] = arg; }
+  if (tid == 0) sm_zl = 0.f;
+  __syncthreads();
+  m = sm_m[0];
+  arg = sm_a[0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w) {
+    const float om = sm_m[w];
+    const int oa = sm_a[w];
+    if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
+  }
+  float s1 = 0.f, ex[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = tid + 256 * i;
+    ex[i] = 1.f;
+    if (c < C) {
+      if (c != arg) { ex[i] = expf(v[i] - m); s1 += ex[i]; }
+      if (c == lab) sm_zl = v[i];                       // exactly one thread
+    }
+  }
+  s1 = warp_sum(s1);
+  if (lane == 0) sm_s[warp] = s1;
+  __syncthreads();
+  s1 = sm_s[0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w) s1 += sm_s[w];
+  const bool ok = lab >= 0 && lab < C;
+  if (tid == 0) row_loss[b] = ok ? (log1pf(s1) - (sm_zl - m)) : NAN;   // torch raises on a bad target
+  if (dz) {
+    const float invs = 1.f / (1.f + s1), invB = 1.f / (float)B;
+    float* dzr = dz + (size_t)b * lddz;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = tid + 256 * i;
+      if (c < C) {
+        float p = ex[i] * invs;
+        if (c == lab) p -= 1.f;
+        dzr[c] = p * invB;
+      }
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  if (warp == 0) {
+    float s = 0.f;
+    for (int r = lane; r < B; r += 32) s += __ldcg(row_loss + r);
+    s = warp_sum(s);
+    if (lane == 0) {
+      if (loss_out) *loss_out = s / (float)B;
       *ticket = 0u;
     }
   }

@@ -471,7 +471,12 @@ int sn_linear_forward_noalloc(const float* x, const float* W, const float* bias,
 
 static int launch_ce(const float* z, int ldz, const int64_t* y, int B, int C, float* dz, int lddz, float* row_loss,
                      unsigned* ticket, float* loss, float* loss2, cudaStream_t st) {
-  launch_k(ce_kernel, dim3(ceil_div(B, 8)), dim3(256), 0, st, z, ldz, y, B, C, dz, lddz, row_loss, ticket, loss, loss2);
+  constexpr int kWideNV = 24;                       // ce_wide_kernel holds rows of up to 6144 classes in registers
+  if (C > 128 && C <= 256 * kWideNV && !loss2) {
+    launch_k(ce_wide_kernel<kWideNV>, dim3(B), dim3(256), 0, st, z, ldz, y, B, C, dz, lddz, row_loss, ticket, loss);
+  } else {
+    launch_k(ce_kernel, dim3(ceil_div(B, 8)), dim3(256), 0, st, z, ldz, y, B, C, dz, lddz, row_loss, ticket, loss, loss2);
+  }
   SN_LAUNCH_CHECK();
   return 0;
 }

@@ -129,7 +129,7 @@ def run_reference(args):
 def workload_config(n_gpus):
     return {"workload": "--vanilla split NN, world_size=5 (1 Bob + 4 Alices round-robin), batch 16, "
                         "model1_sisa + model2_sisa 5408-5000-1000-100, SGD momentum 0.9 per Alice, lr 1e-3",
-            "global_batch": B, "parallelism": "single GPU" if n_gpus == 1 else f"Bob on rank 0 + Alices on ranks 1..{n_gpus - 1} (NCCL send/recv)",
+            "global_batch": B, "parallelism": "single GPU" if n_gpus == 1 else f"Bob on rank 0 + Alices on ranks 1..{n_gpus - 1}",
             "l2": f"per-step working set {20 * P_BOB / 1e6:.0f} MB (weights + momentum) > {L2_MB} MB L2: no flush needed",
             "dropout": "in-kernel Philox (perf mode)"}
 

@@ -237,6 +237,27 @@ int sn_p2p_enable_all(int n_devices);
 int sn_p2p_copy(void* dst, int dst_device, const void* src, int src_device, size_t bytes,
                 void* stream);
 
+/* Peer-memory mailboxes between the one-process-per-GPU ranks: what carries the cut-layer
+ * activations, labels and the cut-layer gradient in place of the reference's rpc_sync /
+ * dist_autograd round trips (data_entities_vanilla.py:63,73 and :231) - and in place of an NCCL
+ * send/recv pair, whose ~20 us latency per message is a quarter of the whole step at batch 16.
+ * A rank allocates a mailbox on its own GPU (sn_ipc_alloc: plain cudaMalloc, zero-filled, plus
+ * its 64-byte CUDA IPC handle), ranks exchange the handles out of band (torch.distributed), and
+ * sn_ipc_open maps a peer's mailbox (another PROCESS's allocation; NVLink peer access is enabled
+ * by the mapping).  The producing kernel then writes its output straight into the consumer's
+ * mailbox over NVLink (the conv kernel's `act`, the backward's `cut_grad` are just peer
+ * pointers), and a 4-byte flag in the same mailbox orders the two streams:
+ *   sn_stream_signal(flag, v, stream)  after all prior work of `stream`: *flag = v
+ *   sn_stream_wait(flag, v, stream)    work enqueued after it starts once *flag >= v
+ * (cuStreamWriteValue32 / cuStreamWaitValue32: no kernel spins, no host involvement).
+ * Flags must be 4-byte aligned device memory of a mailbox; values must grow monotonically. */
+int sn_ipc_alloc(size_t bytes, void** dptr, void* handle64);
+int sn_ipc_open(const void* handle64, void** dptr);
+int sn_ipc_close(void* dptr);
+int sn_ipc_free(void* dptr);
+int sn_stream_signal(void* flag, uint32_t value, void* stream);
+int sn_stream_wait(void* flag, uint32_t value, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -59,6 +59,12 @@ SIGNATURES = {
     "sn_vanilla_step": (_i, [_vp, _vp, _i, _vp, _vp, _i, _u64, _u64, _vp, _vp, _vp, _vp]),
     "sn_p2p_enable_all": (_i, [_i]),
     "sn_p2p_copy": (_i, [_vp, _i, _vp, _i, _sz, _vp]),
+    "sn_ipc_alloc": (_i, [_sz, _pp, _vp]),
+    "sn_ipc_open": (_i, [_vp, _pp]),
+    "sn_ipc_close": (_i, [_vp]),
+    "sn_ipc_free": (_i, [_vp]),
+    "sn_stream_signal": (_i, [_vp, C.c_uint32, _vp]),
+    "sn_stream_wait": (_i, [_vp, C.c_uint32, _vp]),
 }
 
 _lib = None

@@ -1170,4 +1170,63 @@ int sn_p2p_copy(void* dst, int dst_device, const void* src, int src_device, size
   return 0;
 }
 
+// ------------------------------------------------------------------ peer-memory mailboxes
+int sn_ipc_alloc(size_t bytes, void** dptr, void* handle64) {
+  SN_REQUIRE(bytes > 0 && dptr && handle64, "sn_ipc_alloc: bad arguments");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle is 64 bytes");
+  void* p = nullptr;
+  SN_CUDA(cudaMalloc(&p, bytes));
+  cudaError_t e = cudaMemset(p, 0, bytes);
+  cudaIpcMemHandle_t h;
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return fail("sn_ipc_alloc", e, __FILE__, __LINE__);
+  }
+  memcpy(handle64, &h, 64);
+  *dptr = p;
+  return 0;
+}
+int sn_ipc_open(const void* handle64, void** dptr) {
+  SN_REQUIRE(handle64 && dptr, "sn_ipc_open: bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  SN_CUDA(cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+int sn_ipc_close(void* dptr) {
+  SN_REQUIRE(dptr, "sn_ipc_close: bad arguments");
+  SN_CUDA(cudaIpcCloseMemHandle(dptr));
+  return 0;
+}
+int sn_ipc_free(void* dptr) {
+  SN_REQUIRE(dptr, "sn_ipc_free: bad arguments");
+  SN_CUDA(cudaFree(dptr));
+  return 0;
+}
+
+typedef CUresult (*StreamValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static StreamValue32Fn stream_value_fn(const char* name) {
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) return nullptr;
+  return reinterpret_cast<StreamValue32Fn>(p);
+}
+int sn_stream_signal(void* flag, uint32_t value, void* stream) {
+  SN_REQUIRE(flag && (reinterpret_cast<uintptr_t>(flag) & 3) == 0, "sn_stream_signal: flag must be a 4-byte aligned device address");
+  static StreamValue32Fn fn = stream_value_fn("cuStreamWriteValue32");
+  SN_REQUIRE(fn, "sn_stream_signal: cuStreamWriteValue32 is not available from this driver");
+  CUresult r = fn((CUstream)stream, (CUdeviceptr)flag, value, CU_STREAM_WRITE_VALUE_DEFAULT);
+  if (r != CUDA_SUCCESS) return fail_msg("libsplitnn: cuStreamWriteValue32 failed (" + std::to_string((int)r) + ")");
+  return 0;
+}
+int sn_stream_wait(void* flag, uint32_t value, void* stream) {
+  SN_REQUIRE(flag && (reinterpret_cast<uintptr_t>(flag) & 3) == 0, "sn_stream_wait: flag must be a 4-byte aligned device address");
+  static StreamValue32Fn fn = stream_value_fn("cuStreamWaitValue32");
+  SN_REQUIRE(fn, "sn_stream_wait: cuStreamWaitValue32 is not available from this driver");
+  CUresult r = fn((CUstream)stream, (CUdeviceptr)flag, value, CU_STREAM_WAIT_VALUE_GEQ);
+  if (r != CUDA_SUCCESS) return fail_msg("libsplitnn: cuStreamWaitValue32 failed (" + std::to_string((int)r) + ")");
+  return 0;
+}
+
 }  // extern "C"

@@ -81,11 +81,12 @@ class BobEngine:
         return ptr_array(keep), keep
 
     def train_step(self, act, labels, slot=0, masks=None, seed=0, offset=0, want_cut_grad=True,
-                   want_logits=False, loss_out=None):
-        """Returns (loss[device scalar], cut_grad or None, logits or None)."""
+                   want_logits=False, loss_out=None, cut_out=None):
+        """Returns (loss[device scalar], cut_grad or None, logits or None).  `cut_out`: where the
+        cut-layer gradient goes (e.g. a peer GPU's mailbox, peer.py); allocated when omitted."""
         B = act.shape[0]
         _f32c(act)
-        cut = torch.empty_like(act) if want_cut_grad else None
+        cut = cut_out if cut_out is not None else (torch.empty_like(act) if want_cut_grad else None)
         logits = torch.empty(B, self.dims[-1], device=act.device) if want_logits else None
         loss = loss_out if loss_out is not None else torch.empty((), device=act.device)
         marr, keep = self._masks(masks)

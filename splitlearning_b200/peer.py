@@ -1,0 +1,145 @@
+"""Peer-memory transport for the one-process-per-GPU split protocol (NVLink, CUDA IPC).
+
+The reference carries each step's cut-layer activations + labels to Bob and the cut-layer gradient
+back through `rpc_sync` / `dist_autograd` on CPU tensors (`data_entities_vanilla.py:63,73,231`).
+`spmd.py`'s first transport replaced that with one NCCL send/recv pair each way; at batch 16 those
+two messages cost ~43 us of a 205 us step although they move 0.7 MB.  Here nothing is "sent":
+
+    Alice rank (GPU a)                                 Bob rank (GPU 0)
+    conv kernel writes act   ----- NVLink stores ----> Bob's mailbox.act
+    labels                   ----- peer memcpy ------> Bob's mailbox.labels
+    signal(Bob.flag_act, s)                            wait(flag_act >= s)
+                                                       train step reads its own mailbox;
+    Alice's mailbox.cut      <---- NVLink stores ----- its last kernel writes cut_grad
+    wait(flag_cut >= s)                                signal(Alice.flag_cut, s)
+    conv backward reads its own mailbox
+
+Every rank owns one mailbox (`sn_ipc_alloc`), maps the peers' (`sn_ipc_open`), and orders the two
+streams with 4-byte flags written/awaited by the streams themselves (`sn_stream_signal/wait`): no
+host synchronisation, no spinning kernels, no collective.  The step counter `s` is the number of
+steps the link has carried, identical on all ranks because every rank walks the whole schedule.
+"""
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from ._lib import check
+
+D0 = 5408
+
+
+class _Raw:
+    """A device address with just enough of the tensor interface for `engine` (`data_ptr`, dtype,
+    contiguity, the LOCAL device for stream selection): peer memory must not become a torch tensor -
+    torch would place it on the owning device and synchronise across devices on every use."""
+
+    is_cuda = True
+    dtype = torch.float32
+
+    def __init__(self, address, shape, device):
+        self._a, self.shape, self.device = address, tuple(shape), device
+
+    def data_ptr(self):
+        return self._a
+
+    def is_contiguous(self):
+        return True
+
+
+class _View:
+    """torch view of LOCAL library-owned memory through __cuda_array_interface__."""
+
+    def __init__(self, address, count, typestr):
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": typestr, "data": (address, False), "version": 2}
+
+
+class Mailbox:
+    """Layout of one rank's mailbox: act [B,5408] f32 | cut [B,5408] f32 | labels [B] i64 | flags."""
+
+    def __init__(self, B):
+        self.B = B
+        self.off_act = 0
+        self.off_cut = B * D0 * 4
+        self.off_lab = 2 * B * D0 * 4
+        self.off_flag_act = self.off_lab + B * 8
+        self.off_flag_cut = self.off_flag_act + 128
+        self.bytes = self.off_flag_cut + 128
+
+
+class PeerLink:
+    """The vanilla schedule's transport over peer memory (see module docstring).  Collective set-up:
+    every rank must construct it."""
+
+    def __init__(self, rank, world, device, B):
+        self.lib = _lib.load()
+        self.rank, self.world, self.device, self.B = rank, world, device, B
+        self.box = Mailbox(B)
+        self.seq = 0
+        base, handle = C.c_void_p(), (C.c_ubyte * 64)()
+        with torch.cuda.device(device):
+            check(self.lib.sn_ipc_alloc(self.box.bytes, C.byref(base), handle))
+        self.base = base.value
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device=device)
+        every = [torch.empty(64, dtype=torch.uint8, device=device) for _ in range(world)]
+        dist.all_gather(every, mine)
+        self.peer = {}
+        # Bob maps every Alice rank's mailbox, Alice ranks map Bob's
+        wanted = range(1, world) if rank == 0 else [0]
+        for r in wanted:
+            raw = (C.c_ubyte * 64)(*every[r].cpu().tolist())
+            p = C.c_void_p()
+            with torch.cuda.device(device):
+                check(self.lib.sn_ipc_open(raw, C.byref(p)))
+            self.peer[r] = p.value
+        dist.barrier()
+        with torch.cuda.device(device):
+            self.act = torch.as_tensor(_View(self.base + self.box.off_act, B * D0, "<f4"), device=device).view(B, D0)
+            self.cut = torch.as_tensor(_View(self.base + self.box.off_cut, B * D0, "<f4"), device=device).view(B, D0)
+            self.labels = torch.as_tensor(_View(self.base + self.box.off_lab, B, "<i8"), device=device)
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def next_step(self):
+        """Called once per schedule step on EVERY rank (keeps the flag values in lock step)."""
+        self.seq += 1
+
+    # ---- Alice side
+    def alice_targets(self):
+        """Where the conv kernel writes: Bob's mailbox."""
+        return _Raw(self.peer[0] + self.box.off_act, (self.B, D0), self.device)
+
+    def alice_publish(self, y, n):
+        bob = self.peer[0]
+        check(self.lib.sn_p2p_copy(C.c_void_p(bob + self.box.off_lab), 0, C.c_void_p(y.data_ptr()), self.device.index, n * 8,
+                                   self._stream()))
+        check(self.lib.sn_stream_signal(C.c_void_p(bob + self.box.off_flag_act), self.seq, self._stream()))
+
+    def alice_wait_cut(self):
+        check(self.lib.sn_stream_wait(C.c_void_p(self.base + self.box.off_flag_cut), self.seq, self._stream()))
+        return self.cut
+
+    # ---- Bob side
+    def bob_wait_batch(self):
+        check(self.lib.sn_stream_wait(C.c_void_p(self.base + self.box.off_flag_act), self.seq, self._stream()))
+        return self.act, self.labels
+
+    def bob_cut_target(self, alice_rank):
+        return _Raw(self.peer[alice_rank] + self.box.off_cut, (self.B, D0), self.device)
+
+    def bob_publish_cut(self, alice_rank):
+        check(self.lib.sn_stream_signal(C.c_void_p(self.peer[alice_rank] + self.box.off_flag_cut), self.seq, self._stream()))
+
+    def close(self):
+        torch.cuda.synchronize(self.device)
+        if dist.is_initialized():
+            dist.barrier()
+        with torch.cuda.device(self.device):
+            for p in self.peer.values():
+                self.lib.sn_ipc_close(C.c_void_p(p))
+            self.peer = {}
+            if self.base:
+                self.lib.sn_ipc_free(C.c_void_p(self.base))
+                self.base = 0

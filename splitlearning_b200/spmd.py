@@ -43,11 +43,13 @@ def pack_message(B, device):
 
 
 def run_vanilla_schedule(rank, world, bob, alices, batch_fn, n_alices, turn, first_step, n_steps, B, device,
-                         loss_sink=None):
+                         loss_sink=None, link=None):
     """Walk steps [first_step, first_step+n_steps) of the round-robin schedule.
 
     bob: engine or None (ranks != 0); alices: {alice_index: engine} for the Alices this rank hosts;
-    batch_fn(i) -> (x, y) device tensors for step i (only called on the owning rank)."""
+    batch_fn(i) -> (x, y) device tensors for step i (only called on the owning rank).
+    link: a peer.PeerLink (CUDA IPC mailboxes: the kernels write straight into the consumer's GPU and
+    4-byte flags order the streams) or None for send/recv messages (NCCL; gloo in the CPU tests)."""
     msg, act_view, lab_view = pack_message(B, device)
     cut = torch.empty(B, D0, dtype=torch.float32, device=device)
     wbuf = torch.empty(320, dtype=torch.float32, device=device)
@@ -66,11 +68,22 @@ def run_vanilla_schedule(rank, world, bob, alices, batch_fn, n_alices, turn, fir
                 elif rank == own:
                     dist.recv(wbuf, src=src)
                     alices[k].set_weights(wbuf)
+        if link is not None:
+            link.next_step()
         if world == 1:
             x, y = batch_fn(i)
             act = alices[k].forward(x)
             loss, g, _ = bob.train_step(act, y, slot=k)
             alices[k].backward_update(x, g)
+        elif link is not None and rank == own:
+            x, y = batch_fn(i)
+            alices[k].forward(x, out=link.alice_targets())       # the conv kernel stores into Bob's GPU
+            link.alice_publish(y, x.shape[0])
+            alices[k].backward_update(x, link.alice_wait_cut()[:x.shape[0]])
+        elif link is not None and rank == 0:
+            act, lab = link.bob_wait_batch()
+            loss, g, _ = bob.train_step(act, lab, slot=k, cut_out=link.bob_cut_target(own))   # ... and Bob's last kernel into Alice's
+            link.bob_publish_cut(own)
         elif rank == own:
             x, y = batch_fn(i)
             alices[k].forward(x, out=act_view)
@@ -246,10 +259,10 @@ class _CudaBob:
         self.offset = 0
         self.loss = torch.zeros((), device=device)
 
-    def train_step(self, act, y, slot):
+    def train_step(self, act, y, slot, cut_out=None):
         self.offset += 1
         return self.eng.train_step(act, y, slot=slot, masks=None, seed=1, offset=self.offset, want_cut_grad=True,
-                                   loss_out=self.loss)
+                                   loss_out=self.loss, cut_out=cut_out)
 
 
 def bench_sisa(rank, world, device, B, n_alices):
@@ -309,13 +322,19 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
     hy = torch.randint(0, 10, (nb, B), generator=g)
     xs, ys = (hx.to(device), hy.to(device)) if mine else (None, None)
     K, W = args.steps, args.warmup
+    # transport: peer-memory mailboxes (default) or NCCL send/recv (SN_LINK=nccl, for A/B timing)
+    link = None
+    if os.environ.get("SN_LINK", "peer") != "nccl":
+        from .peer import PeerLink
+        link = PeerLink(rank, world, device, B)
+    config = dict(config, transport="peer-memory mailboxes over NVLink (CUDA IPC, stream flags)" if link else "NCCL send/recv")
 
     def timed(batch_fn, first, sink=None):
         dist.barrier()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        run_vanilla_schedule(rank, world, bob, mine, batch_fn, n_alices, turn, first, K, B, device, sink)
+        run_vanilla_schedule(rank, world, bob, mine, batch_fn, n_alices, turn, first, K, B, device, sink, link)
         e1.record()
         torch.cuda.synchronize()
         dist.barrier()
@@ -323,7 +342,7 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    run_vanilla_schedule(rank, world, bob, mine, lambda i: (xs[i % nb], ys[i % nb]), n_alices, turn, 0, W, B, device)
+    run_vanilla_schedule(rank, world, bob, mine, lambda i: (xs[i % nb], ys[i % nb]), n_alices, turn, 0, W, B, device, None, link)
     l0 = lib.sn_launch_count()
     import bench as bench_mod
     with bench_mod.ClockSampler(local) as clk:
@@ -367,5 +386,7 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
                     "two NVLink messages per step; they cannot add throughput without changing results",
         }
         print(json.dumps(line))
+    if link is not None:
+        link.close()
     dist.barrier()
     dist.destroy_process_group()

@@ -257,6 +257,15 @@ int sn_ipc_close(void* dptr);
 int sn_ipc_free(void* dptr);
 int sn_stream_signal(void* flag, uint32_t value, void* stream);
 int sn_stream_wait(void* flag, uint32_t value, void* stream);
+/* The same two operations as one-CTA gate kernels (ld.acquire.sys polling / st.release.sys), which
+ * is what the multi-GPU schedule uses: a stream-ordered value wait costs ~20 us per hop on this
+ * system, a gate kernel ~3 us, and the launch queued behind a waiting gate overlaps its prologue
+ * with the wait.  The waiter polls memory of its OWN GPU that a kernel on the PEER GPU writes.
+ * sn_flag_signal can first copy `copy_bytes` (a multiple of 8, <= 64 KiB; 0 = none) from
+ * `copy_src` to `copy_dst` (the labels, into the peer's mailbox). */
+int sn_flag_signal(void* flag, uint32_t value, void* copy_dst, const void* copy_src, size_t copy_bytes,
+                   void* stream);
+int sn_flag_wait(const void* flag, uint32_t value, void* stream);
 
 #ifdef __cplusplus
 }

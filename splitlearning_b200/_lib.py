@@ -65,6 +65,8 @@ SIGNATURES = {
     "sn_ipc_free": (_i, [_vp]),
     "sn_stream_signal": (_i, [_vp, C.c_uint32, _vp]),
     "sn_stream_wait": (_i, [_vp, C.c_uint32, _vp]),
+    "sn_flag_signal": (_i, [_vp, C.c_uint32, _vp, _vp, _sz, _vp]),
+    "sn_flag_wait": (_i, [_vp, C.c_uint32, _vp]),
 }
 
 _lib = None

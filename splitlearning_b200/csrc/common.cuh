@@ -119,6 +119,33 @@ __device__ __forceinline__ void pdl_wait() {
 }
 __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// Cross-GPU flags (peer-memory mailboxes, include/splitnn.h): gate kernels of one CTA.  The waiter
+// polls a flag in ITS OWN GPU's memory that a kernel on ANOTHER GPU sets over NVLink, so the two
+// never compete for the same SMs; being PDL launches, the kernel queued behind a waiter runs its
+// prologue (weight prefetch) while the waiter polls.  A stream-ordered cuStreamWaitValue32 pair in
+// the same place costs ~20 us per hop (front-end semaphore latency), these ~3.
+__global__ void flag_wait_kernel(const unsigned* flag, unsigned value) {
+  pdl_wait();
+  pdl_launch();
+  if (threadIdx.x == 0) {
+    unsigned cur;
+    do {
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(cur) : "l"(flag) : "memory");
+    } while ((int)(cur - value) < 0);
+  }
+}
+// optional small copy (labels) into the peer's mailbox, then the flag: everything the stream did
+// before this launch, and the copy, are visible to the peer before it sees the new value
+__global__ void flag_signal_kernel(unsigned* flag, unsigned value, unsigned long long* dst,
+                                   const unsigned long long* src, int words) {
+  pdl_wait();
+  pdl_launch();
+  for (int i = threadIdx.x; i < words; i += blockDim.x) dst[i] = src[i];
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

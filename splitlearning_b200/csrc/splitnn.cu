@@ -1205,6 +1205,24 @@ int sn_ipc_free(void* dptr) {
   return 0;
 }
 
+int sn_flag_signal(void* flag, uint32_t value, void* copy_dst, const void* copy_src, size_t copy_bytes, void* stream) {
+  SN_REQUIRE(flag && (reinterpret_cast<uintptr_t>(flag) & 3) == 0, "sn_flag_signal: flag must be a 4-byte aligned device address");
+  SN_REQUIRE(copy_bytes == 0 || (copy_dst && copy_src && copy_bytes % 8 == 0 && copy_bytes <= 65536 &&
+                                 (reinterpret_cast<uintptr_t>(copy_dst) & 7) == 0 && (reinterpret_cast<uintptr_t>(copy_src) & 7) == 0),
+             "sn_flag_signal: the optional copy must be 8-byte aligned, a multiple of 8 and at most 64 KiB");
+  launch_k(flag_signal_kernel, dim3(1), dim3(128), 0, (cudaStream_t)stream, reinterpret_cast<unsigned*>(flag), (unsigned)value,
+           reinterpret_cast<unsigned long long*>(copy_dst), reinterpret_cast<const unsigned long long*>(copy_src),
+           (int)(copy_bytes / 8));
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+int sn_flag_wait(const void* flag, uint32_t value, void* stream) {
+  SN_REQUIRE(flag && (reinterpret_cast<uintptr_t>(flag) & 3) == 0, "sn_flag_wait: flag must be a 4-byte aligned device address");
+  launch_k(flag_wait_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, reinterpret_cast<const unsigned*>(flag), (unsigned)value);
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+
 typedef CUresult (*StreamValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
 static StreamValue32Fn stream_value_fn(const char* name) {
   void* p = nullptr;

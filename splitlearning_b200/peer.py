@@ -15,8 +15,10 @@ two messages cost ~43 us of a 205 us step although they move 0.7 MB.  Here nothi
     conv backward reads its own mailbox
 
 Every rank owns one mailbox (`sn_ipc_alloc`), maps the peers' (`sn_ipc_open`), and orders the two
-streams with 4-byte flags written/awaited by the streams themselves (`sn_stream_signal/wait`): no
-host synchronisation, no spinning kernels, no collective.  The step counter `s` is the number of
+streams with 4-byte flags: by default one-CTA gate kernels (`sn_flag_signal/wait`: the waiter polls
+its own GPU's memory, ~3 us per hop, and the kernel queued behind it overlaps its prologue with the
+wait), or stream-ordered value ops (`sn_stream_signal/wait`, ~20 us per hop, for comparison).  No
+host synchronisation, no collective.  The step counter `s` is the number of
 steps the link has carried, identical on all ranks because every rank walks the whole schedule.
 """
 import ctypes as C
@@ -72,8 +74,11 @@ class PeerLink:
     """The vanilla schedule's transport over peer memory (see module docstring).  Collective set-up:
     every rank must construct it."""
 
-    def __init__(self, rank, world, device, B):
+    def __init__(self, rank, world, device, B, flags="kernel"):
+        """flags: "kernel" = one-CTA gate kernels (sn_flag_signal/wait, ~3 us per hop), "stream" =
+        stream-ordered value ops (sn_stream_signal/wait, ~20 us per hop; kept for A/B timing)."""
         self.lib = _lib.load()
+        self.kernel_flags = flags == "kernel"
         self.rank, self.world, self.device, self.B = rank, world, device, B
         self.box = Mailbox(B)
         self.seq = 0
@@ -113,24 +118,36 @@ class PeerLink:
 
     def alice_publish(self, y, n):
         bob = self.peer[0]
+        if self.kernel_flags:          # the gate kernel carries the labels too
+            check(self.lib.sn_flag_signal(C.c_void_p(bob + self.box.off_flag_act), self.seq, C.c_void_p(bob + self.box.off_lab),
+                                          C.c_void_p(y.data_ptr()), n * 8, self._stream()))
+            return
         check(self.lib.sn_p2p_copy(C.c_void_p(bob + self.box.off_lab), 0, C.c_void_p(y.data_ptr()), self.device.index, n * 8,
                                    self._stream()))
         check(self.lib.sn_stream_signal(C.c_void_p(bob + self.box.off_flag_act), self.seq, self._stream()))
 
+    def _wait(self, flag):
+        fn = self.lib.sn_flag_wait if self.kernel_flags else self.lib.sn_stream_wait
+        check(fn(C.c_void_p(flag), self.seq, self._stream()))
+
     def alice_wait_cut(self):
-        check(self.lib.sn_stream_wait(C.c_void_p(self.base + self.box.off_flag_cut), self.seq, self._stream()))
+        self._wait(self.base + self.box.off_flag_cut)
         return self.cut
 
     # ---- Bob side
     def bob_wait_batch(self):
-        check(self.lib.sn_stream_wait(C.c_void_p(self.base + self.box.off_flag_act), self.seq, self._stream()))
+        self._wait(self.base + self.box.off_flag_act)
         return self.act, self.labels
 
     def bob_cut_target(self, alice_rank):
         return _Raw(self.peer[alice_rank] + self.box.off_cut, (self.B, D0), self.device)
 
     def bob_publish_cut(self, alice_rank):
-        check(self.lib.sn_stream_signal(C.c_void_p(self.peer[alice_rank] + self.box.off_flag_cut), self.seq, self._stream()))
+        flag = C.c_void_p(self.peer[alice_rank] + self.box.off_flag_cut)
+        if self.kernel_flags:
+            check(self.lib.sn_flag_signal(flag, self.seq, None, None, 0, self._stream()))
+        else:
+            check(self.lib.sn_stream_signal(flag, self.seq, self._stream()))
 
     def close(self):
         torch.cuda.synchronize(self.device)

@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 B, N_ALICES, TURN, STEPS = 16, 3, 4, 26
 
 
-def _run(rank, world, out_dir, port, use_link):
+def _run(rank, world, out_dir, port, use_link, flags="kernel"):
     import torch.distributed as dist
     from splitlearning_b200 import spmd
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -35,7 +35,7 @@ def _run(rank, world, out_dir, port, use_link):
     link = None
     if use_link:
         from splitlearning_b200.peer import PeerLink
-        link = PeerLink(rank, world, device, B)
+        link = PeerLink(rank, world, device, B, flags=flags)
     losses = {}
     spmd.run_vanilla_schedule(rank, world, bob, mine, lambda i: (xs[i], ys[i]), N_ALICES, TURN, 0, STEPS, B, device,
                               lambda i, l: losses.__setitem__(i, l.clone()), link)
@@ -45,7 +45,7 @@ def _run(rank, world, out_dir, port, use_link):
         out["losses"] = np.array([float(losses[i]) for i in range(STEPS)])
         for i, p in enumerate(bob.model.parameters()):
             out[f"bob_p{i}"] = p.detach().cpu().numpy()
-    np.savez(os.path.join(out_dir, f"{'peer' if use_link else 'nccl'}_r{rank}.npz"), **out)
+    np.savez(os.path.join(out_dir, f"{('peer-' + flags) if use_link else 'nccl'}_r{rank}.npz"), **out)
     if link is not None:
         link.close()
     dist.barrier()
@@ -65,9 +65,12 @@ def test_peer_mailboxes_match_nccl_transport():
     import torch.multiprocessing as mp
     with tempfile.TemporaryDirectory() as d:
         mp.spawn(_run, args=(2, d, 29811, False), nprocs=2, join=True)
-        mp.spawn(_run, args=(2, d, 29812, True), nprocs=2, join=True)
-        ref, got = _collect(d, "nccl", 2), _collect(d, "peer", 2)
-    assert set(ref) == set(got) and "losses" in ref and "bob_p0" in ref
-    assert np.isfinite(ref["losses"]).all()
-    for k in ref:
-        assert np.array_equal(ref[k], got[k]), k
+        mp.spawn(_run, args=(2, d, 29812, True, "kernel"), nprocs=2, join=True)
+        mp.spawn(_run, args=(2, d, 29813, True, "stream"), nprocs=2, join=True)
+        ref = _collect(d, "nccl", 2)
+        got = {m: _collect(d, "peer-" + m, 2) for m in ("kernel", "stream")}
+    assert "losses" in ref and "bob_p0" in ref and np.isfinite(ref["losses"]).all()
+    for m, g in got.items():
+        assert set(ref) == set(g), m
+        for k in ref:
+            assert np.array_equal(ref[k], g[k]), (m, k)

@@ -266,7 +266,9 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
     if (set_smem(fwd_skinny_kernel, smem)) return 1;
     dim3 grid(p.nx, p.ksplit, tiles);
     cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
-    launch_k(fwd_skinny_kernel, dim3(grid), dim3(256), smem, st, X, ldx, B, W, K, N, K, p.kc, P, Bpad, p.ksplit, layer > 0 ? 1 : 0, l2_keep_w);
+    // the weight ring starts before the dependency wait unless the previous launch may have written W
+    launch_k(fwd_skinny_kernel, dim3(grid), dim3(256), smem, st, X, ldx, B, W, K, N, K, p.kc, P, Bpad, p.ksplit,
+             (layer > 0 || prefetch_w) ? 1 : 0, l2_keep_w);
     Profiler::end(pe, st);
     SN_LAUNCH_CHECK();
     launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, P, kFwdSlots * p.ksplit, Bpad, B, N, bias, relu, mask,

@@ -3,7 +3,7 @@
 The reference carries each step's cut-layer activations + labels to Bob and the cut-layer gradient
 back through `rpc_sync` / `dist_autograd` on CPU tensors (`data_entities_vanilla.py:63,73,231`).
 `spmd.py`'s first transport replaced that with one NCCL send/recv pair each way; at batch 16 those
-two messages cost ~43 us of a 205 us step although they move 0.7 MB.  Here nothing is "sent":
+two messages cost ~40 us of a 200 us step although they move 0.7 MB.  Here nothing is "sent":
 
     Alice rank (GPU a)                                 Bob rank (GPU 0)
     conv kernel writes act   ----- NVLink stores ----> Bob's mailbox.act
@@ -20,6 +20,12 @@ its own GPU's memory, ~3 us per hop, and the kernel queued behind it overlaps it
 wait), or stream-ordered value ops (`sn_stream_signal/wait`, ~20 us per hop, for comparison).  No
 host synchronisation, no collective.  The step counter `s` is the number of
 steps the link has carried, identical on all ranks because every rank walks the whole schedule.
+
+Measured at 2 GPUs (us per vanilla step; 162 on one GPU): NCCL send/recv 199, stream-ordered flags
+202, gate kernels 178-181.  A third form - the flags folded into the step's own kernels (producers
+signalling from their last CTA after fence.sys, consumers polling with ld.acquire.sys in every CTA) -
+was built, matched bit for bit, and ran at 186: slower than the gates (system-scope fences in
+hundreds of CTAs, and no prologue overlap), so it was dropped.
 """
 import ctypes as C
 

@@ -337,6 +337,17 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
     hy = torch.randint(0, 10, (nb, B), generator=g)
     xs, ys = (hx.to(device), hy.to(device)) if mine else (None, None)
     K, W = args.steps, args.warmup
+    # NCCL opens point-to-point connections lazily (~100 ms each): open the ones the Alice->Alice
+    # weight hand-off will use before anything is timed
+    tiny = torch.zeros(4, device=device)
+    for k in range(n_alices):
+        src, dst = owner_rank(k, world), owner_rank((k + 1) % n_alices, world)
+        if src != dst:
+            if rank == src:
+                dist.send(tiny, dst=dst)
+            elif rank == dst:
+                dist.recv(tiny, src=src)
+    torch.cuda.synchronize()
     # transport: peer-memory mailboxes (default) or NCCL send/recv (SN_LINK=nccl, for A/B timing)
     link = None
     mode = os.environ.get("SN_LINK", "peer")          # peer | peer-stream | nccl

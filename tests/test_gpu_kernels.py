@@ -78,7 +78,9 @@ def test_linear_forward(eng, B, K, N, relu):
     assert rel_err(got, ref * torch.from_numpy(mask) * 2.0) <= 1e-5
 
 
-@pytest.mark.parametrize("B,Cn", [(16, 100), (1, 10), (16, 5408), (37, 100), (300, 10)])
+# row forms: registers (<= 128 classes), one CTA per row (129..6144), streaming warp per row (beyond)
+@pytest.mark.parametrize("B,Cn", [(16, 100), (1, 10), (16, 5408), (37, 100), (300, 10), (16, 128), (5, 129), (3, 6144),
+                                  (2, 6145), (9, 1000)])
 def test_cross_entropy(eng, B, Cn):
     rng = np.random.RandomState(B * 7 + Cn)
     z = (rng.randn(B, Cn) * 8).astype(np.float32)
@@ -96,6 +98,13 @@ def test_cross_entropy(eng, B, Cn):
     l2, g2 = NR.cross_entropy(z, y)
     assert abs(loss.item() - float(l2)) <= 1e-4 * abs(float(l2))
     assert rel_err(dz.cpu(), g2) <= 1e-4     # numpy's fp32 exp rounds differently where p-1 cancels
+    # ties: the first maximum is the one left out of the log1p sum (torch's argmax convention)
+    zt2 = z.copy()
+    zt2[0, :] = -3.0
+    zt2[0, [Cn // 3, Cn - 1]] = 5.0
+    loss2, _ = eng.cross_entropy(cu(zt2), cu(y))
+    ref2 = torch.nn.functional.cross_entropy(torch.from_numpy(zt2).double(), torch.from_numpy(y)).item()
+    assert abs(loss2.item() - ref2) <= 1e-5 * abs(ref2)
 
 
 def test_eval_counts_exact(eng):

@@ -15,7 +15,7 @@ import torch
 
 from splitlearning_b200 import _lib
 
-_lib.LIB_PATH = os.path.join(HERE, "libsplitnn_trace.so")
+_lib.LIB_PATH = os.environ.get("SN_TRACE_LIB", os.path.join(HERE, "libsplitnn_trace.so"))
 import bench
 from splitlearning_b200 import engine as E
 

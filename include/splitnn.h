@@ -266,6 +266,38 @@ int sn_stream_wait(void* flag, uint32_t value, void* stream);
 int sn_flag_signal(void* flag, uint32_t value, void* copy_dst, const void* copy_src, size_t copy_bytes,
                    void* stream);
 int sn_flag_wait(const void* flag, uint32_t value, void* stream);
+/* One gate launch that waits for `count` (<= 32) flags, `stride_bytes` apart, all to reach `value`
+ * (the head GPU waiting for every shard's slice). */
+int sn_flag_wait_many(const void* flags, int count, int stride_bytes, uint32_t value, void* stream);
+
+/* ------------------------------------------------------------------ tensor-parallel first layer
+ * the server step is a weight stream, and the first layer is 84 % of it, so its
+ * rows are split over G GPUs: each GPU streams 1/G of W1 and of its optimizer state.  An sn_shard is
+ * rows [n_off, n_off+n_rows) of a [n_total, K] Linear (+ReLU, dropout) with that slice's optimizer
+ * state; it borrows W_slice [n_rows,K] and b_slice [n_rows] (updated in place), batch <= 16.
+ *   sn_shard_forward          H_out[b*ld_out + n_off + j] = dropout(relu(X W_slice^T + b))  -  H_out is
+ *                             the FULL-width activation [B, n_total], normally a peer pointer into the
+ *                             head GPU's mailbox; the dropout decision of an element is that of the
+ *                             unsharded layer (mask bytes [B,n_total] or Philox on the global index).
+ *   sn_shard_backward_update  dH [B, n_total] (row stride ld_dh; normally read from the head GPU over
+ *                             NVLink) is the gradient w.r.t. the layer's OUTPUT as the head's
+ *                             backward returns it (its cut gradient, not yet gated); the slice gates
+ *                             it with its own activation, forms dW, updates W/b and the optimizer
+ *                             state in one traversal, and - when X_next is given (SISA: the next
+ *                             cached batch) - also multiplies the next batch through the updated
+ *                             rows, so the following sn_shard_forward is only an epilogue.
+ * No input gradient is produced (SISA server epochs detach the cached activations,
+ * data_entities_vanilla_sisa.py:307).  No counterpart in the reference (one CPU process per role). */
+typedef struct sn_shard sn_shard;
+int sn_shard_create(sn_shard** out, int device, int K, int n_total, int n_off, int n_rows, int relu,
+                    double dropout_p, int optimizer, double lr, double momentum, double beta1,
+                    double beta2, double eps, double weight_decay, float* W_slice, float* b_slice);
+int sn_shard_destroy(sn_shard* h);
+int sn_shard_reset_opt(sn_shard* h, void* stream);
+int sn_shard_forward(sn_shard* h, const float* X, int B, int train_mode, const uint8_t* keep_mask,
+                     uint64_t seed, uint64_t offset, float* H_out, int ld_out, void* stream);
+int sn_shard_backward_update(sn_shard* h, const float* X, const float* dH, int ld_dh, int B,
+                             const float* X_next, int B_next, void* stream);
 
 #ifdef __cplusplus
 }

@@ -67,6 +67,12 @@ SIGNATURES = {
     "sn_stream_wait": (_i, [_vp, C.c_uint32, _vp]),
     "sn_flag_signal": (_i, [_vp, C.c_uint32, _vp, _vp, _sz, _vp]),
     "sn_flag_wait": (_i, [_vp, C.c_uint32, _vp]),
+    "sn_flag_wait_many": (_i, [_vp, _i, _i, C.c_uint32, _vp]),
+    "sn_shard_create": (_i, [_pp, _i, _i, _i, _i, _i, _i, _d, _i, _d, _d, _d, _d, _d, _d, _vp, _vp]),
+    "sn_shard_destroy": (_i, [_vp]),
+    "sn_shard_reset_opt": (_i, [_vp, _vp]),
+    "sn_shard_forward": (_i, [_vp, _vp, _i, _i, _vp, _u64, _u64, _vp, _i, _vp]),
+    "sn_shard_backward_update": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i, _vp]),
 }
 
 _lib = None

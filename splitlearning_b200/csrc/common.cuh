@@ -124,13 +124,15 @@ __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.laun
 // never compete for the same SMs; being PDL launches, the kernel queued behind a waiter runs its
 // prologue (weight prefetch) while the waiter polls.  A stream-ordered cuStreamWaitValue32 pair in
 // the same place costs ~20 us per hop (front-end semaphore latency), these ~3.
-__global__ void flag_wait_kernel(const unsigned* flag, unsigned value) {
+// thread i < count polls flag[i * stride_words]: one launch can wait for `count` producers
+__global__ void flag_wait_kernel(const unsigned* flag, unsigned value, int count, int stride_words) {
   pdl_wait();
   pdl_launch();
-  if (threadIdx.x == 0) {
+  if ((int)threadIdx.x < count) {
+    const unsigned* f = flag + (size_t)threadIdx.x * stride_words;
     unsigned cur;
     do {
-      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(cur) : "l"(flag) : "memory");
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(cur) : "l"(f) : "memory");
     } while ((int)(cur - value) < 0);
   }
 }

@@ -291,12 +291,16 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
 __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int Bpad, int B, int N,
                                     const float* __restrict__ bias, int relu, const uint8_t* __restrict__ mask,
                                     float keep_prob, float scale, uint64_t seed, uint64_t offset, int layer,
-                                    float* __restrict__ H, int ldh, float* __restrict__ out2) {
+                                    float* __restrict__ H, int ldh, float* __restrict__ out2, int idx_ld, int idx_off) {
+  // idx_ld > 0: this launch computes rows [idx_off, idx_off+N) of a layer that is idx_ld rows wide
+  // (a tensor-parallel shard): the dropout decision of an element must not depend on the sharding,
+  // so the mask / Philox index is the element's index in the FULL [B, idx_ld] activation.
   pdl_wait();
   pdl_launch();
   const size_t total = (size_t)B * N;
   for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
     const int b = (int)(idx / N), n = (int)(idx - (size_t)b * N);
+    const size_t gidx = idx_ld > 0 ? (size_t)b * idx_ld + idx_off + n : idx;
     const float bn = bias[n];                    // requested before the partials, not after them
     float s = 0.f;
     const float* pp = P + (size_t)b * N + n;
@@ -311,9 +315,9 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
     s += bn;
     if (relu) s = fmaxf(s, 0.f);
     if (mask) {
-      s = mask[idx] ? s * scale : 0.f;
+      s = mask[gidx] ? s * scale : 0.f;
     } else if (keep_prob < 1.f) {
-      s = philox_keep(seed, offset, layer, idx, keep_prob) ? s * scale : 0.f;
+      s = philox_keep(seed, offset, layer, gidx, keep_prob) ? s * scale : 0.f;
     }
     H[(size_t)b * ldh + n] = s;
     if (out2) out2[idx] = s;
@@ -772,7 +776,11 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
                   float* __restrict__ s2, float* __restrict__ bs1, float* __restrict__ bs2,
                   const float* __restrict__ dZ, int ldz, const float* __restrict__ A, int lda, int B,
                   float* __restrict__ PA, int kw, int rows_per_cta, OptParams op,
-                  const float* __restrict__ Xn, int Bn, float* __restrict__ PF, int l2_keep_w) {
+                  const float* __restrict__ Xn, int Bn, float* __restrict__ PF, int l2_keep_w,
+                  const float* __restrict__ gate, float gscale) {
+  // gate != nullptr (tensor-parallel shard): dZ arrives UNGATED (it is the head GPU's cut gradient
+  // w.r.t. this layer's output); the ReLU/dropout gate is this shard's own dense activation
+  // gate[b][N]: dZ <- dZ * (gate > 0 ? gscale : 0), applied while the tile is staged.
   extern __shared__ float4 smem4[];
   // rows below l2_keep_w: weights tagged evict_last, their optimizer state evict_first
   const uint64_t pol_keep = l2_policy(1), pol_norm = l2_policy(0), pol_s = l2_policy(l2_keep_w ? 2 : 0);
@@ -812,6 +820,7 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
         const int idx = base_idx + q * 256;
         const int b = idx / nrows, j = idx - b * nrows;
         v[q] = (idx < total && b < B) ? __ldg(dZ + (size_t)b * ldz + nb0 + j) : 0.f;
+        if (gate && idx < total && b < B) v[q] = __ldg(gate + (size_t)b * N + nb0 + j) > 0.f ? v[q] * gscale : 0.f;
       }
 #pragma unroll
       for (int q = 0; q < SB; ++q) {

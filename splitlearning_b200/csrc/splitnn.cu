@@ -257,7 +257,7 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
     Profiler::end(pe, st);
     SN_LAUNCH_CHECK();
     launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, P, p.qmax, kBT, B, N, bias, relu, mask, keep_prob,
-             scale, seed, offset, layer, H, ldh, out2);
+             scale, seed, offset, layer, H, ldh, out2, 0, 0);
     SN_LAUNCH_CHECK();
   } else if (B <= kSkinnyFwdMaxB && (K % 4) == 0) {
     FwdPlan p = plan_fwd(K, N, sms);
@@ -272,7 +272,7 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
     Profiler::end(pe, st);
     SN_LAUNCH_CHECK();
     launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, P, kFwdSlots * p.ksplit, Bpad, B, N, bias, relu, mask,
-                                                                    keep_prob, scale, seed, offset, layer, H, ldh, out2);
+                                                                    keep_prob, scale, seed, offset, layer, H, ldh, out2, 0, 0);
     SN_LAUNCH_CHECK();
   } else if (g_matmul_precision.load() != 2 && tc::usable(X, ldx, W, K, K)) {
     // tensor-bound regime: tcgen05 TF32 GEMM with the bias / ReLU / dropout epilogue fused
@@ -289,7 +289,7 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
     SN_LAUNCH_CHECK();
     SN_REQUIRE(ldh == N, "general-batch forward needs a dense output");
     launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, H, 1, 0, B, N, bias, relu, mask, keep_prob,
-                                                                    scale, seed, offset, layer, H, ldh, out2);
+                                                                    scale, seed, offset, layer, H, ldh, out2, 0, 0);
     SN_LAUNCH_CHECK();
   }
   return 0;
@@ -351,6 +351,22 @@ struct sn_alice {
   float* row_loss = nullptr;
   int gx = 1;
   bool bwd_last = false;                // the last launch on this handle was the weight update
+};
+
+// One row slice of a Linear layer with its optimizer state: the unit of the tensor-parallel first
+// layer (include/splitnn.h, sn_shard_*).
+struct sn_shard {
+  int device = 0, K = 0, n_total = 0, n_off = 0, n_rows = 0, relu = 1, max_batch = 16, sms = 148;
+  float dropout_p = 0.f;
+  Hyper hyper;
+  int64_t step = 0;
+  float *W = nullptr, *b = nullptr;
+  float *s1 = nullptr, *s2 = nullptr, *bs1 = nullptr, *bs2 = nullptr;
+  float* P = nullptr;        // forward split-K partials
+  float* PF = nullptr;       // fused next-forward partials [k slices][16][n_rows]
+  float* Hloc = nullptr;     // dense copy of the slice's activation [16][n_rows] (the backward's gate)
+  bool pf_valid = false, h_valid = false;
+  int l2_keep = 0;
 };
 
 static int conv_bwd_gx(int B, int sms) { return std::max(1, std::min(B, sms * 2)); }
@@ -725,7 +741,7 @@ static int bob_forward_impl(sn_bob* h, const float* act, int B, int train, const
       // layer 0 of this step was already multiplied out by the previous step's fused traversal
       h->pf_valid = false;
       launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, h->sms)), dim3(256), 0, st, h->PF, ceil_div(K, 128), kBT, B, N,
-               h->b[l], relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N, last ? out : nullptr);
+               h->b[l], relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N, last ? out : nullptr, 0, 0);
       SN_LAUNCH_CHECK();
       h->last_writer = -1;
     } else if (launch_linear_fwd(X, ldx, B, h->W[l], h->b[l], K, N, relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N,
@@ -777,7 +793,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         launch_k(bwd_update_kernel<OPT, true>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
                                                               s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, h->PA,
                                                               p.kw, p.rows_per_cta, op, (const float*)nullptr, 0, (float*)nullptr,
-                                                              h->l2_keep[l]);
+                                                              h->l2_keep[l], (const float*)nullptr, 1.f);
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
         launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, p.nsplit, B, K, gateH, K,
@@ -791,7 +807,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         cudaEvent_t pe = h->prof.begin(st, 1, l);
         launch_k(bwd_update_kernel<OPT, false, true>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, h->b[l],
                  s.s1[2 * l], s.s2[2 * l], s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, h->PA, p.kw, p.rows_per_cta, op,
-                 next_act, next_B, h->PF, h->l2_keep[l]);
+                 next_act, next_B, h->PF, h->l2_keep[l], (const float*)nullptr, 1.f);
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
         h->pf_valid = true;
@@ -801,7 +817,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         launch_k(bwd_update_kernel<OPT, false>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
                                                                s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B,
                                                                h->PA, p.kw, p.rows_per_cta, op, (const float*)nullptr, 0, (float*)nullptr,
-                                                               h->l2_keep[l]);
+                                                               h->l2_keep[l], (const float*)nullptr, 1.f);
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
       }
@@ -1172,6 +1188,149 @@ int sn_p2p_copy(void* dst, int dst_device, const void* src, int src_device, size
   return 0;
 }
 
+// ------------------------------------------------------------------ tensor-parallel layer slices
+#define SN_SHARD_ENTER(h)                                              \
+  SN_REQUIRE((h) != nullptr, "null sn_shard handle");                  \
+  SN_CUDA(cudaSetDevice((h)->device))
+
+int sn_shard_destroy(sn_shard* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaFree(h->s1); cudaFree(h->s2); cudaFree(h->bs1); cudaFree(h->bs2);
+  cudaFree(h->P); cudaFree(h->PF); cudaFree(h->Hloc);
+  delete h;
+  return 0;
+}
+
+int sn_shard_create(sn_shard** out, int device, int K, int n_total, int n_off, int n_rows, int relu, double dropout_p,
+                    int optimizer, double lr, double momentum, double beta1, double beta2, double eps,
+                    double weight_decay, float* W_slice, float* b_slice) {
+  SN_REQUIRE(out && W_slice && b_slice, "sn_shard_create: bad arguments");
+  SN_REQUIRE(K > 0 && (K % 4) == 0 && n_rows > 0 && n_off >= 0 && n_off + n_rows <= n_total,
+             "sn_shard_create: need K % 4 == 0 and 0 <= n_off, n_off + n_rows <= n_total");
+  SN_REQUIRE((size_t)n_rows * K > kSmallLayerElems, "sn_shard_create: the slice is too small to be worth a GPU (<= 1 MB of weights)");
+  SN_REQUIRE(optimizer == SN_OPT_SGD_MOMENTUM || optimizer == SN_OPT_ADAM, "sn_shard_create: optimizer must be SGD-momentum or Adam");
+  SN_REQUIRE(dropout_p >= 0.0 && dropout_p < 1.0, "sn_shard_create: dropout_p must be in [0,1)");
+  int ndev = 0;
+  SN_CUDA(cudaGetDeviceCount(&ndev));
+  SN_REQUIRE(device >= 0 && device < ndev, "sn_shard_create: no such CUDA device");
+  SN_CUDA(cudaSetDevice(device));
+  sn_shard* h = new sn_shard();
+  h->device = device; h->K = K; h->n_total = n_total; h->n_off = n_off; h->n_rows = n_rows; h->relu = relu;
+  h->dropout_p = (float)dropout_p;
+  h->hyper.type = optimizer; h->hyper.lr = lr; h->hyper.momentum = momentum; h->hyper.beta1 = beta1;
+  h->hyper.beta2 = beta2; h->hyper.eps = eps; h->hyper.wd = weight_decay;
+  h->sms = sm_count(device);
+  h->W = W_slice; h->b = b_slice;
+  const size_t nw = (size_t)n_rows * K;
+  cudaError_t e = cudaSuccess;
+  auto alloc0 = [&](float** p, size_t n) {
+    if (e == cudaSuccess) e = cudaMalloc(p, n * 4);
+    if (e == cudaSuccess) e = cudaMemset(*p, 0, n * 4);
+  };
+  alloc0(&h->s1, nw); alloc0(&h->bs1, n_rows);
+  if (optimizer == SN_OPT_ADAM) { alloc0(&h->s2, nw); alloc0(&h->bs2, n_rows); }
+  alloc0(&h->P, std::max<size_t>(16, fwd_partial_floats(kBT, K, n_rows, h->sms)));
+  alloc0(&h->PF, (size_t)ceil_div(K, 128) * kBT * n_rows);
+  alloc0(&h->Hloc, (size_t)kBT * n_rows);
+  if (e != cudaSuccess) { sn_shard_destroy(h); return fail("sn_shard_create", e, __FILE__, __LINE__); }
+  size_t carve = 0;
+  if (cudaDeviceGetLimit(&carve, cudaLimitPersistingL2CacheSize) != cudaSuccess) { carve = 0; cudaGetLastError(); }
+  const char* env = getenv("SN_L2_KEEP_MB");
+  const double keep_mb = env ? atof(env) : 0.95 * (double)carve / (1 << 20);
+  h->l2_keep = (int)std::min<double>(n_rows, keep_mb / (K * 4.0 / (1 << 20)));
+  *out = h;
+  return 0;
+}
+
+int sn_shard_reset_opt(sn_shard* h, void* stream) {
+  SN_SHARD_ENTER(h);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t nw = (size_t)h->n_rows * h->K;
+  SN_CUDA(cudaMemsetAsync(h->s1, 0, nw * 4, st));
+  SN_CUDA(cudaMemsetAsync(h->bs1, 0, (size_t)h->n_rows * 4, st));
+  if (h->s2) {
+    SN_CUDA(cudaMemsetAsync(h->s2, 0, nw * 4, st));
+    SN_CUDA(cudaMemsetAsync(h->bs2, 0, (size_t)h->n_rows * 4, st));
+  }
+  h->step = 0;
+  h->pf_valid = false;
+  return 0;
+}
+
+int sn_shard_forward(sn_shard* h, const float* X, int B, int train_mode, const uint8_t* keep_mask, uint64_t seed,
+                     uint64_t offset, float* H_out, int ld_out, void* stream) {
+  SN_SHARD_ENTER(h);
+  SN_REQUIRE(X && H_out && B > 0 && B <= kBT && ld_out >= h->n_off + h->n_rows, "sn_shard_forward: bad arguments (B <= 16)");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int K = h->K, N = h->n_rows;
+  const bool drop = train_mode && h->dropout_p > 0.f;
+  const float keep = 1.f - h->dropout_p, scale = 1.f / keep;
+  const uint8_t* mask = drop ? keep_mask : nullptr;
+  const float kp = (drop && !keep_mask) ? keep : 1.f;
+  const float* P = h->P;
+  int nparts = 0;
+  if (h->pf_valid) {                 // the previous backward traversal already multiplied this batch out
+    P = h->PF;
+    nparts = ceil_div(K, 128);
+    h->pf_valid = false;
+  } else {
+    FwdPlan p = plan_fwd(K, N, h->sms);
+    size_t smem = (size_t)kBT * p.kc * 4 + (size_t)8 * kFwdRing * 8 * 32 * 16;
+    if (set_smem(fwd_skinny_kernel, smem)) return 1;
+    launch_k(fwd_skinny_kernel, dim3(p.nx, p.ksplit, 1), dim3(256), smem, st, X, K, B, h->W, K, N, K, p.kc, h->P, kBT, p.ksplit, 0,
+             h->l2_keep);
+    SN_LAUNCH_CHECK();
+    nparts = kFwdSlots * p.ksplit;
+  }
+  launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, h->sms)), dim3(256), 0, st, P, nparts, kBT, B, N, h->b, h->relu, mask, kp,
+           scale, seed, offset, 0, H_out + h->n_off, ld_out, h->Hloc, h->n_total, h->n_off);
+  SN_LAUNCH_CHECK();
+  h->h_valid = train_mode != 0;
+  return 0;
+}
+
+}  // extern "C" (templates need C++ linkage)
+template <int OPT>
+static int shard_backward_impl(sn_shard* h, const float* X, const float* dH, int ld_dh, int B, const float* X_next,
+                               int B_next, cudaStream_t st) {
+  h->step += 1;
+  const OptParams op = make_opt(h->hyper, h->step);
+  const int K = h->K, N = h->n_rows;
+  const float gscale = h->dropout_p > 0.f ? 1.f / (1.f - h->dropout_p) : 1.f;
+  BwdPlan p = plan_bwd(N, K, h->sms, false, OPT == 2);
+  size_t smem = bwd_smem_bytes(p, false, OPT == 2);
+  dim3 grid(p.kgroups, p.nsplit);
+  const float* dZ = dH + h->n_off;
+  if (X_next && B_next > 0) {
+    if (set_smem(bwd_update_kernel<OPT, false, true>, smem)) return 1;
+    launch_k(bwd_update_kernel<OPT, false, true>, dim3(grid), dim3(256), smem, st, h->W, K, N, K, h->b, h->s1, h->s2, h->bs1, h->bs2,
+             dZ, ld_dh, X, K, B, (float*)nullptr, p.kw, p.rows_per_cta, op, X_next, B_next, h->PF, h->l2_keep,
+             (const float*)h->Hloc, gscale);
+    h->pf_valid = true;
+  } else {
+    if (set_smem(bwd_update_kernel<OPT, false, false>, smem)) return 1;
+    launch_k(bwd_update_kernel<OPT, false, false>, dim3(grid), dim3(256), smem, st, h->W, K, N, K, h->b, h->s1, h->s2, h->bs1, h->bs2,
+             dZ, ld_dh, X, K, B, (float*)nullptr, p.kw, p.rows_per_cta, op, (const float*)nullptr, 0, (float*)nullptr,
+             h->l2_keep, (const float*)h->Hloc, gscale);
+    h->pf_valid = false;
+  }
+  SN_LAUNCH_CHECK();
+  h->h_valid = false;
+  return 0;
+}
+extern "C" {
+
+int sn_shard_backward_update(sn_shard* h, const float* X, const float* dH, int ld_dh, int B, const float* X_next,
+                             int B_next, void* stream) {
+  SN_SHARD_ENTER(h);
+  SN_REQUIRE(X && dH && B > 0 && B <= kBT && ld_dh >= h->n_off + h->n_rows, "sn_shard_backward_update: bad arguments (B <= 16)");
+  SN_REQUIRE(h->h_valid, "sn_shard_backward_update: no matching train-mode sn_shard_forward");
+  SN_REQUIRE(!X_next || (B_next > 0 && B_next <= kBT), "sn_shard_backward_update: bad next batch");
+  if (h->hyper.type == SN_OPT_ADAM) return shard_backward_impl<2>(h, X, dH, ld_dh, B, X_next, B_next, (cudaStream_t)stream);
+  return shard_backward_impl<1>(h, X, dH, ld_dh, B, X_next, B_next, (cudaStream_t)stream);
+}
+
 // ------------------------------------------------------------------ peer-memory mailboxes
 int sn_ipc_alloc(size_t bytes, void** dptr, void* handle64) {
   SN_REQUIRE(bytes > 0 && dptr && handle64, "sn_ipc_alloc: bad arguments");
@@ -1220,7 +1379,16 @@ int sn_flag_signal(void* flag, uint32_t value, void* copy_dst, const void* copy_
 }
 int sn_flag_wait(const void* flag, uint32_t value, void* stream) {
   SN_REQUIRE(flag && (reinterpret_cast<uintptr_t>(flag) & 3) == 0, "sn_flag_wait: flag must be a 4-byte aligned device address");
-  launch_k(flag_wait_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, reinterpret_cast<const unsigned*>(flag), (unsigned)value);
+  launch_k(flag_wait_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, reinterpret_cast<const unsigned*>(flag), (unsigned)value, 1, 0);
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+int sn_flag_wait_many(const void* flags, int count, int stride_bytes, uint32_t value, void* stream) {
+  SN_REQUIRE(flags && (reinterpret_cast<uintptr_t>(flags) & 3) == 0 && count >= 1 && count <= 32 && stride_bytes >= 4 &&
+                 (stride_bytes & 3) == 0,
+             "sn_flag_wait_many: 1..32 flags, 4-byte aligned, stride a multiple of 4 bytes");
+  launch_k(flag_wait_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, reinterpret_cast<const unsigned*>(flags), (unsigned)value,
+           count, stride_bytes / 4);
   SN_LAUNCH_CHECK();
   return 0;
 }

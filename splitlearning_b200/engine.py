@@ -150,6 +150,47 @@ class BobEngine:
         check(self.lib.sn_bob_set_ce_heads(self.h, int(heads)))
 
 
+class ShardEngine:
+    """`sn_shard`: rows [n_off, n_off+n_rows) of a Linear(+ReLU, dropout) layer with that slice's
+    optimizer state - the unit of the tensor-parallel first layer (tp.py).  Borrows `W_slice`
+    [n_rows,K] and `b_slice` [n_rows] (updated in place)."""
+
+    def __init__(self, W_slice, b_slice, n_total, n_off, *, relu=True, dropout_p=0.5, optimizer=SN_OPT_ADAM, lr=1e-3,
+                 momentum=0.0, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+        self.lib = _lib.load()
+        self.W, self.b = _f32c(W_slice), _f32c(b_slice)
+        self.device = W_slice.device
+        self.n_rows, self.K = W_slice.shape
+        self.n_total, self.n_off = int(n_total), int(n_off)
+        h = C.c_void_p()
+        dev = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        check(self.lib.sn_shard_create(C.byref(h), dev, self.K, self.n_total, self.n_off, self.n_rows, int(bool(relu)),
+                                       float(dropout_p), *_opt_args(optimizer, lr, momentum, betas, eps, weight_decay),
+                                       ptr(self.W), ptr(self.b)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.sn_shard_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def forward(self, X, H_out, ld_out, train=True, mask=None, seed=0, offset=0):
+        """`H_out`: the full-width [B, n_total] activation (tensor or raw peer address holder)."""
+        _f32c(X)
+        check(self.lib.sn_shard_forward(self.h, ptr(X), X.shape[0], int(bool(train)), ptr(mask), int(seed), int(offset),
+                                        ptr(H_out), int(ld_out), _stream(self.device)))
+
+    def backward_update(self, X, dH, ld_dh, X_next=None):
+        _f32c(X)
+        check(self.lib.sn_shard_backward_update(self.h, ptr(X), ptr(dH), int(ld_dh), X.shape[0], ptr(X_next),
+                                                0 if X_next is None else X_next.shape[0], _stream(self.device)))
+
+    def reset_opt(self):
+        check(self.lib.sn_shard_reset_opt(self.h, _stream(self.device)))
+
+
 class AliceEngine:
     """`sn_alice`: the client conv block bound to caller-owned conv weight/bias tensors."""
 

@@ -269,6 +269,9 @@ int sn_flag_wait(const void* flag, uint32_t value, void* stream);
 /* One gate launch that waits for `count` (<= 32) flags, `stride_bytes` apart, all to reach `value`
  * (the head GPU waiting for every shard's slice). */
 int sn_flag_wait_many(const void* flags, int count, int stride_bytes, uint32_t value, void* stream);
+/* One gate launch that sets `count` (<= 128) flags whose addresses are in a DEVICE array (one flag
+ * in each consumer's own memory). */
+int sn_flag_signal_many(const void* flag_table_dev, int count, uint32_t value, void* stream);
 
 /* ------------------------------------------------------------------ tensor-parallel first layer
  * the server step is a weight stream, and the first layer is 84 % of it, so its
@@ -298,6 +301,24 @@ int sn_shard_forward(sn_shard* h, const float* X, int B, int train_mode, const u
                      uint64_t seed, uint64_t offset, float* H_out, int ld_out, void* stream);
 int sn_shard_backward_update(sn_shard* h, const float* X, const float* dH, int ld_dh, int B,
                              const float* X_next, int B_next, void* stream);
+/* One pass over cached batches (HOST batch_offsets[n_batches+1], batches of <= 16 rows) with the first
+ * layer sharded over `world` ranks: the tensor-parallel form of sn_bob_server_epoch, i.e. of the
+ * epoch body of bob.train_and_backward, data_entities_vanilla_sisa.py:298-313.  Every rank calls it
+ * with its shard and the same cache (replicated); rank 0 also passes `head` (an sn_bob over the
+ * remaining layers, input width = the sharded layer's width) and the labels.  H1 is the [16, n_total]
+ * activation buffer in rank 0's mailbox (a peer pointer elsewhere) and h_ready_flags the base of the
+ * per-rank flags next to it (rank r's at +128*r bytes); dH1 [16, n_total] and dh_ready_flag are THIS
+ * rank's own gradient buffer and flag.  Rank 0 also passes two DEVICE arrays: dH1_table_dev[world]
+ * (every rank's dH1 buffer - the head pushes rank r's column range into dH1_table_dev[r]) and
+ * dh_flag_table_dev[world-1] (the dh_ready flags of ranks 1..world-1).  Flag values used are
+ * seq0+1 .. seq0+n_batches.  drop_masks: nullable [first layer (n,n_total),
+ * then the head's layers] keep bytes; otherwise Philox keyed by (seed, offset + step). */
+int sn_tp_server_epoch(sn_shard* shard, sn_bob* head, int rank, int world, const float* cache,
+                       const int64_t* labels, const int64_t* batch_offsets, int n_batches,
+                       const uint8_t* const* drop_masks, uint64_t seed, uint64_t offset, float* H1,
+                       float* dH1, void* h_ready_flags, void* dh_ready_flag,
+                       float* const* dH1_table_dev, const void* dh_flag_table_dev, uint32_t seq0,
+                       float* loss_per_step, void* stream);
 
 #ifdef __cplusplus
 }

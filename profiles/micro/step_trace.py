@@ -3,7 +3,8 @@
 in which CTA 0 of each kernel stamps %globaltimer right after its PDL dependency wait (= when the
 previous kernel has completed).  Differences of consecutive stamps are what each kernel costs the
 step with launch overlap as it really is - ncu serialises launches and cannot show that.
-usage: python profiles/micro/step_trace.py [vanilla|sisa|local]"""
+usage: python profiles/micro/step_trace.py [vanilla|sisa|local]
+       python -m torch.distributed.run --nproc-per-node G ... profiles/micro/step_trace.py tp   (tensor-parallel SISA steps)"""
 import ctypes as C
 import os
 import sys
@@ -35,6 +36,39 @@ def read_trace():
     return buf[:min(n.value, 8192)].astype(np.int64)
 
 
+if mode == "tp":
+    import torch.distributed as dist
+    from splitlearning_b200 import models as M, tp
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank)))
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    torch.manual_seed(1)
+    model = M.model2_sisa(dev)
+    srv = tp.TPServer(rank, world, dev, [model.fc1.weight.data, model.fc2.weight.data, model.fc3.weight.data],
+                      [model.fc1.bias.data, model.fc2.bias.data, model.fc3.bias.data], B=B)
+    nbat = 140
+    g = torch.Generator().manual_seed(3)
+    acts = torch.rand(nbat * B, D0, generator=g).to(dev)
+    labels = torch.randint(0, 10, (nbat * B,), generator=g).to(dev)
+    offs = list(range(0, nbat * B + 1, B))
+    srv.server_epoch(acts, labels, offs)
+    torch.cuda.synchronize(); dist.barrier()
+    read_trace()
+    srv.server_epoch(acts, labels, offs)
+    torch.cuda.synchronize(); dist.barrier()
+    t = read_trace()
+    L = len(t) // nbat
+    d = np.diff(t[: (len(t) // L) * L])
+    d = d[: (len(d) // L) * L].reshape(-1, L)[5:-2]
+    med = np.median(d, axis=0) / 1e3
+    for r in range(world):
+        if r == rank:
+            print(f"rank {rank}: {L} launches/step, step {med.sum():.1f} us:", " ".join(f"{m:.1f}" for m in med), flush=True)
+        dist.barrier()
+    srv.close()
+    dist.destroy_process_group()
+    sys.exit(0)
 if mode == "vanilla":
     bob_model, bob, alices = bench.make_world(torch, dev)
     xs, ys = bench.synthetic_batches(torch, 64, dev)

@@ -73,6 +73,9 @@ SIGNATURES = {
     "sn_shard_reset_opt": (_i, [_vp, _vp]),
     "sn_shard_forward": (_i, [_vp, _vp, _i, _i, _vp, _u64, _u64, _vp, _i, _vp]),
     "sn_shard_backward_update": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i, _vp]),
+    "sn_tp_server_epoch": (_i, [_vp, _vp, _i, _i, _vp, _vp, C.POINTER(_i64), _i, _pp, _u64, _u64, _vp, _vp, _vp, _vp,
+                                _vp, _vp, C.c_uint32, _vp, _vp]),
+    "sn_flag_signal_many": (_i, [_vp, _i, C.c_uint32, _vp]),
 }
 
 _lib = None

@@ -139,13 +139,16 @@ __global__ void flag_wait_kernel(const unsigned* flag, unsigned value, int count
 // optional small copy (labels) into the peer's mailbox, then the flag: everything the stream did
 // before this launch, and the copy, are visible to the peer before it sees the new value
 __global__ void flag_signal_kernel(unsigned* flag, unsigned value, unsigned long long* dst,
-                                   const unsigned long long* src, int words) {
+                                   const unsigned long long* src, int words, unsigned* const* flag_table, int nflags) {
   pdl_wait();
   pdl_launch();
   for (int i = threadIdx.x; i < words; i += blockDim.x) dst[i] = src[i];
   __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+  if (threadIdx.x == 0 && flag) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+  // several consumers (one flag in each one's own memory): thread i releases flag_table[i]
+  if ((int)threadIdx.x < nflags)
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag_table[threadIdx.x]), "r"(value) : "memory");
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

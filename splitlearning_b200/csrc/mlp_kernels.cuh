@@ -1075,9 +1075,11 @@ bwd_small_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict
 
 // dst[b][k] = (sum_s PA[s][b][k]) * gate, gate = (H[b][k] > 0 ? scale : 0) for hidden layers
 // (H is the post-ReLU, post-dropout activation so H>0 <=> ReLU active and kept), 1 at the cut.
+// dst_table != nullptr (tensor-parallel head): column k goes to dst_table[k / cols_per_dst] instead of
+// dst - each consumer GPU gets its column range pushed into its own memory over NVLink.
 __global__ void bwd_epilogue_kernel(const float* __restrict__ PA, int nsplit, int B, int K,
                                     const float* __restrict__ H, int ldh, float scale, float* __restrict__ dst,
-                                    int ldd) {
+                                    int ldd, float* const* __restrict__ dst_table, int cols_per_dst) {
   pdl_wait();
   pdl_launch();
   const size_t total = (size_t)B * K;
@@ -1095,7 +1097,8 @@ __global__ void bwd_epilogue_kernel(const float* __restrict__ PA, int nsplit, in
     }
     for (; p < nsplit; ++p) s += pp[(size_t)p * pstride];
     if (H) s = hv > 0.f ? s * scale : 0.f;
-    dst[(size_t)b * ldd + k] = s;
+    float* d = dst_table ? dst_table[k / cols_per_dst] : dst;
+    d[(size_t)b * ldd + k] = s;
   }
 }
 

@@ -328,6 +328,8 @@ struct sn_bob {
   float* row_loss = nullptr;
   unsigned* ticket = nullptr;
   int last_writer = -1;        // layer whose weights the most recent launch on this handle updated (-1: none)
+  float* const* cut_table = nullptr;   // tensor-parallel head: per-consumer destinations of the cut gradient's columns
+  int cut_cols = 1;
   bool stashed = false;
   int stashed_B = 0;
   int heads = 1;
@@ -797,7 +799,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
         launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, p.nsplit, B, K, gateH, K,
-                 gscale, dst, K);
+                 gscale, dst, K, l == 0 ? h->cut_table : (float* const*)nullptr, h->cut_cols);
         SN_LAUNCH_CHECK();
         h->last_writer = -1;
       } else if (l == 0 && next_act && next_B > 0 && next_B <= kBT && (size_t)N * K > kSmallLayerElems) {
@@ -864,7 +866,8 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
       SN_LAUNCH_CHECK();
       if (need_da) {
         // PA holds one dense [B][K] "split"; bwd_epilogue indexes splits with a 16-row stride
-        launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, 1, B, K, gateH, K, gscale, dst, K);
+        launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, 1, B, K, gateH, K, gscale, dst, K,
+                 l == 0 ? h->cut_table : (float* const*)nullptr, h->cut_cols);
         SN_LAUNCH_CHECK();
         h->last_writer = -1;
       }
@@ -1331,6 +1334,79 @@ int sn_shard_backward_update(sn_shard* h, const float* X, const float* dH, int l
   return shard_backward_impl<1>(h, X, dH, ld_dh, B, X_next, B_next, (cudaStream_t)stream);
 }
 
+// One pass over the cached batches with the first layer sharded (tp.py's loop, in C so that the
+// host enqueues ~14 launches per step instead of crossing the Python/ctypes boundary six times:
+// at two GPUs the Python loop ran at 165 us/step, host-bound).
+int sn_tp_server_epoch(sn_shard* shard, sn_bob* head, int rank, int world, const float* cache, const int64_t* labels,
+                       const int64_t* batch_offsets, int n_batches, const uint8_t* const* drop_masks, uint64_t seed,
+                       uint64_t offset, float* H1, float* dH1, void* h_ready_flags, void* dh_ready_flag,
+                       float* const* dH1_table_dev, const void* dh_flag_table_dev, uint32_t seq0, float* loss_per_step,
+                       void* stream) {
+  SN_SHARD_ENTER(shard);
+  if (n_batches == 0) return 0;
+  SN_REQUIRE(cache && batch_offsets && n_batches > 0 && H1 && dH1 && world >= 1 && rank >= 0 && rank < world,
+             "sn_tp_server_epoch: bad arguments");
+  SN_REQUIRE((rank == 0) == (head != nullptr), "sn_tp_server_epoch: rank 0, and only rank 0, passes the head");
+  SN_REQUIRE(rank != 0 || labels, "sn_tp_server_epoch: the head needs the labels");
+  SN_REQUIRE(world == 1 || (h_ready_flags && dh_ready_flag), "sn_tp_server_epoch: flags are required with more than one rank");
+  SN_REQUIRE(world == 1 || rank != 0 || (dH1_table_dev && dh_flag_table_dev),
+             "sn_tp_server_epoch: the head needs the per-rank gradient destinations and flags");
+  SN_REQUIRE(!head || (head->dims[0] == shard->n_total && head->device == shard->device),
+             "sn_tp_server_epoch: the head's input width must be the sharded layer's width");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int K = shard->K, n1 = shard->n_total;
+  const int nm = head ? head->L - 1 : 0;
+  std::vector<const uint8_t*> hm(std::max(nm, 1), nullptr);
+  char* flags = reinterpret_cast<char*>(h_ready_flags);
+  for (int i = 0; i < n_batches; ++i) {
+    const int64_t r0 = batch_offsets[i], r1 = batch_offsets[i + 1];
+    SN_REQUIRE(r1 > r0 && r1 - r0 <= kBT, "sn_tp_server_epoch: batches of 1..16 rows");
+    const int n = (int)(r1 - r0);
+    const float* X = cache + (size_t)r0 * K;
+    const float* Xn = nullptr;
+    int Bn = 0;
+    if (i + 1 < n_batches) {
+      Xn = cache + (size_t)batch_offsets[i + 1] * K;
+      Bn = (int)(batch_offsets[i + 2] - batch_offsets[i + 1]);
+      if (Bn <= 0 || Bn > kBT) { Xn = nullptr; Bn = 0; }
+    }
+    const uint32_t seq = seq0 + (uint32_t)i + 1;
+    const uint8_t* m1 = drop_masks ? drop_masks[0] + (size_t)r0 * n1 : nullptr;
+    int rc = sn_shard_forward(shard, X, n, 1, m1, seed, offset + (uint64_t)i, H1, n1, stream);
+    if (rc) return rc;
+    if (rank != 0) {
+      rc = sn_flag_signal(flags + 128 * rank, seq, nullptr, nullptr, 0, stream);
+      if (rc) return rc;
+      rc = sn_flag_wait(dh_ready_flag, seq, stream);
+      if (rc) return rc;
+    } else {
+      if (world > 1) {
+        rc = sn_flag_wait_many(flags + 128, world - 1, 128, seq, stream);
+        if (rc) return rc;
+      }
+      if (drop_masks)
+        for (int l = 0; l < nm; ++l) hm[l] = drop_masks[l + 1] + (size_t)r0 * head->dims[l + 1];
+      SN_CUDA(cudaSetDevice(head->device));
+      head->pf_valid = false;
+      // the head's cut-gradient reduction pushes every rank's column range into that rank's own
+      // memory (reading it from here over NVLink made the remote traversals 19 us slower)
+      head->cut_table = world > 1 ? dH1_table_dev : nullptr;
+      head->cut_cols = ceil_div(n1, world);
+      rc = bob_train_step_impl(head, 0, H1, labels + r0 * head->heads, n, drop_masks ? hm.data() : nullptr, seed + 1,
+                               offset + (uint64_t)i, dH1, nullptr, loss_per_step ? loss_per_step + i : nullptr, st, nullptr, 0);
+      head->cut_table = nullptr;
+      if (rc) return rc;
+      if (world > 1) {
+        rc = sn_flag_signal_many(dh_flag_table_dev, world - 1, seq, stream);
+        if (rc) return rc;
+      }
+    }
+    rc = sn_shard_backward_update(shard, X, dH1, n1, n, Xn, Bn, stream);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
 // ------------------------------------------------------------------ peer-memory mailboxes
 int sn_ipc_alloc(size_t bytes, void** dptr, void* handle64) {
   SN_REQUIRE(bytes > 0 && dptr && handle64, "sn_ipc_alloc: bad arguments");
@@ -1373,7 +1449,15 @@ int sn_flag_signal(void* flag, uint32_t value, void* copy_dst, const void* copy_
              "sn_flag_signal: the optional copy must be 8-byte aligned, a multiple of 8 and at most 64 KiB");
   launch_k(flag_signal_kernel, dim3(1), dim3(128), 0, (cudaStream_t)stream, reinterpret_cast<unsigned*>(flag), (unsigned)value,
            reinterpret_cast<unsigned long long*>(copy_dst), reinterpret_cast<const unsigned long long*>(copy_src),
-           (int)(copy_bytes / 8));
+           (int)(copy_bytes / 8), (unsigned* const*)nullptr, 0);
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+int sn_flag_signal_many(const void* flag_table_dev, int count, uint32_t value, void* stream) {
+  SN_REQUIRE(flag_table_dev && count >= 1 && count <= 128, "sn_flag_signal_many: a device array of 1..128 flag addresses");
+  launch_k(flag_signal_kernel, dim3(1), dim3(128), 0, (cudaStream_t)stream, (unsigned*)nullptr, (unsigned)value,
+           (unsigned long long*)nullptr, (const unsigned long long*)nullptr, 0,
+           reinterpret_cast<unsigned* const*>(flag_table_dev), count);
   SN_LAUNCH_CHECK();
   return 0;
 }

@@ -312,7 +312,57 @@ def bench_sisa(rank, world, device, B, n_alices):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         out[n1 + "_ms"] = round(float(t.item()), 3)
     out["gather_bytes"] = sum(sizes[k] * (D0 * 4 + 8) for k in range(n_alices) if owner_rank(k, world) != 0)
+    if world > 1 and os.environ.get("SN_NO_TP") is None:
+        out["tensor_parallel"] = bench_tp_epoch(rank, world, device, B, sizes)
     return out
+
+
+def bench_tp_epoch(rank, world, device, B, sizes):
+    """One SISA server epoch with the first layer's rows split over all ranks (tp.TPServer): the
+    activation cache is replicated on every rank (timed separately), then one pass over it, timed
+    as the max over ranks after a warm-up pass over the first 64 batches."""
+    from . import models as M
+    from . import tp
+    n = sum(sizes)
+    g = torch.Generator(device="cpu").manual_seed(17)
+    if rank == 0:
+        acts = (torch.rand(n, D0, generator=g) * 30 * (torch.rand(n, D0, generator=g) < 0.6)).to(device)
+        labels = torch.randint(0, 10, (n,), generator=g).to(device)
+    else:
+        acts = torch.empty(n, D0, device=device)
+        labels = None
+    offs = []
+    base = 0
+    for nk in sizes:                                   # client by client, as the reference's epoch body
+        offs += list(range(base, base + nk, B))
+        base += nk
+    offs.append(n)
+
+    def timed(fn):
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    rep_ms = timed(lambda: dist.broadcast(acts, src=0))
+    torch.manual_seed(1)                               # the same initial server model on every rank
+    model = M.model2_sisa(device)
+    Ws = [model.fc1.weight.data, model.fc2.weight.data, model.fc3.weight.data]
+    bs = [model.fc1.bias.data, model.fc2.bias.data, model.fc3.bias.data]
+    srv = tp.TPServer(rank, world, device, Ws, bs, B=B, lr=1e-3, weight_decay=1e-5, dropout_p=0.5)
+    srv.server_epoch(acts, labels, offs[:65])          # warm-up
+    ms = timed(lambda: srv.server_epoch(acts, labels, offs))
+    steps = len(offs) - 1
+    srv.close()
+    return {"ranks": world, "server_epoch_ms": round(ms, 3), "steps": steps, "us_per_step": round(1e3 * ms / steps, 2),
+            "replicate_cache_ms": round(rep_ms, 3), "cache_bytes": n * D0 * 4,
+            "layout": "fc1 rows split over all ranks (1/G of W1 + Adam state per GPU); fc2, fc3, loss on rank 0"}
 
 
 def bench_vanilla(args, B, n_alices, turn, config, peak):

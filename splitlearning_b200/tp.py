@@ -12,11 +12,12 @@ over the G ranks - each GPU streams 1/G of W1 and of its optimizer state - while
     head's mailbox over NVLink; signal h_ready[r]
                                                           wait for all h_ready; ordinary 2-layer Bob step
                                                           on H1 (fc2, fc3, CE, backward, Adam); its cut
-                                                          gradient dH1 lands in the mailbox; signal dh_ready
-    wait dh_ready (polled over NVLink); slice backward:
-    reads dH1[:, rows_r] from the head's mailbox, gates
-    it with its own activation, dW + Adam in one
-    traversal, fused with the next batch's forward
+                                                          gradient dH1 is pushed, column range by column
+                                                          range, into each rank's own mailbox, and each
+                                                          rank's dh_ready flag is set
+    wait dh_ready (own memory); slice backward: gates
+    dH1[:, rows_r] with its own activation, dW + Adam in
+    one traversal, fused with the next batch's forward
 
 The cached activations are replicated on every rank (1.2 GB); labels live on the head.  The dropout
 decision of every element is that of the unsharded layer (global element index), so the sharded run
@@ -59,32 +60,38 @@ class TPServer:
             dims = [n1] + [w.shape[0] for w in weights[1:]]
             self.head = E.BobEngine(dims, list(weights[1:]), list(biases[1:]), dropout_p=dropout_p, n_opt_slots=1, max_batch=B,
                                     **kw)
-        # mailbox on the head: H1 [B,n1] | dH1 [B,n1] | h_ready[world] (128 B apart) | dh_ready
+        # every rank owns a mailbox: H1 [B,n1] | dH1 [B,n1] | h_ready[world] (128 B apart) | dh_ready.
+        # H1 and h_ready are used on the head only (the shards store their slices there); dH1 and
+        # dh_ready on every rank (the head pushes rank r's column range and flag into rank r's).
         self.off_h, self.off_dh = 0, B * n1 * 4
         self.off_flags = 2 * B * n1 * 4
         self.off_dh_ready = self.off_flags + 128 * world
         nbytes = self.off_dh_ready + 128
         handle = (C.c_ubyte * 64)()
         base = C.c_void_p()
-        if rank == 0:
-            with torch.cuda.device(device):
-                check(self.lib.sn_ipc_alloc(nbytes, C.byref(base), handle))
-        t = torch.tensor(list(handle), dtype=torch.uint8, device=device)
+        with torch.cuda.device(device):
+            check(self.lib.sn_ipc_alloc(nbytes, C.byref(base), handle))
+        self.base = base.value
+        self.peer = {rank: self.base}
         if world > 1:
-            dist.broadcast(t, src=0)
-        if rank == 0:
-            self.base, self.mapped = base.value, False
-        else:
-            raw = (C.c_ubyte * 64)(*t.cpu().tolist())
-            with torch.cuda.device(device):
-                check(self.lib.sn_ipc_open(raw, C.byref(base)))
-            self.base, self.mapped = base.value, True
-        self.H1 = _Raw(self.base + self.off_h, (B, n1), device)
-        self.dH1 = _Raw(self.base + self.off_dh, (B, n1), device)
+            mine = torch.tensor(list(handle), dtype=torch.uint8, device=device)
+            every = [torch.empty(64, dtype=torch.uint8, device=device) for _ in range(world)]
+            dist.all_gather(every, mine)
+            for r in (range(1, world) if rank == 0 else [0]):
+                raw = (C.c_ubyte * 64)(*every[r].cpu().tolist())
+                p = C.c_void_p()
+                with torch.cuda.device(device):
+                    check(self.lib.sn_ipc_open(raw, C.byref(p)))
+                self.peer[r] = p.value
+        self.head_base = self.peer[0]
+        self.dh_table = self.flag_table = None
         if rank == 0:
             with torch.cuda.device(device):
                 self.H1_t = torch.as_tensor(_View(self.base + self.off_h, B * n1, "<f4"), device=device).view(B, n1)
-                self.dH1_t = torch.as_tensor(_View(self.base + self.off_dh, B * n1, "<f4"), device=device).view(B, n1)
+            if world > 1:       # device arrays of addresses for the head's cut-gradient push and its signal
+                self.dh_table = torch.tensor([self.peer[r] + self.off_dh for r in range(world)], dtype=torch.int64, device=device)
+                self.flag_table = torch.tensor([self.peer[r] + self.off_dh_ready for r in range(1, world)], dtype=torch.int64,
+                                               device=device)
         self.seq = 0
         self.offset = 0
         self.loss = torch.zeros((), device=device)
@@ -98,29 +105,28 @@ class TPServer:
         """One pass over the cached batches acts[offsets[i]:offsets[i+1]] (replicated on every
         rank); labels only on rank 0.  masks: optional [m1 (n,n1), m2 (n,n2)] keep bytes for parity
         runs (m1 on every rank, m2 on rank 0); otherwise Philox keyed by (seed, step)."""
-        lib, st = self.lib, self._stream
         nb = len(offsets) - 1
-        for i in range(nb):
-            s, e = offsets[i], offsets[i + 1]
-            X = acts[s:e]
-            Xn = acts[offsets[i + 1]:offsets[i + 2]] if i + 1 < nb else None
-            self.seq += 1
-            self.offset += 1
-            m1 = masks[0][s:e] if masks is not None else None
-            self.shard.forward(X, self.H1, self.n1, train=True, mask=m1, seed=seed, offset=self.offset)
+        if nb <= 0:
+            return
+        offs = (C.c_int64 * (nb + 1))(*[int(o) for o in offsets])
+        marr, keep = None, None
+        if masks is not None:
+            keep = [m if m.dtype == torch.uint8 else m.to(torch.uint8) for m in masks]
             if self.rank != 0:
-                check(lib.sn_flag_signal(C.c_void_p(self.base + self.off_flags + 128 * self.rank), self.seq, None, None, 0, st()))
-                check(lib.sn_flag_wait(C.c_void_p(self.base + self.off_dh_ready), self.seq, st()))
-            else:
-                if self.world > 1:
-                    check(lib.sn_flag_wait_many(C.c_void_p(self.base + self.off_flags + 128), self.world - 1, 128, self.seq, st()))
-                n = e - s
-                loss = loss_per_step[i] if loss_per_step is not None else self.loss
-                self.head.train_step(self.H1_t[:n], labels[s:e], slot=0, masks=None if masks is None else [masks[1][s:e]],
-                                     seed=seed + 1, offset=self.offset, loss_out=loss, cut_out=self.dH1_t[:n])
-                if self.world > 1:
-                    check(lib.sn_flag_signal(C.c_void_p(self.base + self.off_dh_ready), self.seq, None, None, 0, st()))
-            self.shard.backward_update(X, self.dH1, self.n1, X_next=Xn)
+                keep = keep[:1]
+            keep = [m.contiguous() for m in keep]
+            self._keep = keep                                  # alive until the queued kernels have run
+            marr = _lib.ptr_array(keep)
+        # the loop itself runs in the library (sn_tp_server_epoch): from Python the six calls per step
+        # made rank 0 host-bound (165 us/step at two GPUs)
+        check(self.lib.sn_tp_server_epoch(self.shard.h, self.head.h if self.head is not None else None, self.rank, self.world,
+                                          _lib.ptr(acts), _lib.ptr(labels) if self.rank == 0 else None, offs, nb, marr,
+                                          int(seed), int(self.offset), C.c_void_p(self.head_base + self.off_h),
+                                          C.c_void_p(self.base + self.off_dh), C.c_void_p(self.head_base + self.off_flags),
+                                          C.c_void_p(self.base + self.off_dh_ready), _lib.ptr(self.dh_table),
+                                          _lib.ptr(self.flag_table), self.seq, _lib.ptr(loss_per_step), self._stream()))
+        self.seq += nb
+        self.offset += nb
 
     def gather_fc1(self, W1_full, b1_full):
         """Collect the trained slices into rank 0's full fc1 tensors (state_dict interchange)."""
@@ -144,8 +150,10 @@ class TPServer:
         if self.head is not None:
             self.head.close()
         with torch.cuda.device(self.device):
-            if self.mapped:
-                self.lib.sn_ipc_close(C.c_void_p(self.base))
-            elif self.base:
+            for r, p in self.peer.items():
+                if r != self.rank:
+                    self.lib.sn_ipc_close(C.c_void_p(p))
+            if self.base:
                 self.lib.sn_ipc_free(C.c_void_p(self.base))
+        self.peer = {}
         self.base = 0

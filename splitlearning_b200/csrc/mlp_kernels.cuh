@@ -306,6 +306,26 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
     const float* pp = P + (size_t)b * N + n;
     const size_t pstride = (size_t)Bpad * N;
     int ks = 0;
+    if (ksplit > 16) {
+      // many partials (the 43 k-slice partials of a fused traversal): sixteen loads in flight -
+      // with four, this launch is eleven dependent round trips (9-13 us in the chain)
+      for (; ks + 16 <= ksplit; ks += 16) {
+        float t[16];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) t[q] = pp[(size_t)(ks + q) * pstride];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) s += t[q];
+      }
+      if (ks < ksplit) {
+        float t[16];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) t[q] = ks + q < ksplit ? pp[(size_t)(ks + q) * pstride] : 0.f;
+#pragma unroll
+        for (int q = 0; q < 16; ++q)
+          if (ks + q < ksplit) s += t[q];
+        ks = ksplit;
+      }
+    }
     for (; ks + 4 <= ksplit; ks += 4) {          // four independent loads in flight, fixed add order
       const float p0 = pp[(size_t)ks * pstride], p1 = pp[(size_t)(ks + 1) * pstride];
       const float p2 = pp[(size_t)(ks + 2) * pstride], p3 = pp[(size_t)(ks + 3) * pstride];

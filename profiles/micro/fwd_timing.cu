@@ -15,13 +15,13 @@ int main(int argc, char** argv) {
   cudaMemset(W, 0, (size_t)N * K * 4); cudaMemset(X, 0, (size_t)B * K * 4);
   float* flush; cudaMalloc(&flush, 256 << 20);
   size_t smem = (size_t)16 * kc * 4 + (size_t)8 * kFwdRing * 8 * 32 * 16;
-  cudaFuncSetAttribute(fwd_skinny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaFuncSetAttribute(fwd_skinny_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
   float best = 1e9;
   for (int r = 0; r < 5; ++r) {
     cudaMemset(flush, r, 256 << 20);
     cudaEventRecord(a);
-    fwd_skinny_kernel<<<dim3(nx, ksplit, 1), 256, smem>>>(X, K, B, W, K, N, K, kc, P, 16, ksplit, 0);
+    fwd_skinny_kernel<8><<<dim3(nx, ksplit, 1), 256, smem>>>(X, K, B, W, K, N, K, kc, P, 16, ksplit, 0);
     cudaEventRecord(b); cudaEventSynchronize(b);
     float ms; cudaEventElapsedTime(&ms, a, b); if (ms < best) best = ms;
   }

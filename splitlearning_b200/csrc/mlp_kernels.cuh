@@ -100,28 +100,33 @@ __device__ __forceinline__ void cp_async16_zfill(void* smem, const void* gmem, b
 // values per row (64 B).  Lane l of a tile owns k = 4l..4l+3 (one float4 of each W row); its four
 // X rows are stored at physical rows kk*32 + l and the 16-byte batch quads are XOR-swizzled with
 // (row>>1)&3, which makes every LDS.128 of a quarter-warp hit 8 distinct bank groups.
-__global__ void __launch_bounds__(256, 1)
+// R = weight rows per tile (8 or 4), WPC = 64 / R warps per CTA: the same 128 KB of W rings and the
+// same FMAs per SM either way; R = 4 halves the accumulators per thread (64 instead of 128
+// registers), which lets 16 warps instead of 8 be resident to hide the FMA / LDS latencies.
+template <int R>
+__global__ void __launch_bounds__(32 * (64 / R), 1)
 fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N,
                   int K, int kc, float* __restrict__ P, int Bpad, int ksplit, int prefetch_early, int l2_keep_w) {
   extern __shared__ float4 smem4[];
   // rows below l2_keep_w are tagged evict_last (see l2_policy), the others stream
   const uint64_t pol_keep = l2_policy(1);
+  constexpr int WPC = 64 / R, NT = 32 * WPC;        // warps, threads per CTA
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ks = blockIdx.y, k0 = ks * kc;
   const int klen = min(kc, K - k0);
   const int iters = (klen + 127) >> 7;
   const int b0 = blockIdx.z * kBT, nb = min(kBT, B - b0);
   const int kc4 = kc >> 2;
-  float4* wring = smem4 + kBT * kc4 + warp * (kFwdRing * 8 * 32);   // after the X chunk
+  float4* wring = smem4 + kBT * kc4 + warp * (kFwdRing * R * 32);   // after the X chunk
 #ifdef SN_TIMING
   long long tstamp[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long t_red = 0;
 #endif
   SN_T(0);
 
-  const int groups = (N + 7) >> 3;
+  const int groups = (N + R - 1) / R;
   const long long T = (long long)groups * iters;
-  const int gw = blockIdx.x * 8 + warp, nw = gridDim.x * 8;
+  const int gw = blockIdx.x * WPC + warp, nw = gridDim.x * WPC;
   const int t0 = (int)(T * gw / nw), t1 = (int)(T * (gw + 1) / nw);
 
   const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -133,19 +138,19 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
     if (ti < t1) {
       const int k = iti * 128 + lane * 4;
       if (k < klen) {
-        const float* src = W + (size_t)(gi * 8) * ldw + k0 + k;
-        if (gi * 8 + 8 <= N) {
-          if (gi * 8 < l2_keep_w) {
+        const float* src = W + (size_t)(gi * R) * ldw + k0 + k;
+        if (gi * R + R <= N) {
+          if (gi * R < l2_keep_w) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) cp_async16_hint(wring + (slot * 8 + i) * 32 + lane, src + (size_t)i * ldw, pol_keep);
+            for (int i = 0; i < R; ++i) cp_async16_hint(wring + (slot * R + i) * 32 + lane, src + (size_t)i * ldw, pol_keep);
           } else {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) cp_async16(wring + (slot * 8 + i) * 32 + lane, src + (size_t)i * ldw);
+            for (int i = 0; i < R; ++i) cp_async16(wring + (slot * R + i) * 32 + lane, src + (size_t)i * ldw);
           }
         } else {
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
-            cp_async16(wring + (slot * 8 + i) * 32 + lane, src + (size_t)min(i, N - 1 - gi * 8) * ldw);
+          for (int i = 0; i < R; ++i)
+            cp_async16(wring + (slot * R + i) * 32 + lane, src + (size_t)min(i, N - 1 - gi * R) * ldw);
         }
       }
       ++ti;
@@ -173,12 +178,12 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
   // issued before its stores.  (clock64 phase timing: the first version - one LDG.128 then four
   // STS.32 per item, with a divide - cost 12.5k of the kernel's 56k cycles.)
   {
-    constexpr int XI = 2;                                   // k4 items per thread per pass
-    for (int kbase = 0; kbase < kc4; kbase += 256 * XI) {
+    constexpr int XI = R == 8 ? 2 : 1;                      // k4 items per thread per pass (16 float4 of temporaries each)
+    for (int kbase = 0; kbase < kc4; kbase += NT * XI) {
       float4 v[XI][4][4];
 #pragma unroll
       for (int u = 0; u < XI; ++u) {
-        const int k4 = kbase + u * 256 + tid;
+        const int k4 = kbase + u * NT + tid;
 #pragma unroll
         for (int bq = 0; bq < 4; ++bq)
 #pragma unroll
@@ -191,7 +196,7 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
       }
 #pragma unroll
       for (int u = 0; u < XI; ++u) {
-        const int k4 = kbase + u * 256 + tid;
+        const int k4 = kbase + u * NT + tid;
         if (k4 < kc4) {
           const int m = k4 & 31, base = (k4 >> 5) * 128 + m, swz = (m >> 1) & 3;
 #pragma unroll
@@ -210,9 +215,9 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
   __syncthreads();
   SN_T(3);
 
-  float acc[8 * kBT];
+  float acc[R * kBT];
 #pragma unroll
-  for (int i = 0; i < 8 * kBT; ++i) acc[i] = 0.f;
+  for (int i = 0; i < R * kBT; ++i) acc[i] = 0.f;
   int g = t0 / iters, it = t0 - g * iters;
   bool has_first = (it == 0);
   int slot = 0;
@@ -223,12 +228,12 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
   for (int t = t0; t < t1; ++t) {
     issue((slot + kFwdRing - 1) & (kFwdRing - 1));
     cp_async_wait<kFwdRing - 1>();
-    float4 wc[8];
+    float4 wc[R];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) wc[i] = wring[(slot * 8 + i) * 32 + lane];
+    for (int i = 0; i < R; ++i) wc[i] = wring[(slot * R + i) * 32 + lane];
     if (ktail && it == iters - 1 && it * 128 + lane * 4 >= klen) {   // nothing was copied for this lane
 #pragma unroll
-      for (int i = 0; i < 8; ++i) wc[i] = zero;
+      for (int i = 0; i < R; ++i) wc[i] = zero;
     }
     slot = (slot + 1) & (kFwdRing - 1);
     const float4* xrow = smem4 + (size_t)(it * 128 + lane) * 4;     // physical row kk*32 + lane
@@ -239,7 +244,7 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
         const float4 x = xrow[kk * 32 * 4 + (bq ^ sw)];
         const float2 xlo = make_float2(x.x, x.y), xhi = make_float2(x.z, x.w);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < R; ++i) {
           const float w = kk == 0 ? wc[i].x : kk == 1 ? wc[i].y : kk == 2 ? wc[i].z : wc[i].w;
           const float2 ww = make_float2(w, w);
           float* a = acc + i * kBT + bq * 4;
@@ -254,13 +259,15 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
 #ifdef SN_TIMING
       const long long tr0 = clock64();
 #endif
-      butterfly_reduce<8 * kBT>(acc, lane);        // lane ends with row lane>>2, batch (lane&3)*4+j
-      const int row = g * 8 + (lane >> 2);
+      // after the butterfly lane l holds the flat indices (row*16 + b) l*R/2 .. l*R/2 + R/2 - 1
+      butterfly_reduce<R * kBT>(acc, lane);
+      constexpr int PL = R / 2;                    // values per lane
+      const int row = g * R + (lane * PL) / kBT;
       if (row < N) {
         float* dst = Pbase + (has_first ? 0 : slot_stride) + row;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int b = (lane & 3) * 4 + j;
+        for (int j = 0; j < PL; ++j) {
+          const int b = (lane * PL) % kBT + j;
           if (b < nb) {
             dst[(size_t)b * N] = acc[j];
             if (has_first && group_done) dst[slot_stride + (size_t)b * N] = 0.f;
@@ -268,7 +275,7 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
         }
       }
 #pragma unroll
-      for (int i = 0; i < 8 * kBT; ++i) acc[i] = 0.f;
+      for (int i = 0; i < R * kBT; ++i) acc[i] = 0.f;
 #ifdef SN_TIMING
       t_red += clock64() - tr0;
 #endif
@@ -279,7 +286,7 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
   SN_T(4);
 #ifdef SN_TIMING
   if (lane == 0 && blockIdx.z == 0) {
-    long long* o = g_fwd_timing + ((blockIdx.y * gridDim.x + blockIdx.x) * 8 + warp) * 8;
+    long long* o = g_fwd_timing + ((blockIdx.y * gridDim.x + blockIdx.x) * WPC + warp) * 8;
     o[0] = tstamp[1] - tstamp[0]; o[1] = tstamp[2] - tstamp[1]; o[2] = tstamp[3] - tstamp[2];
     o[3] = tstamp[4] - tstamp[3]; o[4] = t_red; o[5] = t1 - t0; o[6] = tstamp[0]; o[7] = tstamp[4];
   }

@@ -47,10 +47,17 @@ constexpr int kSmallLayerMaxK = 2048;             // its X tile [16][K] fp32 mus
 struct FwdPlan { int kc, ksplit, nx; };
 struct BwdPlan { int kw, kgroups, nsplit, rows_per_cta; };
 
+// rows per tile of the FMA weight-stream forward: 8 (8 warps per CTA) or 4 (16 warps per CTA)
+static int fwd_rows() {
+  static const int r = (getenv("SN_FWD_ROWS") && atoi(getenv("SN_FWD_ROWS")) == 4) ? 4 : 8;
+  return r;
+}
+
 static FwdPlan plan_fwd(int K, int N, int sms) {
   // k-chunks of whole 128-float slices, as equal as possible; CTAs per chunk capped so that a
   // warp's tile range is at least one row group long (=> at most two partials per group)
-  const int slices = ceil_div(K, 128), groups = ceil_div(N, 8);
+  const int R = fwd_rows(), WPC = 64 / R;
+  const int slices = ceil_div(K, 128), groups = ceil_div(N, R);
   FwdPlan best{128 * std::min(slices, kMaxKc / 128), 0, 1};
   best.ksplit = ceil_div(K, best.kc);
   double best_score = -1;
@@ -58,9 +65,9 @@ static FwdPlan plan_fwd(int K, int N, int sms) {
     int kc = 128 * ceil_div(slices, s);
     if (kc > kMaxKc) continue;
     int actual = ceil_div(K, kc);
-    int nx = std::max(1, std::min(sms / actual, groups / 8));
+    int nx = std::max(1, std::min(sms / actual, groups / WPC));
     double iters = kc / 128.0;
-    double tp = groups * iters / (nx * 8.0);             // tiles per warp
+    double tp = groups * iters / (nx * (double)WPC);     // tiles per warp
     double util = std::min(1.0, (double)nx * actual / sms);
     double balance = (double)K / ((double)actual * kc);
     double score = util * balance * (tp / (tp + 2.0)) * (iters / (iters + 0.25));
@@ -263,12 +270,18 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
     FwdPlan p = plan_fwd(K, N, sms);
     int tiles = ceil_div(B, kBT), Bpad = tiles * kBT;
     size_t smem = (size_t)kBT * p.kc * 4 + (size_t)8 * kFwdRing * 8 * 32 * 16;   // X chunk + per-warp W rings
-    if (set_smem(fwd_skinny_kernel, smem)) return 1;
     dim3 grid(p.nx, p.ksplit, tiles);
     cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
     // the weight ring starts before the dependency wait unless the previous launch may have written W
-    launch_k(fwd_skinny_kernel, dim3(grid), dim3(256), smem, st, X, ldx, B, W, K, N, K, p.kc, P, Bpad, p.ksplit,
-             (layer > 0 || prefetch_w) ? 1 : 0, l2_keep_w);
+    if (fwd_rows() == 4) {
+      if (set_smem(fwd_skinny_kernel<4>, smem)) return 1;
+      launch_k(fwd_skinny_kernel<4>, dim3(grid), dim3(512), smem, st, X, ldx, B, W, K, N, K, p.kc, P, Bpad, p.ksplit,
+               (layer > 0 || prefetch_w) ? 1 : 0, l2_keep_w);
+    } else {
+      if (set_smem(fwd_skinny_kernel<8>, smem)) return 1;
+      launch_k(fwd_skinny_kernel<8>, dim3(grid), dim3(256), smem, st, X, ldx, B, W, K, N, K, p.kc, P, Bpad, p.ksplit,
+               (layer > 0 || prefetch_w) ? 1 : 0, l2_keep_w);
+    }
     Profiler::end(pe, st);
     SN_LAUNCH_CHECK();
     launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, P, kFwdSlots * p.ksplit, Bpad, B, N, bias, relu, mask,
@@ -1280,9 +1293,15 @@ int sn_shard_forward(sn_shard* h, const float* X, int B, int train_mode, const u
   } else {
     FwdPlan p = plan_fwd(K, N, h->sms);
     size_t smem = (size_t)kBT * p.kc * 4 + (size_t)8 * kFwdRing * 8 * 32 * 16;
-    if (set_smem(fwd_skinny_kernel, smem)) return 1;
-    launch_k(fwd_skinny_kernel, dim3(p.nx, p.ksplit, 1), dim3(256), smem, st, X, K, B, h->W, K, N, K, p.kc, h->P, kBT, p.ksplit, 0,
-             h->l2_keep);
+    if (fwd_rows() == 4) {
+      if (set_smem(fwd_skinny_kernel<4>, smem)) return 1;
+      launch_k(fwd_skinny_kernel<4>, dim3(p.nx, p.ksplit, 1), dim3(512), smem, st, X, K, B, h->W, K, N, K, p.kc, h->P, kBT, p.ksplit, 0,
+               h->l2_keep);
+    } else {
+      if (set_smem(fwd_skinny_kernel<8>, smem)) return 1;
+      launch_k(fwd_skinny_kernel<8>, dim3(p.nx, p.ksplit, 1), dim3(256), smem, st, X, K, B, h->W, K, N, K, p.kc, h->P, kBT, p.ksplit, 0,
+               h->l2_keep);
+    }
     SN_LAUNCH_CHECK();
     nparts = kFwdSlots * p.ksplit;
   }

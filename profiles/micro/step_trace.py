@@ -79,6 +79,21 @@ if mode == "vanilla":
     def run(n):
         for i in range(n):
             E.vanilla_step(alices[0][1], bob, xs[i % 64], ys[i % 64], 0, 1, i + 1, act, cut, loss)
+elif mode == "concat":
+    # BASELINE.json config 4: the concat server (fc1 5000 x 37856), Adam, fused server steps
+    from splitlearning_b200 import models as M
+    torch.manual_seed(0)
+    cm = M.model2_sisa_concat(7, dev)
+    bob = cm.make_engine(optimizer=E.SN_OPT_ADAM, lr=1e-3, weight_decay=1e-5, n_opt_slots=1, max_batch=B)
+    bob.set_ce_heads(7)
+    nbat = 140
+    acts = torch.rand(nbat * B, D0 * 7, device=dev)
+    labels = torch.randint(0, 10, (nbat * B * 7,), device=dev)
+    offs = list(range(0, nbat * B + 1, B))
+    names = None
+
+    def run(n):
+        bob.server_epoch(acts, labels, offs, seed=3)
 elif mode == "local":
     # SISA phase 1: an Alice's local epoch (conv fwd -> CE over the 5408 activations -> conv bwd + Adam)
     from splitlearning_b200 import models as M

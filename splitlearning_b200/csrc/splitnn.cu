@@ -94,6 +94,9 @@ static BwdPlan plan_bwd(int N, int K, int sms, bool need_da, bool adam) {
     double kwaste = (double)K / ((double)kgroups * kw * 128);
     double part = need_da ? (double)nsplit * 16.0 * K * 4.0 * 2.0 : 0.0;
     double score = util * kwaste * main_bytes / (main_bytes + part);
+    // near-ties go to the wider CTA: kw*512 contiguous bytes per row instead of 512 (DRAM page
+    // locality; the 37856-wide concat layer ran at 4.35 TB/s with kw=1)
+    score *= 1.0 + 0.01 * (kw == 2 ? 1 : kw == 4 ? 2 : kw == 8 ? 3 : 0);
     if (score > best_score) { best_score = score; best = BwdPlan{kw, kgroups, nsplit, rows}; }
   }
   return best;

@@ -166,32 +166,50 @@ __global__ void __launch_bounds__(256) conv_pool_bwd_kernel(const float* __restr
   if (!is_last) return;
   __threadfence();
   SN_TP(6);
-  for (int idx = threadIdx.x; idx < kConvParams; idx += 256) {
-    // parameter and optimizer state requested first, then the partials eight at a time (all in
-    // flight together), added in CTA order
-    float* p = idx < 288 ? (w + idx) : (bias + idx - 288);
-    float pv = 0.f, a = 0.f, bq = 0.f;
-    if (OPT != 0) {
-      pv = *p;
-      a = s1[idx];
-      if (OPT == 2) bq = s2[idx];
-    }
-    float s = 0.f;
-    for (unsigned r0 = 0; r0 < gridDim.x; r0 += 8) {
-      float t[8];
+  {
+    // 320 outputs on 256 threads: threads 0..63 own two (idx, idx+256).  Everything a thread needs -
+    // parameter, optimizer state and all partials of BOTH its outputs - is requested before the
+    // first add, so the tail is one round trip; partials are added in CTA order.
+    constexpr int kMaxGx = 32;                       // partial rows summed from registers in one go
+    float pv[2] = {0.f, 0.f}, a[2] = {0.f, 0.f}, bq[2] = {0.f, 0.f}, s[2] = {0.f, 0.f};
+    float* pp[2];
+    bool own[2];
 #pragma unroll
-      for (unsigned q = 0; q < 8; ++q) t[q] = r0 + q < gridDim.x ? __ldcg(partial + (size_t)(r0 + q) * kConvParams + idx) : 0.f;
-#pragma unroll
-      for (unsigned q = 0; q < 8; ++q)
-        if (r0 + q < gridDim.x) s += t[q];
+    for (int j = 0; j < 2; ++j) {
+      const int idx = threadIdx.x + 256 * j;
+      own[j] = idx < kConvParams;
+      pp[j] = idx < 288 ? (w + idx) : (bias + (own[j] ? idx - 288 : 0));
+      if (OPT != 0 && own[j]) {
+        pv[j] = *pp[j];
+        a[j] = s1[idx];
+        if (OPT == 2) bq[j] = s2[idx];
+      }
     }
-    if (OPT == 0) {
-      if (idx < 288) dw_out[idx] = s; else db_out[idx - 288] = s;
-    } else {
-      opt_update<OPT>(op, pv, s, a, bq);
-      *p = pv;
-      s1[idx] = a;
-      if (OPT == 2) s2[idx] = bq;
+    for (unsigned r0 = 0; r0 < gridDim.x; r0 += kMaxGx) {
+      float t[2][kMaxGx];
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (unsigned q = 0; q < kMaxGx; ++q)
+          t[j][q] = (own[j] && r0 + q < gridDim.x) ? __ldcg(partial + (size_t)(r0 + q) * kConvParams + threadIdx.x + 256 * j) : 0.f;
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (unsigned q = 0; q < kMaxGx; ++q)
+          if (r0 + q < gridDim.x) s[j] += t[j][q];
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int idx = threadIdx.x + 256 * j;
+      if (!own[j]) continue;
+      if (OPT == 0) {
+        if (idx < 288) dw_out[idx] = s[j]; else db_out[idx - 288] = s[j];
+      } else {
+        opt_update<OPT>(op, pv[j], s[j], a[j], bq[j]);
+        *pp[j] = pv[j];
+        s1[idx] = a[j];
+        if (OPT == 2) s2[idx] = bq[j];
+      }
     }
   }
   SN_TP(7);

@@ -360,18 +360,20 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
 // form: CG reads the logits with ld.global.cg (L2), needed when other CTAs of the same launch wrote
 // them.
 // ------------------------------------------------------------------------------------------
-template <int NC>
+// GW = lanes per row (32: one row per warp; 16: two rows per warp, in lock step - halves the
+// dependent-latency chain when a few rows are all a CTA has to do)
+template <int NC, int GW = 32>
 __device__ __forceinline__ float ce_row_reg(const float (&zc)[NC], int64_t lab, int C, float invB,
-                                            float* __restrict__ dzr, int lane) {
+                                            float* __restrict__ dzr, int gl) {
   float m = -INFINITY;
   int arg = 0x7fffffff;
 #pragma unroll
   for (int i = 0; i < NC; ++i) {
-    const int c = lane + 32 * i;
+    const int c = gl + GW * i;
     if (c < C && zc[i] > m) { m = zc[i]; arg = c; }
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
+  for (int o = GW / 2; o > 0; o >>= 1) {
     const float om = __shfl_xor_sync(0xffffffffu, m, o);
     const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
     if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
@@ -381,15 +383,18 @@ __device__ __forceinline__ float ce_row_reg(const float (&zc)[NC], int64_t lab, 
   float s1 = 0.f, zl = 0.f, ex[NC];
 #pragma unroll
   for (int i = 0; i < NC; ++i) {
-    const int c = lane + 32 * i;
+    const int c = gl + GW * i;
     ex[i] = 1.f;
     if (c < C) {
       if (c != arg) { ex[i] = expf(zc[i] - m); s1 += ex[i]; }
       if (c == lab) zl = zc[i];
     }
   }
-  s1 = warp_sum(s1);
-  zl = warp_sum(zl);                         // exactly one lane holds z[label], the others add zeros
+#pragma unroll
+  for (int o = GW / 2; o > 0; o >>= 1) {
+    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    zl += __shfl_xor_sync(0xffffffffu, zl, o);     // exactly one lane holds z[label], the others add zeros
+  }
   const bool ok = lab >= 0 && lab < C;
   // -log_softmax(z)[y] = log(sum exp(z-m)) - (z[y]-m): no cancellation against the row max
   const float loss = ok ? (log1pf(s1) - (zl - m)) : NAN;   // torch raises on a bad target
@@ -397,7 +402,7 @@ __device__ __forceinline__ float ce_row_reg(const float (&zc)[NC], int64_t lab, 
     const float invs = 1.f / (1.f + s1);
 #pragma unroll
     for (int i = 0; i < NC; ++i) {
-      const int c = lane + 32 * i;
+      const int c = gl + GW * i;
       if (c < C) {
         float p = ex[i] * invs;
         if (c == lab) p -= 1.f;
@@ -590,11 +595,32 @@ fwd_small_kernel(const float* __restrict__ X, int ldx, int B, const float* __res
   if (!is_last) return;
   __threadfence();
   const float invB = 1.f / (float)ce.rows;
-  for (int r = warp; r < ce.rows; r += 8) {
-    const int64_t lab = r == r_a ? lab_a : r == r_b ? lab_b : ce.labels[r];
-    const float l = ce_row_auto<true>(H + (size_t)r * ce.C, lab, ce.C, invB, ce.dz ? ce.dz + (size_t)r * ce.C : nullptr, lane);
-    if (lane == 0) {
-      if (r < 256) rl[r] = l; else ce.row_loss[r] = l;
+  if (ce.C <= 128) {
+    // two rows per warp (16 lanes x 8 classes each), sixteen rows per pass of the CTA
+    const int gl = lane & 15;
+    for (int r0 = warp * 2; r0 < ce.rows; r0 += 16) {     // warp-uniform trip count: the shuffles use full masks
+      const int r = r0 + (lane >> 4);
+      const bool live = r < ce.rows;
+      const float* zr = H + (size_t)(live ? r : 0) * ce.C;
+      float zc[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int c = gl + 16 * i;
+        zc[i] = (live && c < ce.C) ? __ldcg(zr + c) : -INFINITY;
+      }
+      const int64_t lab = live ? ce.labels[r] : 0;
+      const float l = ce_row_reg<8, 16>(zc, lab, live ? ce.C : 0, invB, (live && ce.dz) ? ce.dz + (size_t)r * ce.C : nullptr, gl);
+      if (live && gl == 0) {
+        if (r < 256) rl[r] = l; else ce.row_loss[r] = l;
+      }
+    }
+  } else {
+    for (int r = warp; r < ce.rows; r += 8) {
+      const int64_t lab = r == r_a ? lab_a : r == r_b ? lab_b : ce.labels[r];
+      const float l = ce_row_auto<true>(H + (size_t)r * ce.C, lab, ce.C, invB, ce.dz ? ce.dz + (size_t)r * ce.C : nullptr, lane);
+      if (lane == 0) {
+        if (r < 256) rl[r] = l; else ce.row_loss[r] = l;
+      }
     }
   }
   __syncthreads();

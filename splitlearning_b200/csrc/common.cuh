@@ -59,6 +59,7 @@ struct OptParams {
   float step_size;     // lr / (1 - beta1^t)
   float bc2_sqrt;      // sqrt(1 - beta2^t)
   float inv_bc2_sqrt;  // 1 / sqrt(1 - beta2^t), formed in double
+  int acc_first;       // gradient-accumulation launches (OPT == 3 in bwd_update_kernel): first batch tile
 };
 
 template <int OPT>

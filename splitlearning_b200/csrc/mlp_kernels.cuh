@@ -851,17 +851,23 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
   auto issue = [&](int slot, int row) {
     if (kok && row < nb1) {
       const size_t o = (size_t)row * ldw + k0;
-      cp_async16_hint(ring + (0 * kRing + slot) * 256 + tid, W + o, row < l2_keep_w ? pol_keep : pol_norm);
-      cp_async16_hint(ring + (1 * kRing + slot) * 256 + tid, s1 + o, pol_s);
+      if (OPT != 3 || NEED_DA) cp_async16_hint(ring + (0 * kRing + slot) * 256 + tid, W + o, row < l2_keep_w ? pol_keep : pol_norm);
+      if (OPT != 3 || !op.acc_first) cp_async16_hint(ring + (1 * kRing + slot) * 256 + tid, s1 + o, pol_s);
       if (OPT == 2) cp_async16_hint(ring + (2 * kRing + slot) * 256 + tid, s2 + o, pol_s);
     }
     cp_async_commit();
   };
   int n = nb0 + wr;
+  if (OPT != 3) {
 #pragma unroll
-  for (int d = 0; d < kRing - 1; ++d) issue(d, n + d * rw);      // start streaming before anything else
+    for (int d = 0; d < kRing - 1; ++d) issue(d, n + d * rw);    // start streaming before anything else
+  }
   pdl_wait();        // W / optimizer state are never written by the kernel just before this one;
   pdl_launch();      // dZ (and A) are, so everything below waits for it
+  if (OPT == 3) {    // ... except the gradient buffer of an accumulation launch (the previous tile's launch wrote it)
+#pragma unroll
+    for (int d = 0; d < kRing - 1; ++d) issue(d, n + d * rw);
+  }
 
   {  // dZ tile, transposed to [row][16]; loads batched ahead of their stores (latency, not bandwidth)
     constexpr int SB = 8;
@@ -922,8 +928,8 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
     cp_async_wait<kRing - 1>();
     float4 w = make_float4(0.f, 0.f, 0.f, 0.f), m1 = w, m2 = w;
     if (kok) {
-      w = ring[(0 * kRing + slot) * 256 + tid];
-      m1 = ring[(1 * kRing + slot) * 256 + tid];
+      if (OPT != 3 || NEED_DA) w = ring[(0 * kRing + slot) * 256 + tid];
+      if (OPT != 3 || !op.acc_first) m1 = ring[(1 * kRing + slot) * 256 + tid];
       if (OPT == 2) m2 = ring[(2 * kRing + slot) * 256 + tid];
     }
     slot = (slot + 1) & (kRing - 1);
@@ -947,7 +953,14 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
       }
     }
     float4 g = make_float4(g2[0].x + g2[0].y, g2[1].x + g2[1].y, g2[2].x + g2[2].y, g2[3].x + g2[3].y);
-    if (kok) {
+    if (OPT == 3) {
+      // accumulation launch (batches of 17..64 rows go through in tiles of 16): the gradient of this
+      // tile is added into the buffer behind `s1`; the weights are only read (for dA)
+      if (kok) {
+        m1 = make_float4(m1.x + g.x, m1.y + g.y, m1.z + g.z, m1.w + g.w);     // m1 is zero on the first tile
+        *reinterpret_cast<float4*>(s1 + (size_t)n * ldw + k0) = m1;
+      }
+    } else if (kok) {
       opt_update<OPT>(op, w.x, g.x, m1.x, m2.x);
       opt_update<OPT>(op, w.y, g.y, m1.y, m2.y);
       opt_update<OPT>(op, w.z, g.z, m1.z, m2.z);
@@ -983,7 +996,7 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
   // bias: db[n] = sum_b dZ[b][n].  One thread per row AFTER the streaming loop (a per-row
   // load->update->store chain inside the loop made the k-group-0 CTAs latency-bound and the
   // whole grid wait for them).
-  if (blockIdx.x == 0) {
+  if (OPT != 3 && blockIdx.x == 0) {
     for (int j = tid; j < nrows; j += 256) {
       float db = 0.f;
 #pragma unroll

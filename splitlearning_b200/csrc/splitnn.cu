@@ -839,6 +839,51 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
       }
+    } else if (B <= kSkinnyFwdMaxB && (K % 4) == 0 && g_matmul_precision.load() != 2) {
+      // 17..64 rows (--batch_size 32/64): still a weight stream, far below the tensor ridge.  The
+      // batch goes through the same fp32 traversal in tiles of 16 rows: each tile's launch forms its
+      // dA rows and ADDS its dW into a gradient buffer (OPT=3); one elementwise pass then applies
+      // the optimizer.  ~3x the bytes of the B<=16 form, but 2-3x faster than 3xTF32 GEMMs whose
+      // reduction dimension is only B.
+      if (!h->dWbuf) {
+        size_t mx = 0;
+        for (int q = 0; q < h->L; ++q) mx = std::max(mx, (size_t)h->dims[q] * h->dims[q + 1]);
+        SN_CUDA(cudaMalloc(&h->dWbuf, mx * 4));
+      }
+      BwdPlan p = plan_bwd(N, K, h->sms, need_da, false);
+      size_t smem = bwd_smem_bytes(p, need_da, false);
+      dim3 grid(p.kgroups, p.nsplit);
+      OptParams acc = op;
+      cudaEvent_t pe = h->prof.begin(st, 1, l);
+      for (int r0 = 0; r0 < B; r0 += kBT) {
+        const int nt = std::min(kBT, B - r0);
+        acc.acc_first = r0 == 0 ? 1 : 0;
+        if (need_da) {
+          if (set_smem(bwd_update_kernel<3, true>, smem)) return 1;
+          launch_k(bwd_update_kernel<3, true>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, (float*)nullptr, h->dWbuf,
+                   (float*)nullptr, (float*)nullptr, (float*)nullptr, dZ + (size_t)r0 * N, N, A + (size_t)r0 * K, K, nt, h->PA, p.kw,
+                   p.rows_per_cta, acc, (const float*)nullptr, 0, (float*)nullptr, 0, (const float*)nullptr, 1.f);
+          SN_LAUNCH_CHECK();
+          launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)nt * K, h->sms)), dim3(256), 0, st, h->PA, p.nsplit, nt, K,
+                   gateH ? gateH + (size_t)r0 * K : (const float*)nullptr, K, gscale, dst + (size_t)r0 * K, K,
+                   (float* const*)nullptr, 1);
+          SN_LAUNCH_CHECK();
+        } else {
+          if (set_smem(bwd_update_kernel<3, false>, smem)) return 1;
+          launch_k(bwd_update_kernel<3, false>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, (float*)nullptr, h->dWbuf,
+                   (float*)nullptr, (float*)nullptr, (float*)nullptr, dZ + (size_t)r0 * N, N, A + (size_t)r0 * K, K, nt, h->PA, p.kw,
+                   p.rows_per_cta, acc, (const float*)nullptr, 0, (float*)nullptr, 0, (const float*)nullptr, 1.f);
+          SN_LAUNCH_CHECK();
+        }
+      }
+      launch_k(opt_elementwise_kernel<OPT>, dim3(ew_grid((size_t)N * K, h->sms)), dim3(256), 0, st, h->W[l], h->dWbuf, s.s1[2 * l],
+               s.s2[2 * l], (size_t)N * K, op);
+      SN_LAUNCH_CHECK();
+      launch_k(bias_grad_update_kernel<OPT>, dim3(ceil_div(N, 256)), dim3(256), 0, st, dZ, N, B, N, h->b[l], s.s1[2 * l + 1],
+               s.s2[2 * l + 1], op);
+      SN_LAUNCH_CHECK();
+      Profiler::end(pe, st);
+      h->last_writer = -1;
     } else if (g_matmul_precision.load() != 2 && (K % 4) == 0 && (N % 4) == 0) {
       // tensor-bound regime (perf mode): dA, then dW fused with the optimizer, both on tcgen05
       if (need_da) {

@@ -161,7 +161,11 @@ int sn_bob_profile_read(sn_bob* h, int kind, int layer, double* total_ms, int* l
  * backward, optimizer update of `slot`; cut_grad [B,dims[0]] = dL/dact (nullable: SISA's input
  * is detached).  drop_masks: nullable host array of (n_layers-1) device pointers to [B,dims[l+1]]
  * keep-bytes (teacher-forced / torch-CPU-stream parity mode); when NULL masks come from Philox
- * keyed by (seed, offset).  logits_out [B,dims[L]] nullable.  loss_out: device scalar, nullable.
+ * keyed by (seed, offset).  logits_out [B,dims[L]] nullable.  loss_out: one float, nullable - device
+ * memory, or pinned HOST memory (device-visible under UVA): the loss kernel then stores the value over
+ * PCIe itself and no D2H copy is needed in the stream (valid once the stream is synchronised).
+ * Batches of 1..16 rows take the fused weight-stream kernels, 17..64 rows the same kernels in tiles of 16
+ * with gradient accumulation, larger ones the tcgen05 GEMMs (sn_set_matmul_precision).
  * Replaces bob.train_and_backward + the Bob half of dist_optimizer.step,
  * data_entities_vanilla.py:226-232,76 ; and the batch body of SISA's server loop,
  * data_entities_vanilla_sisa.py:305-313. */

@@ -514,3 +514,33 @@ def test_skinny_forward_on_tensor_cores_matches_fma_kernel(eng):
         assert np.array_equal(tc, tc2)                  # deterministic
         assert rel_err(fma, ref) <= 2e-6
         assert rel_err(tc, ref) <= 1e-5                 # 3xTF32 + fp32 tensor-core accumulation
+
+
+@pytest.mark.parametrize("B", [17, 33, 64])
+def test_mid_batch_tiled_backward_sgd(eng, B):
+    """17..64 rows go through the fp32 weight-stream kernels in tiles of 16 with the per-tile dW
+    added into a gradient buffer (OPT=3) and one optimizer pass at the end: one SGD-momentum step
+    (momentum buffers pre-loaded) against the oracle, including a ragged last tile and the cut
+    gradient; then a second step to see the buffer is re-armed."""
+    rng = np.random.RandomState(B)
+    dims = [5408, 320, 60, 100]
+    shapes = [(320, 5408), (320,), (60, 320), (60,), (100, 60), (100,)]
+    b = T(seeded_weights(shapes, 33))
+    spec = R.BobSpec(tuple(dims), False, 0.5)
+    gp = [cu(p.numpy()) for p in b]
+    bob = eng.BobEngine(dims, gp[0::2], gp[1::2], optimizer=eng.SN_OPT_SGD_MOMENTUM, lr=1e-3, momentum=0.9, max_batch=64)
+    opt = R.SGDState()
+    for step in range(2):
+        act = (rng.rand(B, 5408) * 40 * (rng.rand(B, 5408) < 0.6)).astype(np.float32)
+        y = rng.randint(0, 10, size=B).astype(np.int64)
+        masks = seeded_masks(B, (320, 60), 70 + step)
+        bl = [p.detach().clone().requires_grad_(True) for p in b]
+        at = torch.from_numpy(act).requires_grad_(True)
+        loss_ref = R.cross_entropy(R.bob_forward(at, bl, spec, T(masks)), torch.from_numpy(y))
+        loss_ref.backward()
+        R.sgd_momentum_(b, [p.grad for p in bl], opt, 1e-3, 0.9)
+        loss, cut, _ = bob.train_step(cu(act), cu(y), masks=[cu(m) for m in masks])
+        assert abs(loss.item() - loss_ref.item()) <= TOL * abs(loss_ref.item())
+        assert rel_err(cut.cpu(), at.grad) <= TOL
+        for p_ref, p in zip(b, gp):
+            assert rel_err(p.cpu(), p_ref) <= 1e-5

@@ -815,7 +815,10 @@ __global__ void __launch_bounds__(256) eval_counts_kernel(const float* __restric
 //   across the CTA's row-warps in shared memory and written to PA[blockIdx.y][b][k]; the n-split
 //   partials are summed in fixed order by bwd_epilogue_kernel.
 // ------------------------------------------------------------------------------------------
-constexpr int kRing = 8;   // rows in flight per thread (W + optimizer state): ~56-84 KB per SM
+#ifndef SN_KRING
+#define SN_KRING 8
+#endif
+constexpr int kRing = SN_KRING;   // rows in flight per thread (W + optimizer state): ~56-84 KB per SM (power of two)
 
 // FUSE_FWD (SISA server epochs): the NEXT batch's activations are already known, so the same
 // traversal also produces the next step's forward through this layer with the freshly updated

@@ -258,10 +258,10 @@ def run_ours_single(args):
     roofline = {"bound": "hbm", "kernel": "bwd_update_kernel<SGD,dA> fc1 (5000x5408): dW+dX+momentum update in one traversal",
                 "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                 # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the committed
-                # `ncu --set full` capture (profiles/r1b_kernels_ncu_full.csv): 217.05 MB read + 140.29 MB
+                # `ncu --set full` capture (profiles/r1c_kernels_ncu_full.csv): 217.06 MB read + 140.41 MB
                 # written; the rest of the 216 MB of writes is still in L2 at exit (evict_last rows,
                 # dirty lines)
-                "traffic": 357341696.0, "peak_source": peak_src, "bytes_per_launch": dom_bytes,
+                "traffic": 357466112.0, "peak_source": peak_src, "bytes_per_launch": dom_bytes,
                 "us_per_launch": round(dom_s * 1e6, 2), "kernel_us": kern,
                 "whole_step": {"algorithmic_bytes": step_bytes, "formula": "16*P + 8*B*d0 (SURVEY 8d)",
                                "achieved": round(step_bytes / (ms * 1e-3 / K) / 1e9, 1),

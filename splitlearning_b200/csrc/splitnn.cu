@@ -967,7 +967,9 @@ static int bob_train_step_impl(sn_bob* h, int slot, const float* act, const int6
   if (!ce_fused &&
       launch_ce(z, Ch, labels, B * h->heads, Ch, h->dZ[h->L], Ch, h->row_loss, h->ticket, loss_out, nullptr, st))
     return 1;
-  return bob_backward_dispatch(h, slot, act, B, cut_grad, st, next_act, next_B);
+  const int rc = bob_backward_dispatch(h, slot, act, B, cut_grad, st, next_act, next_B);
+  h->stashed = false;            // the stashed activations have been consumed
+  return rc;
 }
 
 int sn_bob_train_step(sn_bob* h, int slot, const float* act, const int64_t* labels, int B,
@@ -1005,6 +1007,9 @@ int sn_bob_backward_update(sn_bob* h, int slot, const float* act, const float* d
   } else {
     SN_CUDA(cudaMemcpyAsync(h->dZ[h->L], dout, n * 4, cudaMemcpyDeviceToDevice, st));
   }
+  // one backward per stashed forward: a second one would, for a single-layer net, start reading the
+  // weights before its predecessor - the first backward - has finished writing them (PDL prologue)
+  h->stashed = false;
   return bob_backward_dispatch(h, slot, act, B, cut_grad, st);
 }
 

@@ -13,7 +13,11 @@
  *     holds a message.  Nothing falls back to the CPU.
  *   - calls that take `stream` only enqueue work on that cudaStream_t (pass it as void*;
  *     NULL = legacy default stream) and return without synchronising.
- *   - a handle lives on one device; calls switch to that device themselves.
+ *   - a handle lives on one device; calls switch to that device themselves.  The kernels of a
+ *     step overlap their prologues with the previous launch (programmatic dependent launch) and
+ *     the library tracks, per DEVICE, whether that previous launch may be writing the weights the
+ *     next one wants to prefetch - which assumes the library's work on one device is enqueued on
+ *     one stream at a time.  Order different streams on one device with events yourself.
  *   - weights are [out,in] row-major fp32, exactly PyTorch's nn.Linear / nn.Conv2d layout, and
  *     are OWNED BY THE CALLER (bound by pointer, updated in place); optimizer state,
  *     activations kept for the backward pass and split-K scratch are owned by the handle.
@@ -276,6 +280,14 @@ int sn_flag_wait_many(const void* flags, int count, int stride_bytes, uint32_t v
 /* One gate launch that sets `count` (<= 128) flags whose addresses are in a DEVICE array (one flag
  * in each consumer's own memory). */
 int sn_flag_signal_many(const void* flag_table_dev, int count, uint32_t value, void* stream);
+/* A gate kernel does not poll for ever: after SN_FLAG_TIMEOUT_MS (environment, default 20000; 0 = no
+ * limit) it gives up, records which flag it was waiting on in pinned host memory and lets the stream
+ * run on.  sn_flag_status() returns non-zero (message in sn_last_error()) once that has happened in
+ * this process - results computed after the timed-out wait are invalid - and every later
+ * sn_flag_wait* call fails the same way until sn_flag_status_clear().  The reference's analogue is
+ * the 60 s RPC timeout of TensorPipe raising at the caller. */
+int sn_flag_status(void);
+int sn_flag_status_clear(void);
 
 /* ------------------------------------------------------------------ tensor-parallel first layer
  * the server step is a weight stream, and the first layer is 84 % of it, so its

@@ -76,6 +76,8 @@ SIGNATURES = {
     "sn_tp_server_epoch": (_i, [_vp, _vp, _i, _i, _vp, _vp, C.POINTER(_i64), _i, _pp, _u64, _u64, _vp, _vp, _vp, _vp,
                                 _vp, _vp, C.c_uint32, _vp, _vp]),
     "sn_flag_signal_many": (_i, [_vp, _i, C.c_uint32, _vp]),
+    "sn_flag_status": (_i, []),
+    "sn_flag_status_clear": (_i, []),
 }
 
 _lib = None

@@ -15,6 +15,7 @@ constexpr int kConvParams = 320; // 32*9 weights + 32 biases
 
 extern thread_local std::string g_last_error;
 extern std::atomic<uint64_t> g_launches;
+extern thread_local cudaError_t g_launch_status;
 
 inline int fail(const char* what, cudaError_t e, const char* file, int line) {
   char buf[512];
@@ -33,11 +34,15 @@ inline int fail_msg(const std::string& msg) {
     if (e_ != cudaSuccess) return sn::fail(#expr, e_, __FILE__, __LINE__); \
   } while (0)
 
+// after a launch_k(): the launch call's own status first, then any sticky error; only a launch
+// that went through is counted
 #define SN_LAUNCH_CHECK()                                               \
   do {                                                                  \
-    sn::g_launches.fetch_add(1, std::memory_order_relaxed);             \
-    cudaError_t e_ = cudaGetLastError();                                \
+    cudaError_t e_ = sn::g_launch_status;                               \
+    sn::g_launch_status = cudaSuccess;                                  \
+    if (e_ == cudaSuccess) e_ = cudaGetLastError(); else cudaGetLastError(); \
     if (e_ != cudaSuccess) return sn::fail("kernel launch", e_, __FILE__, __LINE__); \
+    sn::g_launches.fetch_add(1, std::memory_order_relaxed);             \
   } while (0)
 
 #define SN_REQUIRE(cond, msg)                                           \
@@ -126,15 +131,37 @@ __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.laun
 // prologue (weight prefetch) while the waiter polls.  A stream-ordered cuStreamWaitValue32 pair in
 // the same place costs ~20 us per hop (front-end semaphore latency), these ~3.
 // thread i < count polls flag[i * stride_words]: one launch can wait for `count` producers
-__global__ void flag_wait_kernel(const unsigned* flag, unsigned value, int count, int stride_words) {
+// The wait is bounded: a producer that died would otherwise wedge this GPU for good.  After
+// `timeout_ns` of %globaltimer the waiter gives up, writes {1, value, last value seen, index} to
+// `err` (pinned host memory mapped into every device, read by the next library call on the host:
+// sn_flag_status) and lets the stream run on - whatever follows computes on stale data, and the
+// host is told.
+__global__ void flag_wait_kernel(const unsigned* flag, unsigned value, int count, int stride_words,
+                                 unsigned long long timeout_ns, unsigned* err) {
   pdl_wait();
   pdl_launch();
   if ((int)threadIdx.x < count) {
     const unsigned* f = flag + (size_t)threadIdx.x * stride_words;
     unsigned cur;
-    do {
+    unsigned long long t0 = 0, now = 0;
+    unsigned spins = 0;
+    for (;;) {
       asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(cur) : "l"(f) : "memory");
-    } while ((int)(cur - value) < 0);
+      if ((int)(cur - value) >= 0) break;
+      if ((++spins & 1023u) == 0 && timeout_ns) {       // the timer is read once per ~1k polls
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > timeout_ns) {
+          if (err) {
+            err[1] = value; err[2] = cur; err[3] = threadIdx.x;
+            __threadfence_system();
+            *reinterpret_cast<volatile unsigned*>(err) = 1u;
+            __threadfence_system();
+          }
+          break;
+        }
+      }
+    }
   }
 }
 // optional small copy (labels) into the peer's mailbox, then the flag: everything the stream did

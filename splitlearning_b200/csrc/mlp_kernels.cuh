@@ -126,8 +126,11 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
 
   const int groups = (N + R - 1) / R;
   const long long T = (long long)groups * iters;
-  const int gw = blockIdx.x * WPC + warp, nw = gridDim.x * WPC;
-  const int t0 = (int)(T * gw / nw), t1 = (int)(T * (gw + 1) / nw);
+  // a warp's range must be at least one row group long, or a group could be cut into three or more
+  // pieces and two of them would share partial slot 1: with fewer groups than warps (a narrow layer)
+  // only the first `groups` warps take work
+  const int gw = blockIdx.x * WPC + warp, nw = min((int)gridDim.x * WPC, groups);
+  const int t0 = gw < nw ? (int)(T * gw / nw) : (int)T, t1 = gw < nw ? (int)(T * (gw + 1) / nw) : (int)T;
 
   const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
   const bool ktail = (klen & 127) != 0;      // only then can a lane sit beyond the end of K

@@ -27,7 +27,7 @@ static int sm_count(int device) {
   static int cache[64] = {0};
   if (device >= 0 && device < 64 && cache[device]) return cache[device];
   int n = 148;
-  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) n = 148;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { n = 148; cudaGetLastError(); }
   if (device >= 0 && device < 64) cache[device] = n;
   return n;
 }
@@ -167,9 +167,41 @@ struct Profiler {
 // All kernels go through launch_k: cudaLaunchKernelEx with programmatic stream serialization, so a
 // kernel's prologue overlaps its predecessor's tail (see pdl_wait/pdl_launch in common.cuh).
 // SN_NO_PDL=1 in the environment turns the attribute off for A/B timing.
+// Status of the most recent cudaLaunchKernelEx on this thread; SN_LAUNCH_CHECK reports it.
+thread_local cudaError_t g_launch_status = cudaSuccess;
+
+// Which weights did the most recent library launch on each device write?  A streaming kernel may
+// start reading its weights BEFORE its dependency wait only when the launch right before it on the
+// device cannot be writing them.  The record is per device, not per handle: several handles may be
+// bound to the same tensors (a training engine and an inference engine over one module).  Every
+// launch clears it; a launch that updates weights sets it again afterwards (mark_written).  One host
+// thread drives a device and the library's launches on it go to one stream at a time; callers that
+// interleave streams on one device must order them themselves (include/splitnn.h).
+struct WrittenRange { const char* lo; const char* hi; };
+static WrittenRange g_written[64] = {};
+static inline int cur_device() {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess) { cudaGetLastError(); d = 0; }
+  return d;
+}
+static inline void mark_written(const void* p, size_t bytes) {
+  const int d = cur_device();
+  if (d >= 0 && d < 64) g_written[d] = WrittenRange{static_cast<const char*>(p), static_cast<const char*>(p) + bytes};
+}
+static inline bool just_written(const void* p, size_t bytes) {
+  const int d = cur_device();
+  if (d < 0 || d >= 64) return true;
+  const char* lo = static_cast<const char*>(p);
+  return g_written[d].lo && lo < g_written[d].hi && g_written[d].lo < lo + bytes;
+}
+
 template <typename... P, typename... A>
 static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args) {
   static const bool pdl = getenv("SN_NO_PDL") == nullptr;
+  {
+    const int d = cur_device();
+    if (d >= 0 && d < 64) g_written[d] = WrittenRange{nullptr, nullptr};
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -180,7 +212,7 @@ static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t 
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
-  cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);
+  g_launch_status = cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);
 }
 
 // ---------------------------------------------------------------- shared launch helpers
@@ -343,7 +375,6 @@ struct sn_bob {
   float* dWbuf = nullptr;      // general-batch path only (lazy)
   float* row_loss = nullptr;
   unsigned* ticket = nullptr;
-  int last_writer = -1;        // layer whose weights the most recent launch on this handle updated (-1: none)
   float* const* cut_table = nullptr;   // tensor-parallel head: per-consumer destinations of the cut gradient's columns
   int cut_cols = 1;
   bool stashed = false;
@@ -368,7 +399,6 @@ struct sn_alice {
   float* dact = nullptr;
   float* row_loss = nullptr;
   int gx = 1;
-  bool bwd_last = false;                // the last launch on this handle was the weight update
 };
 
 // One row slice of a Linear layer with its optimizer state: the unit of the tensor-parallel first
@@ -418,7 +448,7 @@ int sn_conv_pool_forward(const float* x, const float* w, const float* b, int B, 
 }
 
 size_t sn_conv_pool_backward_scratch_bytes(int B) {
-  int gx = conv_bwd_gx(std::max(B, 1), 148);
+  int gx = conv_bwd_gx(std::max(B, 1), sm_count(cur_device()));
   return (size_t)gx * kConvParams * 4 + 256;
 }
 
@@ -426,7 +456,7 @@ int sn_conv_pool_backward(const float* x, const float* w, const float* b, const 
                           float* db, void* scratch, void* stream) {
   SN_REQUIRE(x && w && b && dact && dw && db && scratch && B > 0, "sn_conv_pool_backward: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
-  int gx = conv_bwd_gx(B, 148);
+  int gx = conv_bwd_gx(B, sm_count(cur_device()));
   unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
   SN_CUDA(cudaMemsetAsync(ticket, 0, 256, st));
@@ -439,7 +469,7 @@ int sn_conv_pool_backward(const float* x, const float* w, const float* b, const 
 
 size_t sn_linear_forward_scratch_bytes(int B, int K, int N) {
   if (B <= 0 || K <= 0 || N <= 0) return 16;
-  return std::max<size_t>(16, fwd_partial_floats(B, K, N, 148) * 4);
+  return std::max<size_t>(16, fwd_partial_floats(B, K, N, sm_count(cur_device())) * 4);
 }
 
 int sn_linear_forward(const float* x, const float* W, const float* bias, int B, int K, int N, int relu,
@@ -761,12 +791,10 @@ static int bob_forward_impl(sn_bob* h, const float* act, int B, int train, const
       launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, h->sms)), dim3(256), 0, st, h->PF, ceil_div(K, 128), kBT, B, N,
                h->b[l], relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N, last ? out : nullptr, 0, 0);
       SN_LAUNCH_CHECK();
-      h->last_writer = -1;
     } else if (launch_linear_fwd(X, ldx, B, h->W[l], h->b[l], K, N, relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N,
                                  last ? out : nullptr, h->P, h->sms, st, &h->prof, last ? ce : nullptr,
-                                 last ? ce_fused : nullptr, h->l2_keep[l], h->last_writer != l))
+                                 last ? ce_fused : nullptr, h->l2_keep[l], !just_written(h->W[l], (size_t)N * K * 4)))
       return 1;
-    h->last_writer = -1;
     X = h->H[l + 1];
     ldx = N;
   }
@@ -789,7 +817,8 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
     float* dst = l > 0 ? h->dZ[l] : cut_grad;
     const float* gateH = l > 0 ? h->H[l] : nullptr;
     const float gscale = (l > 0 && h->dropout_p > 0.f) ? scale : 1.f;
-    h->last_writer = l;        // reset below where a non-updating launch (the dA reduction) comes last
+    // every branch ends with mark_written(W[l]) unless a non-updating launch (the dA reduction) comes last
+    const size_t wbytes = (size_t)N * K * 4;
     if (B <= kBT && (size_t)N * K <= kSmallLayerElems && N <= 8 * kSmallBwdRows) {
       // tiny layer: one launch, no n split, gate applied in place (bwd_small_kernel)
       cudaEvent_t pe = h->prof.begin(st, 1, l);
@@ -801,6 +830,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
                  s.s2[2 * l], s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, op, 0, 1.f, (float*)nullptr, K);
       Profiler::end(pe, st);
       SN_LAUNCH_CHECK();
+      mark_written(h->W[l], wbytes);
     } else if (B <= kBT && (K % 4) == 0) {
       BwdPlan p = plan_bwd(N, K, h->sms, need_da, OPT == 2);
       size_t smem = bwd_smem_bytes(p, need_da, OPT == 2);
@@ -817,7 +847,6 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, p.nsplit, B, K, gateH, K,
                  gscale, dst, K, l == 0 ? h->cut_table : (float* const*)nullptr, h->cut_cols);
         SN_LAUNCH_CHECK();
-        h->last_writer = -1;
       } else if (l == 0 && next_act && next_B > 0 && next_B <= kBT && (size_t)N * K > kSmallLayerElems) {
         // SISA: fuse the next step's layer-0 forward into this traversal
         if (!h->PF) SN_CUDA(cudaMalloc(&h->PF, (size_t)ceil_div(K, 128) * kBT * N * 4));
@@ -828,6 +857,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
                  next_act, next_B, h->PF, h->l2_keep[l], (const float*)nullptr, 1.f);
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
+        mark_written(h->W[l], wbytes);
         h->pf_valid = true;
       } else {
         if (set_smem(bwd_update_kernel<OPT, false>, smem)) return 1;
@@ -838,6 +868,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
                                                                h->l2_keep[l], (const float*)nullptr, 1.f);
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
+        mark_written(h->W[l], wbytes);
       }
     } else if (B <= kSkinnyFwdMaxB && (K % 4) == 0 && g_matmul_precision.load() != 2) {
       // 17..64 rows (--batch_size 32/64): still a weight stream, far below the tensor ridge.  The
@@ -883,7 +914,6 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
                s.s2[2 * l + 1], op);
       SN_LAUNCH_CHECK();
       Profiler::end(pe, st);
-      h->last_writer = -1;
     } else if (g_matmul_precision.load() != 2 && (K % 4) == 0 && (N % 4) == 0) {
       // tensor-bound regime (perf mode): dA, then dW fused with the optimizer, both on tcgen05
       if (need_da) {
@@ -903,6 +933,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
       int rc = launch_tc_gemm<true, true, tc::EPI_UPDATE, OPT>(dZ, N, N, A, K, K, B, h->W[l], K, eu, st);
       Profiler::end(pe, st);
       if (rc) return rc;
+      mark_written(h->W[l], wbytes);
     } else {
       // general-batch path: dA from W_old first, then dW into a buffer, then the updates
       if (!h->dWbuf) {
@@ -930,7 +961,6 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, 1, B, K, gateH, K, gscale, dst, K,
                  l == 0 ? h->cut_table : (float* const*)nullptr, h->cut_cols);
         SN_LAUNCH_CHECK();
-        h->last_writer = -1;
       }
     }
   }
@@ -1134,7 +1164,6 @@ int sn_alice_forward(sn_alice* h, const float* x, int B, float* act, void* strea
   dim3 grid(std::min(B, h->sms * 4), 4);
   launch_k(conv_pool_fwd_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, x, h->w, h->b, B, act);
   SN_LAUNCH_CHECK();
-  h->bwd_last = false;
   return 0;
 }
 
@@ -1146,8 +1175,7 @@ static int alice_bwd(sn_alice* h, const float* x, const float* dact, int B, cuda
   SN_REQUIRE((int)grid.x <= h->gx, "internal: conv backward grid exceeds scratch");
   // the kernel may read the weights before its dependency wait unless the launch right before it
   // could be this Alice's previous weight update (two backward calls in a row)
-  const int early = h->bwd_last ? 0 : 1;
-  h->bwd_last = true;
+  const int early = just_written(h->w, 288 * 4) ? 0 : 1;
   switch (h->hyper.type) {
     case SN_OPT_SGD_MOMENTUM:
       launch_k(conv_pool_bwd_kernel<1>, dim3(grid), dim3(256), 0, st, x, h->w, h->b, dact, B, h->partial, h->ticket, nullptr, nullptr,
@@ -1161,6 +1189,7 @@ static int alice_bwd(sn_alice* h, const float* x, const float* dact, int B, cuda
       return fail_msg("libsplitnn: this sn_alice was created without an optimizer");
   }
   SN_LAUNCH_CHECK();
+  mark_written(h->w, 288 * 4);
   return 0;
 }
 
@@ -1181,7 +1210,6 @@ int sn_alice_local_step(sn_alice* h, const float* x, const int64_t* labels, int 
   dim3 grid(std::min(B, h->sms * 4), 4);
   launch_k(conv_pool_fwd_kernel, dim3(grid), dim3(256), 0, st, x, h->w, h->b, B, h->act);
   SN_LAUNCH_CHECK();
-  h->bwd_last = false;
   if (launch_ce(h->act, kD0, labels, B, kD0, h->dact, kD0, h->row_loss, h->ticket + 1, loss_out, nullptr, st)) return 1;
   return alice_bwd(h, x, h->dact, B, st);
 }
@@ -1391,6 +1419,7 @@ static int shard_backward_impl(sn_shard* h, const float* X, const float* dH, int
     h->pf_valid = false;
   }
   SN_LAUNCH_CHECK();
+  mark_written(h->W, (size_t)N * K * 4);
   h->h_valid = false;
   return 0;
 }
@@ -1533,9 +1562,49 @@ int sn_flag_signal_many(const void* flag_table_dev, int count, uint32_t value, v
   SN_LAUNCH_CHECK();
   return 0;
 }
+// Error word of the gate kernels: 4 words of pinned host memory, mapped into every device.
+static unsigned* g_flag_err = nullptr;
+static std::mutex g_flag_err_mu;
+static unsigned* flag_err_word() {
+  std::lock_guard<std::mutex> lock(g_flag_err_mu);
+  if (!g_flag_err) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    memset(p, 0, 64);
+    g_flag_err = static_cast<unsigned*>(p);
+  }
+  return g_flag_err;
+}
+static unsigned long long flag_timeout_ns() {
+  // SN_FLAG_TIMEOUT_MS: how long a gate kernel polls before it gives up (default 20 s; 0 = for ever)
+  static const unsigned long long ns = [] {
+    const char* e = getenv("SN_FLAG_TIMEOUT_MS");
+    const double ms = e ? atof(e) : 20000.0;
+    return ms <= 0 ? 0ull : (unsigned long long)(ms * 1e6);
+  }();
+  return ns;
+}
+static int flag_check() {
+  unsigned* e = g_flag_err;
+  if (e && *reinterpret_cast<volatile unsigned*>(e)) {
+    const unsigned want = e[1], seen = e[2], idx = e[3];
+    return fail_msg("libsplitnn: a flag wait timed out on the GPU (waiting for value " + std::to_string(want) + ", flag " +
+                    std::to_string(idx) + " still held " + std::to_string(seen) +
+                    "): the peer that should have signalled is gone or stuck; results after that point are invalid");
+  }
+  return 0;
+}
+int sn_flag_status(void) { return flag_check(); }
+int sn_flag_status_clear(void) {
+  if (g_flag_err) memset(g_flag_err, 0, 64);
+  return 0;
+}
+
 int sn_flag_wait(const void* flag, uint32_t value, void* stream) {
   SN_REQUIRE(flag && (reinterpret_cast<uintptr_t>(flag) & 3) == 0, "sn_flag_wait: flag must be a 4-byte aligned device address");
-  launch_k(flag_wait_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, reinterpret_cast<const unsigned*>(flag), (unsigned)value, 1, 0);
+  if (flag_check()) return 2;
+  launch_k(flag_wait_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, reinterpret_cast<const unsigned*>(flag), (unsigned)value, 1, 0,
+           flag_timeout_ns(), flag_err_word());
   SN_LAUNCH_CHECK();
   return 0;
 }
@@ -1543,8 +1612,9 @@ int sn_flag_wait_many(const void* flags, int count, int stride_bytes, uint32_t v
   SN_REQUIRE(flags && (reinterpret_cast<uintptr_t>(flags) & 3) == 0 && count >= 1 && count <= 32 && stride_bytes >= 4 &&
                  (stride_bytes & 3) == 0,
              "sn_flag_wait_many: 1..32 flags, 4-byte aligned, stride a multiple of 4 bytes");
+  if (flag_check()) return 2;
   launch_k(flag_wait_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, reinterpret_cast<const unsigned*>(flags), (unsigned)value,
-           count, stride_bytes / 4);
+           count, stride_bytes / 4, flag_timeout_ns(), flag_err_word());
   SN_LAUNCH_CHECK();
   return 0;
 }

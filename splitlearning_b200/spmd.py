@@ -43,11 +43,15 @@ def pack_message(B, device):
 
 
 def run_vanilla_schedule(rank, world, bob, alices, batch_fn, n_alices, turn, first_step, n_steps, B, device,
-                         loss_sink=None, link=None):
+                         loss_sink=None, link=None, rows_fn=None):
     """Walk steps [first_step, first_step+n_steps) of the round-robin schedule.
 
     bob: engine or None (ranks != 0); alices: {alice_index: engine} for the Alices this rank hosts;
     batch_fn(i) -> (x, y) device tensors for step i (only called on the owning rank).
+    rows_fn(i) -> rows of step i's batch (1..B), evaluated on EVERY rank: the mailboxes and messages
+    are B rows deep, and Bob - who never sees Alice's loader - must know how many of them belong to
+    a short last batch (the reference's DataLoader has no drop_last).  None = every batch has B rows,
+    and a batch_fn that returns anything else is refused.
     link: a peer.PeerLink (CUDA IPC mailboxes: the kernels write straight into the consumer's GPU and
     4-byte flags order the streams) or None for send/recv messages (NCCL; gloo in the CPU tests)."""
     msg, act_view, lab_view = pack_message(B, device)
@@ -70,30 +74,39 @@ def run_vanilla_schedule(rank, world, bob, alices, batch_fn, n_alices, turn, fir
                     alices[k].set_weights(wbuf)
         if link is not None:
             link.next_step()
-        if world == 1:
+        n = B if rows_fn is None else int(rows_fn(i))
+        if not 1 <= n <= B:
+            raise ValueError(f"step {i}: rows_fn gave {n} rows, mailboxes hold 1..{B}")
+        if rank == own or world == 1:
             x, y = batch_fn(i)
+            if x.shape[0] != n:
+                raise ValueError(f"step {i}: batch_fn returned {x.shape[0]} rows where every rank expects {n} "
+                                 "(pass rows_fn for ragged batches)")
+        if world == 1:
             act = alices[k].forward(x)
             loss, g, _ = bob.train_step(act, y, slot=k)
             alices[k].backward_update(x, g)
         elif link is not None and rank == own:
-            x, y = batch_fn(i)
             alices[k].forward(x, out=link.alice_targets())       # the conv kernel stores into Bob's GPU
-            link.alice_publish(y, x.shape[0])
-            alices[k].backward_update(x, link.alice_wait_cut()[:x.shape[0]])
+            link.alice_publish(y, n)
+            alices[k].backward_update(x, link.alice_wait_cut()[:n])
         elif link is not None and rank == 0:
             act, lab = link.bob_wait_batch()
-            loss, g, _ = bob.train_step(act, lab, slot=k, cut_out=link.bob_cut_target(own))   # ... and Bob's last kernel into Alice's
+            # ... and Bob's last kernel stores the n cut-gradient rows into Alice's GPU
+            loss, g, _ = bob.train_step(act[:n], lab[:n], slot=k, cut_out=link.bob_cut_target(own))
             link.bob_publish_cut(own)
         elif rank == own:
-            x, y = batch_fn(i)
-            alices[k].forward(x, out=act_view)
-            lab_view.copy_(y)
+            alices[k].forward(x, out=act_view[:n])
+            lab_view[:n].copy_(y)
             dist.send(msg, dst=0)
             dist.recv(cut, src=0)
-            alices[k].backward_update(x, cut)
+            alices[k].backward_update(x, cut[:n])
         elif rank == 0:
             dist.recv(msg, src=own)
-            loss, g, _ = bob.train_step(act_view, lab_view, slot=k)
+            loss, g, _ = bob.train_step(act_view[:n], lab_view[:n], slot=k)
+            if n < B:                                            # the reply is always B rows deep
+                cut[:n].copy_(g)
+                g = cut
             dist.send(g, dst=own)
         else:
             continue

@@ -62,7 +62,11 @@ def test_conv_pool_backward(eng, B):
 
 @pytest.mark.parametrize("B,K,N,relu", [(16, 5408, 5000, True), (16, 5000, 1000, True), (16, 1000, 100, False),
                                         (3, 5408, 1000, True), (16, 100, 10, False), (40, 1000, 100, True),
-                                        (100, 512, 104, False), (7, 52, 12, True)])
+                                        (100, 512, 104, False), (7, 52, 12, True),
+                                        # narrow layers with a long reduction: fewer row groups than warps
+                                        # (a group cut into 3+ pieces used to lose partial sums)
+                                        (16, 40000, 10, False), (16, 65536, 40, True), (5, 39940, 24, False),
+                                        (16, 2112, 4, False)])
 def test_linear_forward(eng, B, K, N, relu):
     rng = np.random.RandomState(B + K + N)
     x = (rng.rand(B, K) * 50 * (rng.rand(B, K) < 0.6)).astype(np.float32)

@@ -69,7 +69,12 @@ def _batches():
     return x, y
 
 
-def _run(rank, world, out_dir, port):
+def _rows(i):
+    """A short batch every third step (the reference's loaders have no drop_last)."""
+    return B if i % 3 else B - 1 - (i % 2)
+
+
+def _run(rank, world, out_dir, port, ragged=False):
     if world > 1:
         os.environ["MASTER_ADDR"] = "127.0.0.1"
         os.environ["MASTER_PORT"] = str(port)
@@ -79,8 +84,12 @@ def _run(rank, world, out_dir, port):
     bob = FakeBob() if rank == 0 else None
     mine = {k: FakeAlice(100 + k) for k in range(N_ALICES) if spmd.owner_rank(k, world) == rank}
     losses = {}
-    spmd.run_vanilla_schedule(rank, world, bob, mine, lambda i: (x[i], y[i]), N_ALICES, TURN, 0, STEPS, B,
-                              torch.device("cpu"), lambda i, l: losses.__setitem__(i, float(l)))
+    if ragged:
+        spmd.run_vanilla_schedule(rank, world, bob, mine, lambda i: (x[i][:_rows(i)], y[i][:_rows(i)]), N_ALICES, TURN, 0,
+                                  STEPS, B, torch.device("cpu"), lambda i, l: losses.__setitem__(i, float(l)), rows_fn=_rows)
+    else:
+        spmd.run_vanilla_schedule(rank, world, bob, mine, lambda i: (x[i], y[i]), N_ALICES, TURN, 0, STEPS, B,
+                                  torch.device("cpu"), lambda i, l: losses.__setitem__(i, float(l)))
     out = {f"alice{k}": a.get_weights().numpy() for k, a in mine.items()}
     if bob is not None:
         out.update({f"bob{i}": p.numpy() for i, p in enumerate(bob.p)})
@@ -111,6 +120,22 @@ def test_spmd_protocol_matches_single_process(world):
     assert got["slots"].tolist() == [(i // TURN) % N_ALICES for i in range(STEPS)]
     for k in ref:
         assert np.array_equal(got[k], ref[k]), k
+
+
+def test_spmd_ragged_batches_reach_bob_with_their_row_count():
+    """Short batches: Bob must train on exactly the rows Alice sent, not on the stale tail of the
+    B-row message buffer (and a batch_fn that disagrees with rows_fn is refused)."""
+    with tempfile.TemporaryDirectory() as d:
+        _run(0, 1, d, 0, True)
+        ref = _collect(d, 1)
+        mp.spawn(_run, args=(2, d, 29711, True), nprocs=2, join=True)
+        got = _collect(d, 2)
+    for k in ref:
+        assert np.array_equal(got[k], ref[k]), k
+    x, y = _batches()
+    with pytest.raises(ValueError, match="rows_fn"):
+        spmd.run_vanilla_schedule(0, 1, FakeBob(), {k: FakeAlice(k) for k in range(N_ALICES)},
+                                  lambda i: (x[i][:2], y[i][:2]), N_ALICES, TURN, 0, 1, B, torch.device("cpu"))
 
 
 def test_owner_placement():

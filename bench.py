@@ -28,7 +28,6 @@ B = 16
 D0 = 5408
 DIMS = [5408, 5000, 1000, 100]
 N_ALICES = 4
-TURN = 64                     # steps an Alice trains before the next one takes over
 P_BOB = sum(DIMS[i] * DIMS[i + 1] + DIMS[i + 1] for i in range(3))        # 32,146,100
 P_FC1 = DIMS[0] * DIMS[1]
 L2_MB = 126
@@ -92,44 +91,72 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------- reference arm
+REF_MAX_STEPS = 300           # the RPC reference runs ~150 ms per step: keep the arm within a few minutes
+
+
+def turn_for(steps):
+    """Steps an Alice trains before the next one takes over.  The driver's short run (20 steps) must
+    still see every Alice train and time Alice->Alice hand-offs; long runs use 64."""
+    return max(1, min(64, steps // N_ALICES))
+
+
 def run_reference(args):
-    """`--impl reference`: the reference's CPU path on the box's host cores.  /root/reference cannot
-    travel to the GPU box and is not pip-installable (no setup.py), so this times the oracle's
-    torch-CPU port of the same step (oracle/cpu_baseline.py; no RPC -> faster than the original)."""
+    """`--impl reference`: the reference's own CPU path on the box's host cores.  When the copy of
+    the unmodified reference is present (oracle/_ref, made by oracle/fetch_ref.sh in the build
+    container; it travels with the snapshot) this runs its alice/bob entity classes under
+    torch.distributed.rpc in 5 processes (oracle/ref_runner.py) - kind "reference".  Without it, the
+    torch-CPU port of the same step (oracle/cpu_baseline.py; no RPC, so faster) - kind "port"."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import torch
-    from oracle import cpu_baseline as cb
-    w = cb.VanillaCPU(n_alices=N_ALICES, batch=B)
-    # torchrun pins OMP_NUM_THREADS=1; the reference as shipped lets torch use the host's cores.
-    # Try the plausible intra-op thread counts for a few steps each and keep the fastest.
-    ncpu = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    best = None
-    for nt in sorted({ncpu, max(1, ncpu * 2 // 3), max(1, ncpu // 2)}):
-        torch.set_num_threads(nt)
-        t = cb.time_steps(w, 3, 1)
-        if best is None or t < best[0]:
-            best = (t, nt)
-    torch.set_num_threads(best[1])
-    dt = cb.time_steps(w, args.steps, args.warmup)
-    value = args.steps * B / dt
+    from oracle import ref_runner
+    ncpu = ref_runner.host_threads()
+    extra = {}
+    if ref_runner.available():
+        k = min(args.steps, REF_MAX_STEPS)
+        r = ref_runner.time_vanilla_rpc(k, args.warmup, world=N_ALICES + 1, batch=B, threads=ncpu)
+        value, dt, steps, threads = r["samples_per_s"], r["seconds"], r["steps"], r["threads"]
+        kind = "reference"
+        sample = (f"{steps} vanilla split steps of B={B} after {r['warmup']} warm-up steps through the UNMODIFIED reference: "
+                  f"data_entities_vanilla.alice/bob in {N_ALICES + 1} processes over torch.distributed.rpc + dist_autograd + "
+                  f"DistributedOptimizer, {threads} intra-op threads per process (torch default = all cores), "
+                  f"LDA-partitioned synthetic shards {r['shard_train_sizes']}")
+        if steps < args.steps:
+            sample += f"; capped from --steps {args.steps} to keep the arm within minutes"
+        extra = {"world_size": N_ALICES + 1}
+    else:
+        from oracle import cpu_baseline as cb
+        w = cb.VanillaCPU(n_alices=N_ALICES, batch=B)
+        # torchrun pins OMP_NUM_THREADS=1; the reference as shipped lets torch use the host's cores.
+        best = None
+        for nt in sorted({ncpu, max(1, ncpu * 2 // 3), max(1, ncpu // 2)}):
+            torch.set_num_threads(nt)
+            t = cb.time_steps(w, 3, 1)
+            if best is None or t < best[0]:
+                best = (t, nt)
+        torch.set_num_threads(best[1])
+        steps = args.steps
+        dt = cb.time_steps(w, steps, args.warmup)
+        value, threads, kind = steps * B / dt, best[1], "port"
+        sample = f"{steps} vanilla split steps of B={B} on torch-CPU, single process, no RPC (oracle/_ref absent)"
     line = {
         "impl": "reference", "metric": "split_nn_train_samples_per_sec", "value": value, "unit": "samples/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.gpus),
-        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": "port",
-                         "sample": f"{args.steps} vanilla split steps of B={B} on torch-CPU, single process, no RPC"},
+        "config": workload_config(args.gpus, turn_for(args.steps)),
+        "cpu_baseline": dict({"value": value, "unit": "samples/s", "cores": threads, "kind": kind, "sample": sample}, **extra),
         "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "host": {"cpu_count": os.cpu_count(), "torch_threads": torch.get_num_threads()},
+        "host": {"cpu_count": os.cpu_count(), "usable_threads": ncpu},
     }
     print(json.dumps(line))
 
 
-def workload_config(n_gpus):
+def workload_config(n_gpus, turn=64):
     return {"workload": "--vanilla split NN, world_size=5 (1 Bob + 4 Alices round-robin), batch 16, "
-                        "model1_sisa + model2_sisa 5408-5000-1000-100, SGD momentum 0.9 per Alice, lr 1e-3",
+                        "model1_sisa + model2_sisa 5408-5000-1000-100, SGD momentum 0.9 per Alice, lr 1e-3; "
+                        f"each Alice trains {turn} steps, then hands her weights to the next (every Alice trains and "
+                        "hand-offs fall inside the timed window)",
             "global_batch": B, "parallelism": "single GPU" if n_gpus == 1 else f"Bob on rank 0 + Alices on ranks 1..{n_gpus - 1}",
             "l2": f"per-step working set {20 * P_BOB / 1e6:.0f} MB (weights + momentum) > {L2_MB} MB L2: no flush needed",
             "dropout": "in-kernel Philox (perf mode)"}
@@ -177,6 +204,8 @@ def run_ours_single(args):
     from splitlearning_b200 import engine as E
     act_buf = torch.empty(B, D0, device=dev)
     cut_buf = torch.empty(B, D0, device=dev)
+
+    TURN = turn_for(args.steps)
 
     def step(i, x, y, loss_out):
         k = (i // TURN) % N_ALICES
@@ -257,11 +286,9 @@ def run_ours_single(args):
     step_bytes = 16.0 * P_BOB + 8.0 * B * D0
     roofline = {"bound": "hbm", "kernel": "bwd_update_kernel<SGD,dA> fc1 (5000x5408): dW+dX+momentum update in one traversal",
                 "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the committed
-                # `ncu --set full` capture (profiles/r1c_kernels_ncu_full.csv): 217.06 MB read + 140.41 MB
-                # written; the rest of the 216 MB of writes is still in L2 at exit (evict_last rows,
-                # dirty lines)
-                "traffic": 357466112.0, "peak_source": peak_src, "bytes_per_launch": dom_bytes,
+                # dram bytes of this kernel per launch from the committed `ncu --set full` capture; null
+                # when the kernel sources changed after it was taken (profiles/ncu_traffic.json)
+                "traffic": ncu_traffic("bwd_update_sgd_da_fc1"), "peak_source": peak_src, "bytes_per_launch": dom_bytes,
                 "us_per_launch": round(dom_s * 1e6, 2), "kernel_us": kern,
                 "whole_step": {"algorithmic_bytes": step_bytes, "formula": "16*P + 8*B*d0 (SURVEY 8d)",
                                "achieved": round(step_bytes / (ms * 1e-3 / K) / 1e9, 1),
@@ -270,25 +297,77 @@ def run_ours_single(args):
     # ---- SISA server epoch (BASELINE.json's second number), same process
     sisa = run_sisa_epoch(torch, dev, peak)
 
+    # ---- SISA --concat server (BASELINE.json configs[3] shape) on this GPU
+    from splitlearning_b200 import spmd
+    sisa_concat = spmd.bench_sisa_concat(0, 1, dev, B, peak)
+
     # ---- CPU baseline on the host cores (bounded sample)
-    from oracle import cpu_baseline as cb
-    v, n, dt, thr = cb.bounded(cb.VanillaCPU, budget_s=12.0, n_alices=N_ALICES, batch=B)
-    cpu = {"value": round(v, 1), "unit": "samples/s", "cores": thr, "kind": "port",
-           "sample": f"{n} vanilla split steps of B={B} ({dt:.1f} s) on torch-CPU, single process, no RPC"}
-    v2, n2, dt2, _ = cb.bounded(cb.SisaServerCPU, budget_s=8.0, batch=B)
-    sisa["cpu_baseline_ms_per_step"] = round(1e3 * B / v2, 2)
-    sisa["cpu_sample"] = f"{n2} SISA server steps of B={B} ({dt2:.1f} s), Adam wd 1e-5"
+    cpu, sisa_cpu = cpu_baselines()
+    sisa.update(sisa_cpu)
 
     line = {
         "metric": "split_nn_train_samples_per_sec", "value": round(value, 1), "unit": "samples/s", "n_gpus": 1,
         "steps": K, "warmup": W, "ms_per_step": round(ms / K, 5), "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(1),
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(1, TURN),
         "clocks": clk.summary(), "gpu_launches": int(launches),
         "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "h2d_bytes_per_step": B * 784 * 4 + B * 8,
                 "d2h_bytes_per_step": 4, "ms_per_step": round(e2e_ms / K, 5)},
-        "roofline": roofline, "cpu_baseline": cpu, "sisa": sisa, "final_loss": final_loss,
+        "roofline": roofline, "cpu_baseline": cpu, "sisa": sisa, "sisa_concat": sisa_concat, "final_loss": final_loss,
     }
     print(json.dumps(line))
+
+
+def cpu_baselines():
+    """The timed CPU baseline next to the GPU numbers (rank 0, N=1 only; ~10 s + ~10 s of CPU work
+    plus process start-up).  With oracle/_ref present: the UNMODIFIED reference through its RPC path
+    (kind "reference"), and the single-process torch-CPU port as a second, labelled figure."""
+    from oracle import cpu_baseline as cb
+    from oracle import ref_runner
+    v, n, dt, thr = cb.bounded(cb.VanillaCPU, budget_s=6.0, n_alices=N_ALICES, batch=B)
+    port = {"value": round(v, 1), "unit": "samples/s", "cores": thr, "kind": "port",
+            "sample": f"{n} vanilla split steps of B={B} ({dt:.1f} s) on torch-CPU, single process, no RPC"}
+    v2, n2, dt2, _ = cb.bounded(cb.SisaServerCPU, budget_s=5.0, batch=B)
+    sisa_cpu = {"cpu_baseline_ms_per_step": round(1e3 * B / v2, 2), "cpu_kind": "port",
+                "cpu_sample": f"{n2} SISA server steps of B={B} ({dt2:.1f} s), Adam wd 1e-5, torch-CPU port"}
+    if not ref_runner.available():
+        return port, sisa_cpu
+    try:
+        r = ref_runner.time_vanilla_rpc(64, 4, world=N_ALICES + 1, batch=B)
+        cpu = {"value": round(r["samples_per_s"], 1), "unit": "samples/s", "cores": r["threads"], "kind": "reference",
+               "world_size": N_ALICES + 1,
+               "sample": f"{r['steps']} vanilla split steps of B={B} ({r['seconds']:.1f} s) through the unmodified reference "
+                         f"(data_entities_vanilla.py over torch.distributed.rpc, {N_ALICES + 1} processes, "
+                         f"{r['threads']} intra-op threads each)",
+               "port": port}
+        q = ref_runner.time_sisa_server(40, batch=B)
+        sisa_cpu = {"cpu_baseline_ms_per_step": round(q["ms_per_step"], 2), "cpu_kind": "reference",
+                    "cpu_sample": f"{q['steps']} steps of the reference's own bob.train_and_backward "
+                                  f"(data_entities_vanilla_sisa.py:294-315) on a pre-filled cache ({q['seconds']:.1f} s, "
+                                  f"{q['threads']} threads)",
+                    "cpu_port_ms_per_step": sisa_cpu["cpu_baseline_ms_per_step"]}
+        return cpu, sisa_cpu
+    except Exception as e:                                  # the RPC harness could not start here: say so, keep the port
+        port["reference_error"] = f"{type(e).__name__}: {e}"[:300]
+        return port, sisa_cpu
+
+
+def ncu_traffic(kernel_key):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel_key` from the committed ncu
+    capture (profiles/ncu_traffic.json, written by profiles/summarize.py from an `ncu --set full`
+    run), or None when the kernel sources have changed since that capture."""
+    import hashlib
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            tab = json.load(f)
+        h = hashlib.sha256()
+        for name in tab["sources"]:
+            with open(os.path.join(ROOT, name), "rb") as f:
+                h.update(f.read())
+        if h.hexdigest()[:16] != tab["source_sha16"]:
+            return None
+        return float(tab["kernels"][kernel_key]["dram_bytes_per_launch"])
+    except Exception:
+        return None
 
 
 def run_sisa_epoch(torch, dev, peak):
@@ -376,7 +455,8 @@ def run_sisa_epoch(torch, dev, peak):
 # ----------------------------------------------------------------------------------- our arm, N > 1
 def run_ours_multi(args):
     from splitlearning_b200 import spmd
-    spmd.bench_vanilla(args, B, N_ALICES, TURN, workload_config(args.gpus), measured_peak())
+    turn = turn_for(args.steps)
+    spmd.bench_vanilla(args, B, N_ALICES, turn, workload_config(args.gpus, turn), measured_peak())
 
 
 def main():

@@ -217,6 +217,13 @@ int sn_alice_set_opt_step(sn_alice* h, int64_t step);
 
 /* act [B,5408] may live on another device (peer-mapped) — e.g. directly in Bob's HBM. */
 int sn_alice_forward(sn_alice* h, const float* x, int B, float* act, void* stream);
+/* The same with a row stride: sample b's 5408 activations go to act + b*ld_act (ld_act >= 5408, in
+ * floats).  With ld_act = 5408*K and act pointing at column 5408*k of the --concat server's
+ * [rows, 5408*K] cache - normally a peer pointer into Bob's GPU - one launch per Alice fills her slot
+ * of every concatenated row in place: the gather of alice.give_activation_and_labels,
+ * data_entities_vanilla_sisa.py:196-211, feeding model2_sisa_concat's input, models.py:75-76, without
+ * a torch.cat.  From 512 samples up both forms run a streaming kernel (same numbers). */
+int sn_alice_forward_ld(sn_alice* h, const float* x, int B, float* act, size_t ld_act, void* stream);
 /* conv weight gradient from the cut-layer gradient + optimizer update.  x must be the batch given
  * to the matching forward.  Replaces Alice's share of dist_autograd.backward +
  * dist_optimizer.step, data_entities_vanilla.py:231,76. */
@@ -313,6 +320,13 @@ int sn_shard_create(sn_shard** out, int device, int K, int n_total, int n_off, i
                     double beta2, double eps, double weight_decay, float* W_slice, float* b_slice);
 int sn_shard_destroy(sn_shard* h);
 int sn_shard_reset_opt(sn_shard* h, void* stream);
+/* Optimizer-state access of a slice, for checkpointing and teacher-forced tests: which 0 = momentum
+ * / exp_avg, 1 = exp_avg_sq; param 0 = the weight slice [n_rows,K], 1 = the bias slice [n_rows].
+ * Setting the step counter also drops any fused next-forward partials (the caller has rewritten
+ * weights or state). */
+int sn_shard_opt_state(sn_shard* h, int which, int param, float** dptr, size_t* count);
+int sn_shard_get_opt_step(sn_shard* h, int64_t* step);
+int sn_shard_set_opt_step(sn_shard* h, int64_t step);
 int sn_shard_forward(sn_shard* h, const float* X, int B, int train_mode, const uint8_t* keep_mask,
                      uint64_t seed, uint64_t offset, float* H_out, int ld_out, void* stream);
 int sn_shard_backward_update(sn_shard* h, const float* X, const float* dH, int ld_dh, int B,

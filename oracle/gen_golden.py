@@ -1,7 +1,7 @@
 """Writes tests/golden/* from the UNMODIFIED reference in /root/reference (run in the build
 container only; the GPU box has no /root/reference and only reads the committed fixtures).
 
-    TORCH_FORCE_NO_WEIGHTS_ONLY_LOAD=1 python -m oracle.gen_golden [modules] [rpc]
+    TORCH_FORCE_NO_WEIGHTS_ONLY_LOAD=1 python -m oracle.gen_golden [modules] [rpc] [concat7]
 
 Two kinds of fixture:
   modules_*.npz  module-level vectors: the reference's own `models.py` classes loaded with
@@ -230,6 +230,57 @@ def gen_modules():
     print("module fixtures written to", OUT)
 
 
+def concat7_inputs(K=7, B=16):
+    """Seeded weights / batch / masks / labels of the K=7 concat fixture (shared with the tests)."""
+    w = seeded_weights([(5000, 5408 * K), (5000,), (1000, 5000), (1000,), (100 * K, 1000), (100 * K,)], 21)
+    rng = np.random.RandomState(22)
+    # sparse non-negative activations like the real cut tensor (SURVEY A.6: 63 % non-zero, mean 45)
+    xs = [(rng.rand(B, 5408 * K) * 90 * (rng.rand(B, 5408 * K) < 0.63)).astype(np.float32) for _ in range(2)]
+    ys = [rng.randint(0, 10, size=(B, K)).astype(np.int64) for _ in range(2)]
+    masks = [seeded_masks(B, (5000, 1000), 23 + s) for s in range(2)]
+    return w, xs, ys, masks
+
+
+def gen_concat7():
+    """modules_concat7.npz: BASELINE.json config 4's server (`model2_sisa_concat(7)`, fc1 5000 x 37856)
+    through the reference's own module + torch autograd + torch.optim.Adam(wd 1e-5), two steps.  The
+    7-head loss is this build's definition (see oracle/torch_ref.concat_server_step)."""
+    sys.path.insert(0, REF)
+    import models as ref_models
+    import torch.nn as nn
+    K, B = 7, 16
+    w, xs, ys, masks = concat7_inputs(K, B)
+    mc = ref_models.model2_sisa_concat(K)
+    sd = mc.state_dict()
+    mc.load_state_dict({k: torch.from_numpy(a) for k, a in zip(sd.keys(), w)})
+    opt = torch.optim.Adam(mc.parameters(), lr=1e-3, weight_decay=1e-5)
+    crit = nn.CrossEntropyLoss()
+
+    class Fixed(nn.Module):
+        def __init__(self, m):
+            super().__init__()
+            self.m = torch.from_numpy(m.astype(np.float32)) / 0.5
+
+        def forward(self, x):
+            return x * self.m
+    st = {}
+    for step in range(2):
+        mc.dropout1, mc.dropout2 = Fixed(masks[step][0]), Fixed(masks[step][1])
+        opt.zero_grad()
+        logits = mc(torch.from_numpy(xs[step]))
+        loss = crit(logits.reshape(B * K, 100), torch.from_numpy(ys[step]).reshape(B * K))
+        loss.backward()
+        summarize(f"s{step}_logits", logits, st)
+        st[f"s{step}_loss"] = np.float32(loss.item())
+        for n, p in mc.named_parameters():
+            summarize(f"s{step}_grad_{n}", p.grad, st)
+        opt.step()
+        for n, p in mc.named_parameters():
+            summarize(f"s{step}_new_{n}", p, st)
+    np.savez_compressed(os.path.join(OUT, "modules_concat7.npz"), **st)
+    print("modules_concat7.npz written")
+
+
 # ----------------------------------------------------------------------------- RPC trajectories
 def _write_loaders(workdir, n, K, batch_size):
     """Synthetic .pt loaders through the REFERENCE's own image_preprocess_dl."""
@@ -346,3 +397,5 @@ if __name__ == "__main__":
         gen_modules()
     if "rpc" in what:
         gen_rpc()
+    if "concat7" in what:
+        gen_concat7()

@@ -159,6 +159,20 @@ def sisa_server_step(bob_params, act, labels, masks, spec: BobSpec = MODEL2_SISA
     return dict(logits=logits.detach(), loss=loss.detach(), bob_grads=[p.grad for p in b])
 
 
+def concat_server_step(bob_params, act_cat, labels_bk, masks, num_clients):
+    """One `--sisa --concat` server batch up to the Adam step.  Forward/backward are the
+    reference module's (`model2_sisa_concat`, models.py:66-82) on the feature-concatenated
+    activations [B, 5408*K]; the loss is the one DEFINED BY THIS BUILD (the reference's loop crashes
+    before it forms one, data_entities_sisa_concat.py:270-276): the output [B, 100*K] read as K heads
+    of 100 logits, mean CE over the B*K (row, head) pairs with labels [B, K]."""
+    spec = model2_sisa_concat_spec(num_clients)
+    b = _leaf(bob_params)
+    logits = bob_forward(act_cat.detach(), b, spec, masks)
+    loss = cross_entropy(logits.reshape(-1, 100), labels_bk.reshape(-1))
+    loss.backward()
+    return dict(logits=logits.detach(), loss=loss.detach(), bob_grads=[p.grad for p in b])
+
+
 def sisa_alice_step(alice_params, x, labels):
     """One batch of SISA `alice.train` up to the Adam step
     (data_entities_vanilla_sisa.py:62-68): CE taken directly over the 5408 cut activations."""

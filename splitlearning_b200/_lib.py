@@ -53,6 +53,7 @@ SIGNATURES = {
     "sn_alice_get_opt_step": (_i, [_vp, C.POINTER(_i64)]),
     "sn_alice_set_opt_step": (_i, [_vp, _i64]),
     "sn_alice_forward": (_i, [_vp, _vp, _i, _vp, _vp]),
+    "sn_alice_forward_ld": (_i, [_vp, _vp, _i, _vp, _sz, _vp]),
     "sn_alice_backward_update": (_i, [_vp, _vp, _vp, _i, _vp]),
     "sn_alice_local_step": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "sn_alice_local_epoch": (_i, [_vp, _vp, _vp, _i64, _i, _vp, _vp]),
@@ -71,6 +72,9 @@ SIGNATURES = {
     "sn_shard_create": (_i, [_pp, _i, _i, _i, _i, _i, _i, _d, _i, _d, _d, _d, _d, _d, _d, _vp, _vp]),
     "sn_shard_destroy": (_i, [_vp]),
     "sn_shard_reset_opt": (_i, [_vp, _vp]),
+    "sn_shard_opt_state": (_i, [_vp, _i, _i, _pp, C.POINTER(_sz)]),
+    "sn_shard_get_opt_step": (_i, [_vp, C.POINTER(_i64)]),
+    "sn_shard_set_opt_step": (_i, [_vp, _i64]),
     "sn_shard_forward": (_i, [_vp, _vp, _i, _i, _vp, _u64, _u64, _vp, _i, _vp]),
     "sn_shard_backward_update": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i, _vp]),
     "sn_tp_server_epoch": (_i, [_vp, _vp, _i, _i, _vp, _vp, C.POINTER(_i64), _i, _pp, _u64, _u64, _vp, _vp, _vp, _vp,

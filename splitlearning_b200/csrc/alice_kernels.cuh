@@ -32,10 +32,12 @@ __device__ __forceinline__ void conv4(const float* __restrict__ img, const float
   }
 }
 
-// grid (samples, 4 channel groups), 256 threads.  act index = c*169 + i*13 + j.
+// grid (samples, 4 channel groups), 256 threads.  act index = b*ld_act + c*169 + i*13 + j
+// (ld_act = 5408 for a dense [B,5408] block; 5408*K when the rows are one Alice's slot of the
+// --concat server's [rows, 5408*K] cache).
 __global__ void __launch_bounds__(256) conv_pool_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                             const float* __restrict__ bias, int B,
-                                                            float* __restrict__ act) {
+                                                            float* __restrict__ act, size_t ld_act) {
   __shared__ float img[28 * 28];
   __shared__ float ws[kConvCG * 9];
   __shared__ float bs[kConvCG];
@@ -63,9 +65,97 @@ __global__ void __launch_bounds__(256) conv_pool_fwd_kernel(const float* __restr
       float v[4];
       conv4(img, ws + c * 9, bs[c], i, j, v);
       float m = fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3]));
-      act[(size_t)b * kD0 + (size_t)cg * kConvCG * kPooled + o] = fmaxf(m, 0.f);
+      act[(size_t)b * ld_act + (size_t)cg * kConvCG * kPooled + o] = fmaxf(m, 0.f);
     }
   }
+}
+
+// The same block over a WHOLE SHARD (SISA's activation-cache fill: one frozen Alice over all her
+// samples, data_entities_vanilla_sisa.py:196-211): a streaming kernel, bounded by the FP32 pipe
+// (36 FMA per output) and by the 21.6 KB it writes per sample, where the kernel above is a latency
+// kernel for 16 samples.  Persistent grid; a CTA takes one image per iteration (double-buffered
+// cp.async staging).  Work item = (pooled position, channel half): 338 of the CTA's 352 threads.  A
+// thread keeps the 4x4 input patch of its position in registers as broadcast pairs (p,p) and walks
+// its 8 CHANNEL PAIRS: the weights of channels (2q, 2q+1) lie interleaved in shared memory, so five
+// broadcast LDS.128 deliver the nine (w_2q, w_2q+1) pairs and the bias pair as ready-made 64-bit
+// operands, and every FMA is a packed fma.rn.f32x2 with no register moves around it - the same
+// operand order per output as conv4, so the results are bit-identical to conv_pool_fwd_kernel's.
+// Lanes are consecutive pooled positions: a warp's store is one contiguous run of a channel row.
+constexpr int kStreamThreads = 352;
+
+__global__ void __launch_bounds__(kStreamThreads, 2) conv_pool_stream_kernel(const float* __restrict__ x,
+                                                                             const float* __restrict__ w,
+                                                                             const float* __restrict__ bias, int B,
+                                                                             float* __restrict__ act, size_t ld_act) {
+  __shared__ __align__(16) float img[2][784];
+  __shared__ __align__(16) float2 wsm[16][10];         // [channel pair][9 weights, bias] as (even, odd) channel
+  const int tid = threadIdx.x;
+  const bool active = tid < 2 * kPooled;
+  const int p = tid % kPooled, half = tid / kPooled;
+  const int i = p / 13, j = p - i * 13;
+
+  auto stage = [&](int buf, int b) {
+    if (tid < 196) {
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(&img[buf][tid * 4]);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(x + (size_t)b * 784 + tid * 4) : "memory");
+    }
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+  };
+  int b = blockIdx.x;
+  if (b < B) stage(0, b);                              // x is an input: staged before the dependency wait
+  pdl_wait();
+  pdl_launch();
+  for (int t = tid; t < 16 * 10 * 2; t += kStreamThreads) {
+    const int odd = t & 1, q = (t >> 1) % 10, cp = t / 20;
+    const int c = 2 * cp + odd;
+    reinterpret_cast<float*>(&wsm[cp][q])[odd] = q < 9 ? w[c * 9 + q] : bias[c];
+  }
+  int buf = 0;
+  for (; b < B; b += gridDim.x, buf ^= 1) {
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    __syncthreads();                                   // this image has landed; the other buffer is free
+    if (b + (int)gridDim.x < B) stage(buf ^ 1, b + gridDim.x);
+    if (!active) continue;
+    float2 pt[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const float2 a0 = *reinterpret_cast<const float2*>(&img[buf][(2 * i + r) * 28 + 2 * j]);
+      const float2 a1 = *reinterpret_cast<const float2*>(&img[buf][(2 * i + r) * 28 + 2 * j + 2]);
+      pt[r][0] = make_float2(a0.x, a0.x);
+      pt[r][1] = make_float2(a0.y, a0.y);
+      pt[r][2] = make_float2(a1.x, a1.x);
+      pt[r][3] = make_float2(a1.y, a1.y);
+    }
+    float* out = act + (size_t)b * ld_act + p;
+#pragma unroll 2
+    for (int cc = 0; cc < 8; ++cc) {
+      const int cp = half * 8 + cc;
+      const float4* wq = reinterpret_cast<const float4*>(&wsm[cp][0]);
+      float2 wv[10];
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        const float4 t = wq[q];
+        wv[2 * q] = make_float2(t.x, t.y);
+        wv[2 * q + 1] = make_float2(t.z, t.w);
+      }
+      float2 v[4];
+#pragma unroll
+      for (int d = 0; d < 4; ++d) {
+        const int di = d >> 1, dj = d & 1;
+        float2 a = wv[9];
+#pragma unroll
+        for (int u = 0; u < 3; ++u)
+#pragma unroll
+          for (int q = 0; q < 3; ++q) a = __ffma2_rn(wv[u * 3 + q], pt[di + u][dj + q], a);
+        v[d] = a;
+      }
+      const float m0 = fmaxf(fmaxf(fmaxf(v[0].x, v[1].x), fmaxf(v[2].x, v[3].x)), 0.f);
+      const float m1 = fmaxf(fmaxf(fmaxf(v[0].y, v[1].y), fmaxf(v[2].y, v[3].y)), 0.f);
+      __stcs(out + (2 * cp) * kPooled, m0);
+      __stcs(out + (2 * cp + 1) * kPooled, m1);
+    }
+  }
+  asm volatile("cp.async.wait_group 0;\n" ::: "memory");
 }
 
 // Weight gradient.  grid (gx, 4): CTA (bx, cg) loops over samples bx, bx+gx, ...; warp = one

@@ -419,6 +419,23 @@ struct sn_shard {
 
 static int conv_bwd_gx(int B, int sms) { return std::max(1, std::min(B, sms * 2)); }
 
+// Alice's forward: the 16-sample latency kernel, or - from kConvStreamMinB samples up (a whole
+// shard: SISA's cache fill, evaluation) - the persistent streaming kernel.  Same numbers either way.
+static int conv_stream_min() {
+  static const int v = getenv("SN_CONV_STREAM_MIN") ? atoi(getenv("SN_CONV_STREAM_MIN")) : 512;
+  return v;
+}
+static int launch_conv_fwd(const float* x, const float* w, const float* b, int B, float* act, size_t ld_act, int sms,
+                           cudaStream_t st) {
+  if (B >= conv_stream_min()) {
+    launch_k(conv_pool_stream_kernel, dim3(std::min(B, sms * 2)), dim3(kStreamThreads), 0, st, x, w, b, B, act, ld_act);
+  } else {
+    launch_k(conv_pool_fwd_kernel, dim3(std::min(B, sms * 4), 4), dim3(256), 0, st, x, w, b, B, act, ld_act);
+  }
+  SN_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" {
 
 int sn_version(void) { return 1; }
@@ -441,10 +458,7 @@ int sn_conv_pool_forward(const float* x, const float* w, const float* b, int B, 
   SN_REQUIRE(x && w && b && act && B > 0, "sn_conv_pool_forward: bad arguments");
   int dev = 0;
   SN_CUDA(cudaGetDevice(&dev));
-  dim3 grid(std::min(B, sm_count(dev) * 4), 4);
-  launch_k(conv_pool_fwd_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, x, w, b, B, act);
-  SN_LAUNCH_CHECK();
-  return 0;
+  return launch_conv_fwd(x, w, b, B, act, kD0, sm_count(dev), (cudaStream_t)stream);
 }
 
 size_t sn_conv_pool_backward_scratch_bytes(int B) {
@@ -1161,10 +1175,13 @@ int sn_alice_set_opt_step(sn_alice* h, int64_t step) {
 int sn_alice_forward(sn_alice* h, const float* x, int B, float* act, void* stream) {
   SN_ALICE_ENTER(h);
   SN_REQUIRE(x && act && B > 0, "sn_alice_forward: bad arguments");
-  dim3 grid(std::min(B, h->sms * 4), 4);
-  launch_k(conv_pool_fwd_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, x, h->w, h->b, B, act);
-  SN_LAUNCH_CHECK();
-  return 0;
+  return launch_conv_fwd(x, h->w, h->b, B, act, kD0, h->sms, (cudaStream_t)stream);
+}
+
+int sn_alice_forward_ld(sn_alice* h, const float* x, int B, float* act, size_t ld_act, void* stream) {
+  SN_ALICE_ENTER(h);
+  SN_REQUIRE(x && act && B > 0 && ld_act >= (size_t)kD0, "sn_alice_forward_ld: bad arguments (ld_act >= 5408)");
+  return launch_conv_fwd(x, h->w, h->b, B, act, ld_act, h->sms, (cudaStream_t)stream);
 }
 
 static int alice_bwd(sn_alice* h, const float* x, const float* dact, int B, cudaStream_t st) {
@@ -1207,9 +1224,7 @@ int sn_alice_local_step(sn_alice* h, const float* x, const int64_t* labels, int 
     SN_CUDA(cudaMalloc(&h->act, (size_t)h->max_batch * kD0 * 4));
     SN_CUDA(cudaMalloc(&h->dact, (size_t)h->max_batch * kD0 * 4));
   }
-  dim3 grid(std::min(B, h->sms * 4), 4);
-  launch_k(conv_pool_fwd_kernel, dim3(grid), dim3(256), 0, st, x, h->w, h->b, B, h->act);
-  SN_LAUNCH_CHECK();
+  if (launch_conv_fwd(x, h->w, h->b, B, h->act, kD0, h->sms, st)) return 1;
   if (launch_ce(h->act, kD0, labels, B, kD0, h->dact, kD0, h->row_loss, h->ticket + 1, loss_out, nullptr, st)) return 1;
   return alice_bwd(h, x, h->dact, B, st);
 }
@@ -1352,6 +1367,25 @@ int sn_shard_reset_opt(sn_shard* h, void* stream) {
   }
   h->step = 0;
   h->pf_valid = false;
+  return 0;
+}
+
+int sn_shard_opt_state(sn_shard* h, int which, int param, float** dptr, size_t* count) {
+  SN_REQUIRE(h && dptr && count && (which == 0 || which == 1) && (param == 0 || param == 1), "sn_shard_opt_state: bad arguments");
+  SN_REQUIRE(which == 0 || h->s2, "sn_shard_opt_state: no second moment for this optimizer");
+  *dptr = which == 0 ? (param == 0 ? h->s1 : h->bs1) : (param == 0 ? h->s2 : h->bs2);
+  *count = param == 0 ? (size_t)h->n_rows * h->K : (size_t)h->n_rows;
+  return 0;
+}
+int sn_shard_get_opt_step(sn_shard* h, int64_t* step) {
+  SN_REQUIRE(h && step, "sn_shard_get_opt_step: bad arguments");
+  *step = h->step;
+  return 0;
+}
+int sn_shard_set_opt_step(sn_shard* h, int64_t step) {
+  SN_REQUIRE(h && step >= 0, "sn_shard_set_opt_step: bad arguments");
+  h->step = step;
+  h->pf_valid = false;       // whoever sets the step has rewritten the state: fused partials are stale
   return 0;
 }
 

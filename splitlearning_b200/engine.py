@@ -190,6 +190,21 @@ class ShardEngine:
     def reset_opt(self):
         check(self.lib.sn_shard_reset_opt(self.h, _stream(self.device)))
 
+    def opt_state(self, which, param):
+        """A torch view (no copy) of the slice's optimizer state: which 0/1 = first/second moment,
+        param 0/1 = weight slice / bias slice."""
+        p, n = C.c_void_p(), C.c_size_t()
+        check(self.lib.sn_shard_opt_state(self.h, which, param, C.byref(p), C.byref(n)))
+        return _view_f32(p.value, n.value, self.device)
+
+    def get_opt_step(self):
+        s = C.c_int64()
+        check(self.lib.sn_shard_get_opt_step(self.h, C.byref(s)))
+        return s.value
+
+    def set_opt_step(self, step):
+        check(self.lib.sn_shard_set_opt_step(self.h, int(step)))
+
 
 class AliceEngine:
     """`sn_alice`: the client conv block bound to caller-owned conv weight/bias tensors."""
@@ -215,11 +230,19 @@ class AliceEngine:
 
     __del__ = close
 
-    def forward(self, x, out=None):
+    def forward(self, x, out=None, ld=None):
+        """act = conv block(x).  `out`: where to write (a tensor, or a raw peer address wrapper);
+        `ld`: row stride of `out` in floats when the 5408 activations of a sample are one slot of
+        a wider row (the --concat server's cache) - `out` then points at the slot's first column."""
         B = x.shape[0]
         _f32c(x)
-        out = out if out is not None else torch.empty(B, D0, device=x.device)
-        check(self.lib.sn_alice_forward(self.h, ptr(x), B, ptr(out), _stream(x.device)))
+        if ld is None:
+            out = out if out is not None else torch.empty(B, D0, device=x.device)
+            check(self.lib.sn_alice_forward(self.h, ptr(x), B, ptr(out), _stream(x.device)))
+        else:
+            if out is None or int(ld) < D0:
+                raise ValueError("forward(ld=...) needs an output address and ld >= 5408")
+            check(self.lib.sn_alice_forward_ld(self.h, ptr(x), B, C.c_void_p(out.data_ptr()), int(ld), _stream(x.device)))
         return out
 
     def backward_update(self, x, cut_grad):

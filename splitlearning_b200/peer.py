@@ -166,3 +166,60 @@ class PeerLink:
             if self.base:
                 self.lib.sn_ipc_free(C.c_void_p(self.base))
                 self.base = 0
+
+
+class ConcatCache:
+    """Bob's activation cache for `--sisa --concat` as ONE peer-visible allocation on rank 0:
+    acts [rows, 5408*K] fp32 followed by labels [rows, K] int64.  Every Alice rank maps it (CUDA IPC)
+    and her conv kernel stores her 5408-column slot of every row straight into it over NVLink
+    (`engine.AliceEngine.forward(out=cache.slot(k), ld=5408*K)`), which replaces both the per-batch
+    activation lists of `bob.get_activation_and_labels` (`data_entities_vanilla_sisa.py:272-292`) and
+    the torch.cat a single-process concat needs.  Collective set-up: every rank constructs it."""
+
+    def __init__(self, rank, world, device, rows, K):
+        self.lib = _lib.load()
+        self.rank, self.world, self.device, self.rows, self.K = rank, world, device, int(rows), int(K)
+        self.act_bytes = self.rows * self.K * D0 * 4
+        total = self.act_bytes + self.rows * self.K * 8
+        handle = torch.zeros(64, dtype=torch.uint8, device=device)
+        self.base, self.mapped = 0, 0
+        if rank == 0:
+            base, raw = C.c_void_p(), (C.c_ubyte * 64)()
+            with torch.cuda.device(device):
+                check(self.lib.sn_ipc_alloc(max(total, 256), C.byref(base), raw))
+            self.base = base.value
+            handle.copy_(torch.tensor(list(raw), dtype=torch.uint8))
+        if world > 1:
+            dist.broadcast(handle, src=0)
+        if rank != 0:
+            raw = (C.c_ubyte * 64)(*handle.cpu().tolist())
+            p = C.c_void_p()
+            with torch.cuda.device(device):
+                check(self.lib.sn_ipc_open(raw, C.byref(p)))
+            self.mapped = p.value
+        if world > 1:
+            dist.barrier()
+        self.acts = self.labels = None
+        if rank == 0:
+            with torch.cuda.device(device):
+                self.acts = torch.as_tensor(_View(self.base, self.rows * self.K * D0, "<f4"), device=device).view(self.rows, self.K * D0)
+                self.labels = torch.as_tensor(_View(self.base + self.act_bytes, self.rows * self.K, "<i8"),
+                                              device=device).view(self.rows, self.K)
+
+    def slot(self, k):
+        """Address of column 5408*k of row 0, as seen from THIS rank (Bob's own memory on rank 0)."""
+        origin = self.base if self.rank == 0 else self.mapped
+        return _Raw(origin + k * D0 * 4, (self.rows, D0), self.device)
+
+    def close(self):
+        torch.cuda.synchronize(self.device)
+        if self.world > 1 and dist.is_initialized():
+            dist.barrier()
+        with torch.cuda.device(self.device):
+            if self.mapped:
+                self.lib.sn_ipc_close(C.c_void_p(self.mapped))
+                self.mapped = 0
+            if self.base:
+                self.acts = self.labels = None
+                self.lib.sn_ipc_free(C.c_void_p(self.base))
+                self.base = 0

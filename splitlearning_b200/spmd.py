@@ -202,6 +202,127 @@ def run_sisa_schedule(rank, world, bob, alices, data, sizes, B, local_epochs, se
     return cache
 
 
+def concat_rows(sizes, B):
+    """Rows of the --concat server's cache: full batches only, as many as the smallest shard has
+    (`data_entities_sisa_concat.py` here: steps/epoch = min_k(number of FULL batches of Alice k))."""
+    return min(int(n) // B for n in sizes) * B
+
+
+def run_sisa_concat_schedule(rank, world, bob, alices, data, sizes, B, local_epochs, server_epochs, device,
+                             unlearn=None, timers=None, cache=None):
+    """`--sisa --concat` over ranks (BASELINE.json config 4: Bob on rank 0, K Alices on ranks 1..W-1;
+    CLI branch `split_nn.py:64-72`, unlearning order `split_nn.py:95-110`, server model
+    `models.py:66-82`).  The reference's own concat loop crashes (`data_entities_sisa_concat.py:270-276`),
+    so the semantics are the ones `splitlearning_b200/data_entities_sisa_concat.py` defines: row j of
+    Bob's cache is cat_k(act_k[j]) -> [rows, 5408*K] with labels [rows, K], rows = full batches of the
+    smallest shard, K-head CE.
+      phase 1  each rank trains its Alices locally (as --sisa);
+      phase 2  Alice k runs her frozen model over her first `rows` samples and fills COLUMN SLOT k of
+               Bob's cache: with `cache` (a peer.ConcatCache) her conv kernel stores straight into
+               Bob's GPU over NVLink, row stride 5408*K, no staging copy and no torch.cat; without
+               it (gloo tests) she sends the [rows,5408] block and rank 0 copies it into the slot;
+      phase 3  rank 0 runs the server epochs over the concatenated rows;
+      phase 4  (unlearn=(k, omit_label)) Alice k drops the label, retrains with a fresh optimizer and
+               rebuilds ONLY her slot (the row count can only shrink); Bob trains again.
+    Returns rank 0's (acts [rows,5408K], labels [rows,K]) (None elsewhere)."""
+    K = len(sizes)
+    tick = timers if timers is not None else (lambda name: None)
+    rows0 = concat_rows(sizes, B)
+    if rank == 0:
+        if cache is not None:
+            acts, labels = cache.acts, cache.labels
+        else:
+            acts = torch.zeros(rows0, K * D0, dtype=torch.float32, device=device)
+            labels = torch.zeros(rows0, K, dtype=torch.int64, device=device)
+    else:
+        acts = labels = None
+
+    def train_local(k, x, y):
+        for _ in range(local_epochs):
+            if hasattr(alices[k], "local_epoch"):
+                alices[k].local_epoch(x, y, B)
+            else:
+                for s in range(0, x.shape[0], B):
+                    alices[k].local_step(x[s:s + B], y[s:s + B])
+
+    def fill_slot(k, rows):
+        own = owner_rank(k, world)
+        if rank == own:
+            x, y = data[k]
+            if cache is not None:
+                alices[k].forward(x[:rows], out=cache.slot(k), ld=K * D0)
+                if own == 0:
+                    labels[:rows, k] = y[:rows]
+                else:
+                    dist.send(y[:rows].contiguous(), dst=0)
+            else:
+                block = alices[k].forward(x[:rows])
+                if own == 0:
+                    acts[:rows, k * D0:(k + 1) * D0] = block
+                    labels[:rows, k] = y[:rows]
+                else:
+                    dist.send(block, dst=0)
+                    dist.send(y[:rows].contiguous(), dst=0)
+        elif rank == 0:
+            if cache is None:
+                block = torch.empty(rows, D0, dtype=torch.float32, device=device)
+                dist.recv(block, src=own)
+                acts[:rows, k * D0:(k + 1) * D0] = block
+            lab = torch.empty(rows, dtype=torch.int64, device=device)
+            dist.recv(lab, src=own)
+            labels[:rows, k] = lab
+
+    def fence():
+        # the slot writes are plain kernels on the Alice GPUs: Bob may read once they have finished
+        if cache is not None:
+            torch.cuda.synchronize(device)
+        if world > 1:
+            dist.barrier()
+
+    def server(rows):
+        if rows:
+            for _ in range(server_epochs):
+                bob.server_epoch(acts[:rows], labels[:rows], list(range(0, rows + 1, B)))
+
+    tick("start")
+    for k in sorted(alices):
+        train_local(k, *data[k])
+    tick("local_training")
+    for k in range(K):
+        fill_slot(k, rows0)
+    fence()
+    tick("activation_gather")
+    if rank == 0:
+        server(rows0)
+    tick("server_epochs")
+    rows = rows0
+    if unlearn is not None:
+        k, omit = unlearn
+        if k in alices:
+            x, y = data[k]
+            keep = y != omit
+            xu, yu = x[keep].contiguous(), y[keep].contiguous()
+            alices[k].reset_opt()
+            train_local(k, xu, yu)
+            data = dict(data)
+            data[k] = (xu, yu)
+        if world > 1:
+            n_new = torch.tensor([data[k][0].shape[0] if k in alices else 0], device=device, dtype=torch.int64)
+            dist.broadcast(n_new, src=owner_rank(k, world))
+            n_k = int(n_new.item())
+        else:
+            n_k = data[k][0].shape[0]
+        rows = min(rows0, (n_k // B) * B)
+        tick("unlearn_retrain")
+        fill_slot(k, rows)
+        fence()
+        tick("unlearn_gather")
+        if rank == 0:
+            server(rows)
+        tick("unlearn_server_epochs")
+    return (acts[:rows], labels[:rows]) if rank == 0 else None
+
+
 # ------------------------------------------------------------------------------- CUDA engines
 class _CudaAlice:
     def __init__(self, device, lr):
@@ -330,6 +451,92 @@ def bench_sisa(rank, world, device, B, n_alices):
     return out
 
 
+class _CudaConcatBob:
+    """The --concat server: model2_sisa_concat(K) with K CE heads, Adam wd 1e-5 (`models.py:66-82`)."""
+
+    def __init__(self, device, lr, B, K):
+        from . import engine as E
+        from . import models as M
+        self.model = M.model2_sisa_concat(num_clients=K, device=device)
+        self.eng = self.model.make_engine(optimizer=E.SN_OPT_ADAM, lr=lr, weight_decay=1e-5, n_opt_slots=1, max_batch=B)
+        self.eng.set_ce_heads(K)
+        self.offset = 0
+        self.losses = None
+
+    def server_epoch(self, acts, labels, offsets):
+        self.eng.server_epoch(acts, labels, offsets, slot=0, masks=None, seed=7, offset=self.offset, loss_per_step=self.losses)
+        self.offset += len(offsets)
+
+
+CONCAT_K = 7
+# LDA K=7 client sizes of the 70,000-sample set (SURVEY.md Appendix B), 80 % train
+CONCAT_SIZES = [n * 8 // 10 for n in (10448, 11355, 10069, 6662, 8509, 9968, 12989)]
+
+
+def bench_sisa_concat(rank, world, device, B, peak):
+    """BASELINE.json configs[3]: `--sisa --concat`, world_size 8 (Bob + 7 Alices), one local epoch,
+    one server epoch over the concatenated cache, then Alice 1 unlearns label 9 and Bob retrains
+    (`split_nn.py:64-72,95-110`).  At N GPUs the 7 Alices sit on ranks 1..N-1 (all on rank 0 when
+    N = 1) and each one's conv kernel fills her column slot of Bob's cache over NVLink.  Phase times
+    are max over ranks."""
+    from .peer import ConcatCache
+    K, sizes = CONCAT_K, CONCAT_SIZES
+    g = torch.Generator().manual_seed(9)
+    data, mine = {}, {}
+    for k, n in enumerate(sizes):
+        x = torch.randint(0, 256, (n, 1, 28, 28), generator=g).float() * (torch.rand(n, 1, 28, 28, generator=g) < 0.4)
+        y = torch.randint(0, 10, (n,), generator=g)
+        if owner_rank(k, world) == rank:
+            data[k] = (x.to(device), y.to(device))
+            mine[k] = _CudaSisaAlice(device, 1e-3, B)
+    torch.manual_seed(3)
+    bob = _CudaConcatBob(device, 1e-3, B, K) if rank == 0 else None
+    rows = concat_rows(sizes, B)
+    cache = ConcatCache(rank, world, device, rows, K)
+    if world > 1:
+        tiny = torch.zeros(4, device=device)              # open the lazy NCCL point-to-point connections untimed
+        for r in range(1, world):
+            if rank == 0:
+                dist.recv(tiny, src=r)
+            elif rank == r:
+                dist.send(tiny, dst=0)
+    if bob is not None:                                    # warm-up: first-use costs of the big kernels stay out of the phases
+        bob.server_epoch(cache.acts[:4 * B], cache.labels[:4 * B], list(range(0, 4 * B + 1, B)))
+        for p in bob.model.parameters():
+            pass
+    torch.cuda.synchronize()
+    marks = []
+
+    def tick(name):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        marks.append((name, ev))
+    run_sisa_concat_schedule(rank, world, bob, mine, data, sizes, B, 1, 1, device, unlearn=(0, 9), timers=tick, cache=cache)
+    torch.cuda.synchronize()
+    P = sum(bob.model.dims[i] * bob.model.dims[i + 1] + bob.model.dims[i + 1] for i in range(3)) if bob is not None else 0
+    out = {"alices": K, "placement": [owner_rank(k, world) for k in range(K)], "rows": rows, "steps": rows // B,
+           "cache_bytes": rows * K * D0 * 4,
+           "semantics": "feature-concat, K CE heads: defined by this build, reference unpinned (its loop crashes)"}
+    for (n0, e0), (n1, e1) in zip(marks[:-1], marks[1:]):
+        t = torch.tensor([e0.elapsed_time(e1)], device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out[n1 + "_ms"] = round(float(t.item()), 3)
+    if rank == 0:
+        steps = rows // B
+        step_bytes = 24.0 * P + 4.0 * B * K * D0
+        us = 1e3 * out["server_epochs_ms"] / max(steps, 1)
+        out.update({"server_epoch_ms": out["server_epochs_ms"], "us_per_step": round(us, 2), "gather_ms": out["activation_gather_ms"],
+                    "params": P, "algorithmic_bytes_per_step": step_bytes, "formula": "24*P + 4*B*K*d0",
+                    "achieved_gbs": round(step_bytes / (us * 1e-6) / 1e9, 1),
+                    "frac_of_24P": round(step_bytes / (us * 1e-6) / 1e9 / peak, 4)})
+    cache.close()
+    return out
+
+
 def bench_tp_epoch(rank, world, device, B, sizes):
     """One SISA server epoch with the first layer's rows split over all ranks (tp.TPServer): the
     activation cache is replicated on every rank (timed separately), then one pass over it, timed
@@ -376,6 +583,78 @@ def bench_tp_epoch(rank, world, device, B, sizes):
     return {"ranks": world, "server_epoch_ms": round(ms, 3), "steps": steps, "us_per_step": round(1e3 * ms / steps, 2),
             "replicate_cache_ms": round(rep_ms, 3), "cache_bytes": n * D0 * 4,
             "layout": "fc1 rows split over all ranks (1/G of W1 + Adam state per GPU); fc2, fc3, loss on rank 0"}
+
+
+def bench_parity(rank, world, device, B, link):
+    """Outside every timed region, on the ranks the bench already has: do the multi-GPU paths
+    compute what the one-GPU path computes?  (The driver's GPU test box has one GPU, so the two-GPU
+    tests in tests/ are skipped there; this block puts the same comparison into the bench line.)
+      vanilla   first 3 losses with Alice on rank 1 and Bob on rank 0 over the peer mailboxes, against
+                the same model, data and Philox stream stepped on rank 0 alone;
+      tp        first 3 losses of sn_tp_server_epoch over all ranks against sn_bob_server_epoch on
+                rank 0, same cached batches and dropout masks.
+    Returns {"vanilla_rel": [...], "tp_rel": [...]} on rank 0."""
+    from . import engine as E
+    from . import models as M
+    from . import tp
+    steps = 3
+    g = torch.Generator().manual_seed(77)
+    x = (torch.randint(0, 256, (steps, B, 1, 28, 28), generator=g).float() * (torch.rand(steps, B, 1, 28, 28, generator=g) < 0.4)).to(device)
+    y = torch.randint(0, 10, (steps, B), generator=g).to(device)
+    out = {}
+
+    def fresh(with_bob, with_alice):
+        torch.manual_seed(11)
+        bob = _CudaBob(device, 1e-3, 1, B) if with_bob else None
+        torch.manual_seed(12)
+        alice = _CudaAlice(device, 1e-3) if with_alice else None
+        return bob, alice
+
+    def run(r, w, bob, alice, lk):
+        got = []
+        run_vanilla_schedule(r, w, bob, {0: alice} if alice is not None else {}, lambda i: (x[i], y[i]), 1, 64, 0, steps, B,
+                             device, lambda i, l: got.append(l.clone()), lk)
+        torch.cuda.synchronize()
+        return [float(v.item()) for v in got]
+
+    if link is not None:
+        bob, alice = fresh(rank == 0, rank == owner_rank(0, world))
+        over_link = run(rank, world, bob, alice, link)
+        dist.barrier()
+        if rank == 0:
+            bob1, alice1 = fresh(True, True)
+            alone = run(0, 1, bob1, alice1, None)
+            out["vanilla_losses"] = over_link
+            out["vanilla_rel"] = [abs(a - b) / max(abs(b), 1e-30) for a, b in zip(over_link, alone)]
+
+    # tensor-parallel server against the unsharded epoch
+    torch.manual_seed(5)
+    model = M.model2_sisa(device)
+    Ws = [model.fc1.weight.data, model.fc2.weight.data, model.fc3.weight.data]
+    bs = [model.fc1.bias.data, model.fc2.bias.data, model.fc3.bias.data]
+    ref_W, ref_b = [w.clone() for w in Ws], [b.clone() for b in bs]
+    n = steps * B
+    acts = (torch.rand(n, D0, generator=g) * 30 * (torch.rand(n, D0, generator=g) < 0.6)).to(device)
+    labels = torch.randint(0, 10, (n,), generator=g).to(device)
+    m1 = (torch.rand(n, 5000, generator=g) < 0.5).to(torch.uint8).to(device)
+    m2 = (torch.rand(n, 1000, generator=g) < 0.5).to(torch.uint8).to(device)
+    offs = list(range(0, n + 1, B))
+    srv = tp.TPServer(rank, world, device, Ws, bs, B=B, lr=1e-3, weight_decay=1e-5, dropout_p=0.5)
+    l_tp = torch.zeros(steps, device=device)
+    srv.server_epoch(acts, labels, offs, masks=[m1, m2], loss_per_step=l_tp if rank == 0 else None)
+    torch.cuda.synchronize()
+    srv.close()
+    if rank == 0:
+        bob = E.BobEngine([D0, 5000, 1000, 100], ref_W, ref_b, optimizer=E.SN_OPT_ADAM, lr=1e-3, weight_decay=1e-5,
+                          n_opt_slots=1, max_batch=B)
+        l_ref = torch.zeros(steps, device=device)
+        bob.server_epoch(acts, labels, offs, masks=[m1, m2], loss_per_step=l_ref)
+        torch.cuda.synchronize()
+        out["tp_losses"] = [float(v) for v in l_tp.tolist()]
+        out["tp_rel"] = [abs(a - b) / max(abs(b), 1e-30) for a, b in zip(l_tp.tolist(), l_ref.tolist())]
+        out["ok"] = bool(all(v <= 1e-4 for v in out["tp_rel"]) and all(v <= 1e-4 for v in out.get("vanilla_rel", [0.0])))
+        bob.close()
+    return out
 
 
 def bench_vanilla(args, B, n_alices, turn, config, peak):
@@ -471,6 +750,8 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
     if bob is not None:
         bob.loss_host = None
     sisa = bench_sisa(rank, world, device, B, n_alices)
+    sisa_concat = bench_sisa_concat(rank, world, device, B, peak[0])
+    parity = bench_parity(rank, world, device, B, link)
 
     if rank == 0:
         value = K * B / (ms * 1e-3)
@@ -487,7 +768,7 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
                          "frac": round(step_bytes / (ms * 1e-3 / K) / 1e9 / peak[0], 4), "traffic": None,
                          "peak_source": peak[1]},
             "nvlink_bytes_per_step": 2 * B * D0 * 4 + B * 8,
-            "sisa": sisa,
+            "sisa": sisa, "sisa_concat": sisa_concat, "parity": parity,
             "note": "vanilla split learning is a sequential chain (SURVEY.md 8e): extra GPUs host Alices and add "
                     "two NVLink messages per step; they cannot add throughput without changing results",
         }

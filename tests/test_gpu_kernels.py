@@ -204,6 +204,56 @@ def test_sisa_server_steps_vs_oracle_and_golden(eng):
     check_summary(g, "eval_logits", out, TOL)
 
 
+def test_concat7_server_steps_vs_oracle_and_golden(eng):
+    """BASELINE.json config 4: the --sisa --concat server at K = 7 clients (fc1 5000 x 37856 = 757 MB,
+    fc3 1000 -> 700, seven CE heads), two teacher-forced Adam(wd 1e-5) steps against the oracle and
+    against the fixture written from the reference's model2_sisa_concat module."""
+    from oracle.gen_golden import concat7_inputs
+    K = 7
+    g = load_golden("modules_concat7.npz")
+    w, xs, ys, masks = concat7_inputs()
+    b = T(w)
+    gp = [cu(p.numpy()) for p in b]
+    bob = eng.BobEngine([5408 * K, 5000, 1000, 100 * K], gp[0::2], gp[1::2], optimizer=eng.SN_OPT_ADAM, lr=1e-3,
+                        weight_decay=1e-5)
+    bob.set_ce_heads(K)
+    opt = R.AdamState()
+    for step in range(2):
+        ref = R.concat_server_step(b, torch.from_numpy(xs[step]), torch.from_numpy(ys[step]), T(masks[step]), K)
+        R.adam_(b, ref["bob_grads"], opt, 1e-3, weight_decay=1e-5)
+        loss, cut, logits = bob.train_step(cu(xs[step]), cu(ys[step]), masks=[cu(m) for m in masks[step]],
+                                           want_cut_grad=False, want_logits=True)
+        assert cut is None and logits.shape == (16, 100 * K)
+        assert rel_err(logits.cpu(), ref["logits"]) <= TOL
+        assert abs(loss.item() - ref["loss"].item()) <= TOL * abs(ref["loss"].item())
+        check_summary(g, f"s{step}_logits", logits, TOL)
+        assert abs(loss.item() - float(g[f"s{step}_loss"])) <= TOL * abs(float(g[f"s{step}_loss"]))
+        for n, p_ref, p in zip(B_NAMES, b, gp):
+            check_adam_weights(p.cpu(), p_ref, n)
+            check_summary(g, f"s{step}_new_{n}", p, 1e-3)
+        for i, (p_ref, p) in enumerate(zip(b, gp)):      # teacher forcing for the next step
+            p.copy_(p_ref)
+            bob.opt_state(0, 0, i).copy_(opt.m[i].reshape(-1))
+            bob.opt_state(0, 1, i).copy_(opt.v[i].reshape(-1))
+    # the server-epoch form (first layer's next forward fused into the Adam traversal) on the same two
+    # batches must give the step-wise losses
+    for i, p in enumerate(T(w)):
+        gp[i].copy_(p)
+    bob.reset_opt_slot(0)
+    acts = cu(np.concatenate(xs, 0))
+    labels = cu(np.concatenate(ys, 0))
+    mm = [cu(np.concatenate([masks[0][l], masks[1][l]], 0)) for l in range(2)]
+    losses = torch.empty(2, device="cuda")
+    bob.server_epoch(acts, labels, [0, 16, 32], slot=0, masks=mm, loss_per_step=losses)
+    torch.cuda.synchronize()
+    b2 = T(w)
+    opt2 = R.AdamState()
+    for step in range(2):
+        ref = R.concat_server_step(b2, torch.from_numpy(xs[step]), torch.from_numpy(ys[step]), T(masks[step]), K)
+        R.adam_(b2, ref["bob_grads"], opt2, 1e-3, weight_decay=1e-5)
+        assert abs(losses[step].item() - ref["loss"].item()) <= (TOL if step == 0 else 2e-3) * abs(ref["loss"].item())
+
+
 def test_sisa_alice_local_steps(eng):
     g = load_golden("modules_sisa_alice.npz")
     a = T(seeded_weights(A_SHAPES, 11))

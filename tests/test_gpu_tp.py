@@ -93,6 +93,60 @@ def test_two_shards_on_one_gpu_match_unsharded_epoch():
         shards[0].backward_update(acts[:16], dH1, 5000)
 
 
+def test_sharded_first_layer_steps_vs_oracle():
+    """Teacher-forced against the CPU oracle (not against this library's own unsharded path): three
+    SISA server steps with fc1 split into two uneven sn_shard slices + a head over fc2/fc3 on one GPU;
+    logits and loss at 1e-4, Adam-updated weights by check_adam_weights, every step restarted from the
+    oracle's weights and moments (`data_entities_vanilla_sisa.py:305-313`, torch Adam wd 1e-5)."""
+    from oracle import torch_ref as R
+    from splitlearning_b200 import engine as E
+    from tests.helpers import check_adam_weights, rel_err
+    dev = torch.device("cuda", 0)
+    Ws, bs = _weights(dev)
+    acts, y, m1, m2, offs = _data(dev)
+    ref_p = []
+    for w, b in zip(Ws, bs):
+        ref_p += [w.cpu().clone(), b.cpu().clone()]
+    cuts = [0, 2600, 5000]
+    kw = dict(optimizer=E.SN_OPT_ADAM, lr=1e-3, weight_decay=1e-5)
+    shards = [E.ShardEngine(Ws[0][lo:hi], bs[0][lo:hi], 5000, lo, dropout_p=0.5, **kw) for lo, hi in zip(cuts[:-1], cuts[1:])]
+    head = E.BobEngine(DIMS[1:], Ws[1:], bs[1:], dropout_p=0.5, n_opt_slots=1, max_batch=B, **kw)
+    H1 = torch.zeros(B, 5000, device=dev)
+    dH1 = torch.zeros(B, 5000, device=dev)
+    opt = R.AdamState()
+    for i in (0, 1, 5):                                    # two full batches and the ragged last one
+        s, e = offs[i], offs[i + 1]
+        masks = [m1[s:e].cpu(), m2[s:e].cpu()]
+        ref = R.sisa_server_step(ref_p, acts[s:e].cpu(), y[s:e].cpu(), masks)
+        R.adam_(ref_p, ref["bob_grads"], opt, 1e-3, weight_decay=1e-5)
+        for sh in shards:
+            sh.forward(acts[s:e], H1, 5000, train=True, mask=m1[s:e])
+        loss, _, logits = head.train_step(H1[:e - s], y[s:e], masks=[m2[s:e]], cut_out=dH1[:e - s], want_logits=True)
+        for sh in shards:
+            sh.backward_update(acts[s:e], dH1, 5000)
+        torch.cuda.synchronize()
+        assert rel_err(logits.cpu(), ref["logits"]) <= 1e-4
+        assert abs(loss.item() - ref["loss"].item()) <= 1e-4 * abs(ref["loss"].item())
+        for j, (w, b) in enumerate(zip(Ws, bs)):
+            check_adam_weights(w.cpu(), ref_p[2 * j], f"fc{j + 1}.weight")
+            check_adam_weights(b.cpu(), ref_p[2 * j + 1], f"fc{j + 1}.bias")
+        # teacher forcing: the next step starts from the oracle's weights, moments and step count
+        for j, (w, b) in enumerate(zip(Ws, bs)):
+            w.copy_(ref_p[2 * j])
+            b.copy_(ref_p[2 * j + 1])
+        for sh, lo, hi in zip(shards, cuts[:-1], cuts[1:]):
+            sh.opt_state(0, 0).copy_(opt.m[0][lo:hi].reshape(-1))
+            sh.opt_state(1, 0).copy_(opt.v[0][lo:hi].reshape(-1))
+            sh.opt_state(0, 1).copy_(opt.m[1][lo:hi])
+            sh.opt_state(1, 1).copy_(opt.v[1][lo:hi])
+            sh.set_opt_step(opt.step)
+            assert sh.get_opt_step() == opt.step
+        for j in range(2, 6):
+            head.opt_state(0, 0, j - 2).copy_(opt.m[j].reshape(-1))
+            head.opt_state(0, 1, j - 2).copy_(opt.v[j].reshape(-1))
+        assert head.get_opt_step(0) == opt.step
+
+
 def _tp_rank(rank, world, out_dir, port):
     import torch.distributed as dist
     from splitlearning_b200 import tp

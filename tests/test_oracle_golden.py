@@ -107,6 +107,25 @@ def test_modules_concat_shapes():
     check_summary(g, "eval_logits", out, TOL)
 
 
+def test_modules_concat7_oracle_step():
+    """BASELINE.json config 4's server shape (7 clients, fc1 5000 x 37856): the oracle's concat step
+    against the reference module's own forward/backward + torch.optim.Adam (gen_golden.gen_concat7)."""
+    from oracle.gen_golden import concat7_inputs
+    g = load_golden("modules_concat7.npz")
+    w, xs, ys, masks = concat7_inputs()
+    b = T(w)
+    opt = R.AdamState()
+    for step in range(2):
+        out = R.concat_server_step(b, torch.from_numpy(xs[step]), torch.from_numpy(ys[step]), T(masks[step]), 7)
+        check_summary(g, f"s{step}_logits", out["logits"], TOL)
+        assert abs(float(out["loss"]) - float(g[f"s{step}_loss"])) <= TOL * abs(float(g[f"s{step}_loss"]))
+        for n, gr in zip(B_NAMES, out["bob_grads"]):
+            check_summary(g, f"s{step}_grad_{n}", gr, TOL)
+        R.adam_(b, out["bob_grads"], opt, 1e-3, weight_decay=1e-5)
+        for n, p in zip(B_NAMES, b):
+            check_summary(g, f"s{step}_new_{n}", p, TOL)
+
+
 # ----------------------------------------------------------------------------- RPC trajectories
 def _loaders(n=300, K=2):
     import random

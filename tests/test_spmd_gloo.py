@@ -230,3 +230,91 @@ def test_sisa_schedule_matches_single_process(world):
     assert (ref["cache0_labels"] != 9).all() and int(ref["cache0_n"]) < SISA_SIZES[0]      # the unlearned shard was re-shipped
     for k in ref:
         assert np.array_equal(got[k], ref[k]), k
+
+
+# ----------------------------------------------------------------------------- --sisa --concat over ranks
+CONCAT_SIZES = [13, 9, 11]           # rows = full batches of the smallest shard = 8 at B = 4
+CONCAT_SPEC = R.BobSpec((5408 * 3, 24, 10 * 3), False, 0.0)
+
+
+class FakeConcatBob:
+    """K-head server on the feature-concatenated rows (semantics of data_entities_sisa_concat.py)."""
+
+    def __init__(self):
+        g = torch.Generator().manual_seed(6)
+        self.p = [torch.randn(24, 5408 * 3, generator=g) * 0.01, torch.zeros(24), torch.randn(30, 24, generator=g) * 0.1,
+                  torch.zeros(30)]
+        self.adam = R.AdamState()
+        self.seen = []
+
+    def server_epoch(self, acts, labels, offsets):
+        assert acts.shape[1] == 5408 * 3 and labels.shape[1] == 3
+        for s, e in zip(offsets[:-1], offsets[1:]):
+            leaf = [t.detach().clone().requires_grad_(True) for t in self.p]
+            logits = R.bob_forward(acts[s:e], leaf, CONCAT_SPEC, None)
+            R.cross_entropy(logits.reshape(-1, 10), labels[s:e].reshape(-1)).backward()
+            R.adam_(self.p, [t.grad for t in leaf], self.adam, 1e-3, weight_decay=1e-5)
+            self.seen.append(e - s)
+
+
+def _concat_data():
+    g = torch.Generator().manual_seed(78)
+    return {k: (torch.randint(0, 256, (n, 1, 28, 28), generator=g).float(), torch.randint(7, 10, (n,), generator=g))
+            for k, n in enumerate(CONCAT_SIZES)}
+
+
+def _run_concat(rank, world, out_dir, port):
+    if world > 1:
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    full = _concat_data()
+    mine = {k: FakeSisaAlice(400 + k) for k in range(len(CONCAT_SIZES)) if spmd.owner_rank(k, world) == rank}
+    data = {k: full[k] for k in mine}
+    bob = FakeConcatBob() if rank == 0 else None
+    res = spmd.run_sisa_concat_schedule(rank, world, bob, mine, data, CONCAT_SIZES, B, 1, 2, torch.device("cpu"), unlearn=(0, 9))
+    out = {f"alice{k}": a.get_weights().numpy() for k, a in mine.items()}
+    if rank == 0:
+        out.update({f"bob{i}": p.numpy() for i, p in enumerate(bob.p)})
+        out["seen"] = np.array(bob.seen)
+        out["acts"] = res[0].numpy()
+        out["labels"] = res[1].numpy()
+    np.savez(os.path.join(out_dir, f"c{world}_r{rank}.npz"), **out)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [3, 4])
+def test_sisa_concat_schedule_matches_single_process(world):
+    """World 3: two Alices share rank 1; world 4: one Alice per rank (config 4's placement in small).
+    The concatenated cache, the batch sequence and every weight must equal the one-process run, and
+    the cache must be what the entity module defines: row j = cat_k(act_k[j]), labels [rows, K]."""
+    def collect(d, w):
+        merged = {}
+        for r in range(w):
+            with np.load(os.path.join(d, f"c{w}_r{r}.npz")) as f:
+                merged.update({k: f[k] for k in f.files})
+        return merged
+    with tempfile.TemporaryDirectory() as d:
+        _run_concat(0, 1, d, 0)
+        ref = collect(d, 1)
+        mp.spawn(_run_concat, args=(world, d, 29740 + world), nprocs=world, join=True)
+        got = collect(d, world)
+    assert set(got) == set(ref)
+    for k in ref:
+        assert np.array_equal(got[k], ref[k]), k
+    # 8 rows before the unlearning (2 full batches of the 9-sample shard), then Alice 0 loses her 9s
+    full = _concat_data()
+    n0 = int((full[0][1] != 9).sum())
+    rows_after = min(8, n0 // B * B)
+    assert ref["seen"].tolist() == [B] * (2 * 2) + [B] * (2 * rows_after // B)
+    assert ref["acts"].shape == (rows_after, 5408 * 3) and ref["labels"].shape == (rows_after, 3)
+    assert (ref["labels"][:, 0] != 9).all()
+    assert np.array_equal(ref["labels"][:, 1], full[1][1][:rows_after].numpy())
+    a1 = FakeSisaAlice(401)                      # Alice 1 never retrains after phase 1: her slot can be recomputed
+    for s in range(0, CONCAT_SIZES[1], B):
+        a1.local_step(full[1][0][s:s + B], full[1][1][s:s + B])
+    assert np.array_equal(ref["acts"][:, 5408:2 * 5408], a1.forward(full[1][0][:rows_after]).numpy())
+    assert spmd.concat_rows([16271, 21685, 15329], 16) == 15328

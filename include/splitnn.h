@@ -154,6 +154,16 @@ int sn_bob_set_lr(sn_bob* h, double lr);
  * 100 logits per client (models.py:73); the reference's own concat loop crashes before any loss
  * is computed (data_entities_sisa_concat.py:270-276), so these semantics are defined here. */
 int sn_bob_set_ce_heads(sn_bob* h, int heads);
+/* Evaluation over a whole test shard in a few launches.  By default forward batches above 64 rows
+ * take the tcgen05 GEMM (3xTF32: 1e-5 off the 16-row path, enough to flip a near-tie argmax).  After
+ * this call, sn_bob_forward calls of up to `rows` rows (<= max_batch) run the fp32
+ * weight-stream kernels in row tiles of 16 inside one launch per layer: each row's arithmetic is then
+ * exactly what a batch-of-16 loop computes, so the counters of alice.eval_breakdown
+ * (data_entities_vanilla.py:159-202; sisa :93-137) come out identical with ~7 launches per shard
+ * instead of 7 per 16 samples.  The split-K scratch grows with `rows`; when max_scratch_bytes > 0 the
+ * row count is halved until the scratch fits, and *rows_granted (nullable) returns what was set.
+ * Synchronises the device (it swaps the scratch buffer). */
+int sn_bob_set_stream_rows(sn_bob* h, int rows, size_t max_scratch_bytes, int* rows_granted);
 /* Measurement aid (no counterpart in the reference): while enabled, every launch of the two
  * weight-streaming kernels is bracketed by CUDA events on the launching stream.
  * sn_bob_profile_read sums them for kind 0 = forward (layer l), 1 = backward+update (layer l),

@@ -39,6 +39,35 @@ class RngStream:
         return False
 
 
+def entity_device(args, rank):
+    """Where an entity lives: rank 0 = Bob on `args.bob_device`; Alice r on `args.alice_devices[r]`
+    when `split_nn.place_entities` spread the Alices over the GPUs of the box (one process drives
+    them all), else on `args.alice_device`, else on the default device."""
+    from .models import default_device
+    if rank == 0:
+        return getattr(args, "bob_device", None) or default_device()
+    devs = getattr(args, "alice_devices", None)
+    if devs and rank in devs:
+        return devs[rank]
+    return getattr(args, "alice_device", None) or default_device()
+
+
+def handoff(src_device, dst_device):
+    """Order two GPUs' streams inside one process: everything enqueued so far on `src_device`'s
+    current stream happens before whatever is enqueued next on `dst_device`'s.  A no-op on one GPU.
+    (Stands where the reference has an RPC boundary: `rpc_sync` returns only when the callee is done.)"""
+    if src_device == dst_device:
+        return
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(src_device))
+    torch.cuda.current_stream(dst_device).wait_event(ev)
+
+
+def move(t, device):
+    """`t` on `device` (a stream-ordered peer copy when it lives elsewhere)."""
+    return t if t.device == device else t.to(device, non_blocking=True)
+
+
 def entity_seed(args, rank):
     """rank 0 = Bob, r >= 1 = Alice r; None when the caller did not ask for per-entity streams."""
     seeds = getattr(args, "torch_seeds", None)
@@ -145,14 +174,31 @@ def log_data_stats(logger, train, test):
     logger.info("Test dataset: {}".format(dict(Counter(test.labels_list()))))
 
 
-def eval_loop(forward_fn, test, omit_label, rng=None):
+def eval_chunk_rows():
+    """Rows per evaluation pass (SN_EVAL_CHUNK; 0 = the reference's per-batch loop, kept for A/B runs)."""
+    return int(os.environ.get("SN_EVAL_CHUNK", "4096"))
+
+
+def eval_loop(forward_fn, test, omit_label, rng=None, chunk_rows=None):
     """Shared body of `alice.eval` / `alice.eval_breakdown` (`data_entities_vanilla.py:82-98,
-    159-202`): per test batch, activations -> Bob -> first-argmax -> six counters, accumulated on
-    the device and read back once."""
+    159-202`): activations -> Bob -> first-argmax -> six counters, accumulated on the device and
+    read back once.  The reference walks the test loader 16 samples at a time (an RPC per batch);
+    here a whole chunk of the shard (`chunk_rows`, default 4096) goes through in one pass: one conv
+    launch, one launch (+ its split-K reduction) per server layer, one counter launch.  Every row
+    still gets exactly the numbers the batch-of-16 loop gives it (the server's forward runs the same
+    fp32 weight-stream kernels in row tiles of 16), so the counters are identical;
+    tests/test_gpu_entities.py checks that.  The generator is consumed as by one pass over the loader."""
+    chunk = eval_chunk_rows() if chunk_rows is None else int(chunk_rows)
     counters = torch.zeros(6, dtype=torch.int64, device=test.device)
-    for x, y in test.batches(rng):
-        out = forward_fn(x)
-        E.eval_counts(out, y, -1 if omit_label is None else omit_label, counters)
+    omit = -1 if omit_label is None else omit_label
+    if chunk <= test.batch_size:
+        for x, y in test.batches(rng):
+            E.eval_counts(forward_fn(x), y, omit, counters)
+    else:
+        x, y = test.epoch(rng)
+        chunk -= chunk % test.batch_size                      # whole loader batches per pass
+        for s in range(0, test.n, chunk):
+            E.eval_counts(forward_fn(x[s:s + chunk]), y[s:s + chunk], omit, counters)
     return [int(v) for v in counters.cpu().tolist()]
 
 

@@ -40,6 +40,7 @@ SIGNATURES = {
     "sn_bob_set_opt_step": (_i, [_vp, _i, _i64]),
     "sn_bob_set_lr": (_i, [_vp, _d]),
     "sn_bob_set_ce_heads": (_i, [_vp, _i]),
+    "sn_bob_set_stream_rows": (_i, [_vp, _i, _sz, C.POINTER(_i)]),
     "sn_bob_profile": (_i, [_vp, _i]),
     "sn_bob_profile_read": (_i, [_vp, _i, _i, C.POINTER(_d), C.POINTER(_i)]),
     "sn_bob_train_step": (_i, [_vp, _i, _vp, _vp, _i, _pp, _u64, _u64, _vp, _vp, _vp, _vp]),

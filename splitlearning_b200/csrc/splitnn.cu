@@ -274,9 +274,12 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
                              int relu, const uint8_t* mask, float keep_prob, float scale, uint64_t seed,
                              uint64_t offset, int layer, float* H, int ldh, float* out2, float* P, int sms,
                              cudaStream_t st, Profiler* prof = nullptr, const CeTail* ce = nullptr,
-                             bool* ce_fused = nullptr, int l2_keep_w = 0, bool prefetch_w = false) {
+                             bool* ce_fused = nullptr, int l2_keep_w = 0, bool prefetch_w = false,
+                             int skinny_max = kSkinnyFwdMaxB) {
+  // skinny_max: batches up to this many rows go through the fp32 weight-stream kernels in row tiles
+  // of 16 (every row's arithmetic is then independent of the batch it arrives in)
   if (ce_fused) *ce_fused = false;
-  if (B <= kSkinnyFwdMaxB && (size_t)N * K <= kSmallLayerElems && K <= kSmallLayerMaxK) {
+  if (B <= skinny_max && (size_t)N * K <= kSmallLayerElems && K <= kSmallLayerMaxK) {
     dim3 grid(ceil_div(N, kHeadRows), ceil_div(B, kBT));
     const size_t smem_small = 0;
     cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
@@ -301,7 +304,7 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
     launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, P, p.qmax, kBT, B, N, bias, relu, mask, keep_prob,
              scale, seed, offset, layer, H, ldh, out2, 0, 0);
     SN_LAUNCH_CHECK();
-  } else if (B <= kSkinnyFwdMaxB && (K % 4) == 0) {
+  } else if (B <= skinny_max && (K % 4) == 0) {
     FwdPlan p = plan_fwd(K, N, sms);
     int tiles = ceil_div(B, kBT), Bpad = tiles * kBT;
     size_t smem = (size_t)kBT * p.kc * 4 + (size_t)8 * kFwdRing * 8 * 32 * 16;   // X chunk + per-warp W rings
@@ -343,8 +346,8 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
   return 0;
 }
 
-static size_t fwd_partial_floats(int B, int K, int N, int sms) {
-  if (B > kSkinnyFwdMaxB || ((size_t)N * K <= kSmallLayerElems && K <= kSmallLayerMaxK)) return 0;
+static size_t fwd_partial_floats(int B, int K, int N, int sms, int skinny_max = kSkinnyFwdMaxB) {
+  if (B > skinny_max || ((size_t)N * K <= kSmallLayerElems && K <= kSmallLayerMaxK)) return 0;
   if ((K % 4) != 0) return 0;
   FwdPlan p = plan_fwd(K, N, sms);
   size_t need = (size_t)kFwdSlots * p.ksplit * round_up(B, kBT) * N;
@@ -370,6 +373,7 @@ struct sn_bob {
   std::vector<Slot> slots;
   std::vector<float*> H, dZ;   // index l = 1..L ([Bpad][dims[l]])
   float* P = nullptr;          // forward split-K partials
+  int stream_rows = kSkinnyFwdMaxB;   // forward batches up to this many rows use the weight-stream kernels
   float* PA = nullptr;         // backward dA partials
   size_t PA_floats = 0;
   float* dWbuf = nullptr;      // general-batch path only (lazy)
@@ -772,6 +776,30 @@ int sn_bob_profile_read(sn_bob* h, int kind, int layer, double* total_ms, int* l
   *launches = n;
   return 0;
 }
+int sn_bob_set_stream_rows(sn_bob* h, int rows, size_t max_scratch_bytes, int* rows_granted) {
+  SN_BOB_ENTER(h);
+  SN_REQUIRE(rows >= 1, "sn_bob_set_stream_rows: rows must be positive");
+  rows = std::min(rows, h->max_batch);
+  auto need = [&](int r) {
+    size_t f = 16;
+    for (int l = 0; l < h->L; ++l) f = std::max(f, fwd_partial_floats(r, h->dims[l], h->dims[l + 1], h->sms, r));
+    return f * 4;
+  };
+  int r = std::max(rows, kSkinnyFwdMaxB);
+  r = std::min(round_up(r, kBT), std::max(kSkinnyFwdMaxB, h->max_batch));
+  if (max_scratch_bytes)
+    while (r > kSkinnyFwdMaxB && need(r) > max_scratch_bytes) r = std::max(kSkinnyFwdMaxB, (r / 2 + kBT - 1) / kBT * kBT);
+  const size_t bytes = std::max(need(r), need(std::min(h->max_batch, kSkinnyFwdMaxB)));
+  float* p = nullptr;
+  SN_CUDA(cudaMalloc(&p, bytes));
+  SN_CUDA(cudaDeviceSynchronize());           // the old buffer may still be in use by queued kernels
+  cudaFree(h->P);
+  h->P = p;
+  h->stream_rows = r;
+  if (rows_granted) *rows_granted = r;
+  return 0;
+}
+
 int sn_bob_set_ce_heads(sn_bob* h, int heads) {
   SN_BOB_ENTER(h);
   SN_REQUIRE(heads >= 1 && h->dims[h->L] % heads == 0, "sn_bob_set_ce_heads: heads must divide the output width");
@@ -787,7 +815,7 @@ int sn_bob_set_ce_heads(sn_bob* h, int heads) {
 
 static int bob_forward_impl(sn_bob* h, const float* act, int B, int train, const uint8_t* const* masks, uint64_t seed,
                             uint64_t offset, float* out, cudaStream_t st, const CeTail* ce = nullptr,
-                            bool* ce_fused = nullptr) {
+                            bool* ce_fused = nullptr, int skinny_max = kSkinnyFwdMaxB) {
   if (ce_fused) *ce_fused = false;
   const float keep = 1.f - h->dropout_p, scale = 1.f / keep;
   const float* X = act;
@@ -807,7 +835,8 @@ static int bob_forward_impl(sn_bob* h, const float* act, int B, int train, const
       SN_LAUNCH_CHECK();
     } else if (launch_linear_fwd(X, ldx, B, h->W[l], h->b[l], K, N, relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N,
                                  last ? out : nullptr, h->P, h->sms, st, &h->prof, last ? ce : nullptr,
-                                 last ? ce_fused : nullptr, h->l2_keep[l], !just_written(h->W[l], (size_t)N * K * 4)))
+                                 last ? ce_fused : nullptr, h->l2_keep[l], !just_written(h->W[l], (size_t)N * K * 4),
+                                 skinny_max))
       return 1;
     X = h->H[l + 1];
     ldx = N;
@@ -1033,7 +1062,8 @@ int sn_bob_forward(sn_bob* h, const float* act, int B, int train_mode, const uin
   h->pf_valid = false;
   h->stashed = train_mode != 0;
   h->stashed_B = B;
-  return bob_forward_impl(h, act, B, train_mode, drop_masks, seed, offset, out, (cudaStream_t)stream);
+  return bob_forward_impl(h, act, B, train_mode, drop_masks, seed, offset, out, (cudaStream_t)stream, nullptr, nullptr,
+                          h->stream_rows);
 }
 
 int sn_bob_backward_update(sn_bob* h, int slot, const float* act, const float* dout, int B, float* cut_grad,

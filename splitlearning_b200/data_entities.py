@@ -22,8 +22,8 @@ from copy import deepcopy
 import torch
 
 from . import engine as E
-from ._entity_common import (DeviceDataset, RngStream, bob_log_accuracy, entity_seed, eval_loop, filter_label,
-                             load_loader, log_breakdown, log_data_stats, make_logger)
+from ._entity_common import (DeviceDataset, RngStream, bob_log_accuracy, entity_device, entity_seed, eval_loop,
+                             filter_label, load_loader, log_breakdown, log_data_stats, make_logger, move)
 from .models import default_device, model1, model2, model3
 
 
@@ -33,7 +33,8 @@ class alice(object):
         self.epochs = args.epochs
         self.start_logger()
         self.bob = server
-        self.device = getattr(args, "alice_device", None) or default_device()
+        self.device = entity_device(args, rank)
+        self.logger.info(f"Alice-{rank} on {self.device}")
         self.rng = RngStream(entity_seed(args, rank))
         with self.rng:
             self.model1 = model1(self.device)       # construction order as in the reference (:31-32)
@@ -51,10 +52,12 @@ class alice(object):
 
     def _run_batches(self, dataset):
         for inputs, labels in dataset.batches(self.rng):
-            a1 = self.head.forward(inputs)
-            hb = self.bob.inference_train(a1)
+            # the four hops of the U-shape step (:70-79); each `move` is a stream-ordered NVLink copy
+            # when Bob sits on another GPU of the box, and nothing at all on one GPU
+            a1 = move(self.head.forward(inputs), self.bob.device)
+            hb = move(self.bob.inference_train(a1), self.device)
             _, dhb, _ = self.tail.train_step(hb, labels, want_cut_grad=True)
-            cut = self.bob.backward(a1, dhb, self.slot)
+            cut = move(self.bob.backward(a1, move(dhb, self.bob.device), self.slot), self.device)
             self.head.backward_update(inputs, cut)
 
     def train(self, last_alice_rref, last_alice_id):
@@ -73,7 +76,7 @@ class alice(object):
         return [deepcopy(self.model1.state_dict()), deepcopy(self.model2.state_dict())]
 
     def _predict(self, x):
-        return self.model2(self.bob.inference(self.head.forward(x)))
+        return self.model2(move(self.bob.inference(move(self.head.forward(x), self.bob.device)), self.device))
 
     def eval(self):
         c = eval_loop(self._predict, self.test_data, None, self.rng)
@@ -111,7 +114,7 @@ class alice(object):
 class bob(object):
     def __init__(self, args):
         self.server = self
-        self.device = getattr(args, "bob_device", None) or default_device()
+        self.device = entity_device(args, 0)
         self.rng = RngStream(entity_seed(args, 0))
         with self.rng:
             self.model = model2(self.device)
@@ -124,6 +127,7 @@ class bob(object):
         self.last_alice_id = None
         self.client_num_in_total = args.client_num_in_total
         self.start_logger()
+        self.logger.info(f"Bob on {self.device}")
 
     def train_request(self, client_id):
         self.logger.info(f"Train Request for Alice-{client_id}")

@@ -28,7 +28,8 @@ from .models import model2_sisa_concat
 
 class alice(sisa.alice):
     def _predict(self, x):
-        return self.bob.inference_slot(self.engine.forward(x), self.client_id)
+        out = self.bob.inference_slot(self.engine.forward(x), self.client_id)
+        return out if out.device == self.device else out.to(self.device, non_blocking=True)
 
     def eval(self):
         self.bob.switch_mode_to_eval()

@@ -21,8 +21,8 @@ import torch
 from tqdm import tqdm
 
 from . import engine as E
-from ._entity_common import (DeviceDataset, RngStream, bob_log_accuracy, entity_seed, eval_loop, filter_label,
-                             load_loader, log_breakdown, log_data_stats, make_logger)
+from ._entity_common import (DeviceDataset, RngStream, bob_log_accuracy, entity_device, entity_seed, eval_loop,
+                             filter_label, handoff, load_loader, log_breakdown, log_data_stats, make_logger, move)
 from .models import default_device, model1_sisa, model2_sisa
 
 
@@ -33,6 +33,7 @@ class StepContext:
     def __init__(self, slot):
         self.slot = slot
         self.cut_grad = None
+        self.cut_out = None        # where Bob should write the cut-layer gradient (Alice on another GPU)
 
 
 class alice(object):
@@ -41,7 +42,8 @@ class alice(object):
         self.epochs = args.epochs
         self.start_logger()
         self.bob = server
-        self.device = getattr(args, "alice_device", None) or default_device()
+        self.device = entity_device(args, rank)
+        self.logger.info(f"Alice-{rank} on {self.device}")
         self.rng = RngStream(entity_seed(args, rank))
         with self.rng:
             self.model = model1_sisa(self.device)
@@ -63,11 +65,32 @@ class alice(object):
             self.train_batch(inputs, labels)
 
     def train_batch(self, inputs, labels):
-        """One split step (:70-76) on a device-resident batch; returns the loss (device scalar)."""
-        activation_alice = self.engine.forward(inputs)
-        loss = self.bob.train_and_backward(activation_alice, labels, self.context)
+        """One split step (:70-76) on a device-resident batch; returns the loss (device scalar).
+        With Bob on another GPU of the box nothing is copied: Alice's conv kernel stores its
+        activations straight into a buffer in Bob's HBM over NVLink, Bob's last backward kernel
+        stores the cut-layer gradient into Alice's, and two events order the two streams."""
+        bob_dev = self.bob.device
+        if bob_dev == self.device:
+            activation_alice = self.engine.forward(inputs)
+            loss = self.bob.train_and_backward(activation_alice, labels, self.context)
+            self.engine.backward_update(inputs, self.context.cut_grad)
+            return loss
+        n = inputs.shape[0]
+        if getattr(self, "_act_on_bob", None) is None:
+            self._act_on_bob = torch.empty(self.batch_size, 5408, device=bob_dev)
+            self._cut_here = torch.empty(self.batch_size, 5408, device=self.device)
+        activation_alice = self.engine.forward(inputs, out=self._act_on_bob[:n])
+        labels_bob = move(labels, bob_dev)
+        handoff(self.device, bob_dev)
+        self.context.cut_out = self._cut_here[:n]
+        loss = self.bob.train_and_backward(activation_alice, labels_bob, self.context)
+        handoff(bob_dev, self.device)
         self.engine.backward_update(inputs, self.context.cut_grad)
         return loss
+
+    def _predict(self, x):
+        """Test batch -> Bob's logits, back on this Alice's GPU for the counters."""
+        return move(self.bob.inference(move(self.engine.forward(x), self.bob.device)), self.device)
 
     def train(self, last_alice_rref, last_alice_id):
         self.logger.info("Training")
@@ -83,7 +106,7 @@ class alice(object):
         return deepcopy(self.model.state_dict())
 
     def eval(self):
-        c = eval_loop(lambda x: self.bob.inference(self.engine.forward(x)), self.test_data, None, self.rng)
+        c = eval_loop(self._predict, self.test_data, None, self.rng)
         self.logger.info(f"Alice-{self.client_id} Evaluating Data: {round(c[0] / c[1], 3)}")
         return c[0], c[1]
 
@@ -114,7 +137,7 @@ class alice(object):
             self._run_batches(self.unlearn_data)
 
     def eval_breakdown(self, omit_label):
-        c = eval_loop(lambda x: self.bob.inference(self.engine.forward(x)), self.test_data, omit_label, self.rng)
+        c = eval_loop(self._predict, self.test_data, omit_label, self.rng)
         log_breakdown(self.logger, self.client_id, omit_label, c, vanilla_style=True)
         return tuple(c)
 
@@ -129,10 +152,11 @@ class alice(object):
 class bob(object):
     def __init__(self, args):
         self.server = self
-        self.device = getattr(args, "bob_device", None) or default_device()
+        self.device = entity_device(args, 0)
         self.rng = RngStream(entity_seed(args, 0))
         with self.rng:
             self.model = model2_sisa(self.device)
+        self.model.eval_batch = args.batch_size
         if getattr(args, "dropout_parity", False):       # draw masks from torch's CPU stream like the reference
             from .models import TorchCpuMasks
             self.model.mask_source = TorchCpuMasks(self.model.dims[1:-1], self.model.dropout_p)
@@ -148,13 +172,14 @@ class bob(object):
                        for rank in range(args.client_num_in_total)}
         self.last_alice_id = None
         self.start_logger()
+        self.logger.info(f"Bob on {self.device}")
         self.last_loss = None
 
     def train_and_backward(self, x, labels, context_id):
         with self.rng:
             masks, seed, offset = self.model.dropout_args(x.shape[0], x.device)
         loss, cut, _ = self.engine.train_step(x, labels, slot=context_id.slot, masks=masks, seed=seed, offset=offset,
-                                              want_cut_grad=True)
+                                              want_cut_grad=True, cut_out=getattr(context_id, "cut_out", None))
         context_id.cut_grad = cut
         self.last_loss = loss
         return loss

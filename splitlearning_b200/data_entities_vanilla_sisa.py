@@ -28,8 +28,8 @@ from copy import deepcopy
 import torch
 
 from . import engine as E
-from ._entity_common import (DeviceDataset, RngStream, bob_log_accuracy, entity_seed, eval_loop, filter_label,
-                             load_loader, log_breakdown, log_data_stats, make_logger)
+from ._entity_common import (DeviceDataset, RngStream, bob_log_accuracy, entity_device, entity_seed, eval_loop,
+                             filter_label, load_loader, log_breakdown, log_data_stats, make_logger, move)
 from .models import TorchCpuMasks, default_device, model1_sisa, model2_sisa
 
 
@@ -59,7 +59,8 @@ class alice(object):
         self.server_epochs = args.server_epochs
         self.start_logger()
         self.bob = server
-        self.device = getattr(args, "alice_device", None) or default_device()
+        self.device = entity_device(args, rank)
+        self.logger.info(f"Alice-{rank} on {self.device}")
         self.rng = RngStream(entity_seed(args, rank))
         with self.rng:
             self.model = model1_sisa(self.device)
@@ -85,15 +86,19 @@ class alice(object):
         assert not self.frozen, "weights are frozen"
         self._local_epochs(self.train_data)
 
+    def _predict(self, x):
+        """Test batch -> Bob's logits, back on this Alice's GPU for the counters."""
+        return move(self.bob.inference(move(self.engine.forward(x), self.bob.device)), self.device)
+
     def eval(self):
         self.bob.switch_mode_to_eval()
-        c = eval_loop(lambda x: self.bob.inference(self.engine.forward(x)), self.test_data, None, self.rng)
+        c = eval_loop(self._predict, self.test_data, None, self.rng)
         self.logger.info(f"Alice-{self.client_id} Evaluating Data: {round(c[0] / c[1], 3)}")
         return c[0], c[1]
 
     def eval_breakdown(self, omit_label):
         self.bob.switch_mode_to_eval()
-        c = eval_loop(lambda x: self.bob.inference(self.engine.forward(x)), self.test_data, omit_label, self.rng)
+        c = eval_loop(self._predict, self.test_data, omit_label, self.rng)
         log_breakdown(self.logger, self.client_id, omit_label, c, vanilla_style=False)
         return tuple(c)
 
@@ -127,9 +132,15 @@ class alice(object):
         out_device = out_device or self.device
         if out_device == self.device:
             acts = self.engine.forward(x)
-        else:                                      # Alice on another GPU: compute locally, one NVLink copy
-            acts = self.engine.forward(x).to(out_device, non_blocking=True)
+        else:
+            # Alice on another GPU of the box: her kernel stores the whole block straight into Bob's
+            # HBM over NVLink (no local staging copy); Bob's stream then waits for hers
+            from ._entity_common import handoff
+            acts = torch.empty(x.shape[0], 5408, device=out_device)
+            if x.shape[0]:
+                self.engine.forward(x, out=acts)
             y = y.to(out_device, non_blocking=True)
+            handoff(self.device, out_device)
         return ActivationCache(acts, y, data.batch_size)
 
     def give_weights(self):
@@ -162,16 +173,18 @@ class alice(object):
 class bob(object):
     def __init__(self, args):
         self.server = self
-        self.device = getattr(args, "bob_device", None) or default_device()
+        self.device = entity_device(args, 0)
         self.rng = RngStream(entity_seed(args, 0))
         with self.rng:
             self.model = self._make_model(args)
+        self.model.eval_batch = args.batch_size
         if getattr(args, "dropout_parity", False):
             self.model.mask_source = TorchCpuMasks(self.model.dims[1:-1], self.model.dropout_p)
         self.server_epochs = args.server_epochs
         self.client_num_in_total = args.client_num_in_total
         self.batch_size = args.batch_size
         self.start_logger()
+        self.logger.info(f"Bob on {self.device}")
         # torch.optim.Adam(lr, weight_decay=1e-5) over Bob's parameters (:266)
         self.engine = self.model.make_engine(optimizer=E.SN_OPT_ADAM, lr=args.lr, weight_decay=1e-5,
                                              n_opt_slots=1, max_batch=args.batch_size)

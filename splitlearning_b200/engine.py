@@ -149,6 +149,14 @@ class BobEngine:
     def set_ce_heads(self, heads):
         check(self.lib.sn_bob_set_ce_heads(self.h, int(heads)))
 
+    def set_stream_rows(self, rows, max_scratch_bytes=1 << 30):
+        """Let eval-mode `forward` calls of up to `rows` rows run the exact fp32 weight-stream
+        kernels (row tiles of 16 in one launch per layer); returns the row count granted."""
+        got = C.c_int(0)
+        check(self.lib.sn_bob_set_stream_rows(self.h, int(rows), int(max_scratch_bytes), C.byref(got)))
+        self.stream_rows = got.value
+        return got.value
+
 
 class ShardEngine:
     """`sn_shard`: rows [n_off, n_off+n_rows) of a Linear(+ReLU, dropout) layer with that slice's

@@ -125,14 +125,43 @@ class _ServerMLP(nn.Module):
             return self.mask_source.draw(batch, device), 0, 0
         return self.mask_source.next()
 
+    # Inference over more than 64 rows (a whole test shard at once): chunks of up to this many rows go
+    # through the exact fp32 weight-stream kernels in one launch per layer (sn_bob_set_stream_rows), so
+    # every row gets the numbers a batch-of-16 loop would give it.
+    max_infer_rows = 4096
+    # rows per dropout draw in train-mode inference with TorchCpuMasks: the reference draws one mask per
+    # loader batch, so a fused pass must consume the CPU stream batch by batch (None: one draw per call)
+    eval_batch = None
+
+    def _chunk_masks(self, rows, device):
+        """(masks, seed, offset) for a train-mode inference chunk of `rows` rows."""
+        bs = self.eval_batch
+        if bs and isinstance(self.mask_source, TorchCpuMasks) and self.dropout_p > 0 and rows > bs:
+            per_layer = [[] for _ in self.mask_source.widths]
+            for s in range(0, rows, bs):
+                for l, m in enumerate(self.mask_source.draw(min(bs, rows - s), device)):
+                    per_layer[l].append(m)
+            return [torch.cat(ms, 0) for ms in per_layer], 0, 0
+        return self.dropout_args(rows, device)
+
     def forward(self, x):
         w0 = self.weight_list()[0]
         x = torch.flatten(x.to(device=w0.device, dtype=torch.float32), 1).contiguous()
         B = x.shape[0]
-        if self._infer is None or self._infer.max_batch < B or self._infer.weights[0].data_ptr() != w0.data_ptr():
-            self._infer = self.make_engine(optimizer=E.SN_OPT_NONE, max_batch=max(B, 16))
-        masks, seed, offset = self.dropout_args(B, x.device) if self.training else (None, 0, 0)
-        return self._infer.forward(x, train_mode=self.training, masks=masks, seed=seed, offset=offset)
+        want = B if B <= 64 else min(B, self.max_infer_rows)
+        if self._infer is None or self._infer.max_batch < want or self._infer.weights[0].data_ptr() != w0.data_ptr():
+            self._infer = self.make_engine(optimizer=E.SN_OPT_NONE, max_batch=max(want, 16))
+            self._infer_rows = self._infer.set_stream_rows(want) if want > 64 else self._infer.max_batch
+        rows = max(1, min(self._infer_rows, self._infer.max_batch))
+        if B <= rows:
+            masks, seed, offset = self._chunk_masks(B, x.device) if self.training else (None, 0, 0)
+            return self._infer.forward(x, train_mode=self.training, masks=masks, seed=seed, offset=offset)
+        out = torch.empty(B, self.dims[-1], device=x.device)
+        for s in range(0, B, rows):
+            n = min(rows, B - s)
+            masks, seed, offset = self._chunk_masks(n, x.device) if self.training else (None, 0, 0)
+            self._infer.forward(x[s:s + n], train_mode=self.training, masks=masks, seed=seed, offset=offset, out=out[s:s + n])
+        return out
 
 
 class model2(_ServerMLP):

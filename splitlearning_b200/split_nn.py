@@ -4,8 +4,10 @@
 The reference spawns world_size processes joined by torch.distributed.rpc (rank 0 = Bob, the
 others idle RPC servers hosting one Alice each).  Here one process drives every entity: Bob and the
 Alices are plain objects whose methods enqueue CUDA work; with several GPUs visible Bob sits on
-cuda:0 and Alice r on cuda:(1 + (r-1) mod (n_gpus-1)), activations and cut-layer gradients moving
-over NVLink peer copies.  `--world_size` keeps its meaning: 1 server + (world_size-1) clients.
+cuda:0 and Alice r on cuda:(1 + (r-1) mod (n_gpus-1)) (`place_entities`; every entity logs its
+device), the producing kernel storing activations / cut-layer gradients straight into the consuming
+GPU's memory over NVLink with events ordering the streams.  `--world_size` keeps its meaning:
+1 server + (world_size-1) clients.  (The one-process-per-GPU form that bench.py times is spmd.py.)
 
     python -m splitlearning_b200.split_nn --vanilla --world_size 5 --epochs 1 --iterations 1
 """
@@ -44,6 +46,7 @@ def build_parser():
     # additions (absent from the reference; defaults keep its behaviour)
     parser.add_argument('--synthetic_samples', type=int, default=70000, help='size of the synthetic MNIST-shaped set used when no mnist_784.npz is under --datapath')
     parser.add_argument('--seed', type=int, default=None, help='seed numpy/random (partition) and give every entity its own torch stream (Bob 100, Alice r 200+r)')
+    parser.add_argument('--n_gpus', type=int, default=None, help='use at most this many of the visible GPUs (Bob on cuda:0, Alices on the others); default: all')
     parser.add_argument('--dropout_parity', action='store_true', help="draw dropout masks from torch's CPU generator like the reference instead of in-kernel Philox")
     return parser
 
@@ -61,13 +64,23 @@ def validate(args):
 
 
 def place_entities(args):
-    """Bob on cuda:0; Alices spread over the remaining GPUs when there are any."""
+    """Bob on cuda:0; Alice r on cuda:(1 + (r-1) mod (n-1)) when the box shows n > 1 GPUs (all on
+    cuda:0 otherwise).  `--n_gpus` limits how many of the visible GPUs are used.  Peer access is
+    enabled between all of them: the entity classes let a kernel on one GPU store its result in
+    another GPU's memory."""
     n = torch.cuda.device_count()
     if n == 0:
         from ._lib import SplitNNError
         raise SplitNNError("no CUDA device: the split-NN hot path has no CPU fallback")
+    want = getattr(args, "n_gpus", None)
+    n = max(1, min(n, want)) if want else n
     args.bob_device = torch.device("cuda", 0)
     args.n_gpus = n
+    args.alice_devices = {r: torch.device("cuda", 0 if n == 1 else 1 + (r - 1) % (n - 1))
+                          for r in range(1, args.client_num_in_total + 1)}
+    if n > 1:
+        from . import _lib
+        _lib.check(_lib.load().sn_p2p_enable_all(n))
     return args
 
 

@@ -363,8 +363,8 @@ class _CudaSisaAlice:
     def local_epoch(self, x, y, B):
         self.eng.local_epoch(x, y, B)
 
-    def forward(self, x):
-        return self.eng.forward(x)
+    def forward(self, x, out=None, ld=None):
+        return self.eng.forward(x, out=out, ld=ld)
 
     def reset_opt(self):
         self.eng.reset_opt()

@@ -96,7 +96,10 @@ REF_MAX_STEPS = 300           # the RPC reference runs ~150 ms per step: keep th
 
 def turn_for(steps):
     """Steps an Alice trains before the next one takes over.  The driver's short run (20 steps) must
-    still see every Alice train and time Alice->Alice hand-offs; long runs use 64."""
+    still see every Alice train and time Alice->Alice hand-offs; long runs use 64.  (SN_TURN overrides,
+    for A/B timing of the hand-off cost.)"""
+    if os.environ.get("SN_TURN"):
+        return max(1, int(os.environ["SN_TURN"]))
     return max(1, min(64, steps // N_ALICES))
 
 
@@ -198,8 +201,8 @@ def run_ours_single(args):
     xs, ys = synthetic_batches(torch, nb, dev)
     seed_ctr = [0]
 
-    def hand_off(src, dst):      # give_weights / load_state_dict between consecutive Alices
-        dst[0].load_state_dict(src[0].state_dict())
+    def hand_off(src, dst):      # the Alice -> Alice weight hand-off, as alice.train does it
+        dst[0].copy_weights_from(src[0])
 
     from splitlearning_b200 import engine as E
     act_buf = torch.empty(B, D0, device=dev)
@@ -242,13 +245,14 @@ def run_ours_single(args):
     # The loss read: ce_kernel stores each step's loss straight into pinned host memory (UVA-mapped,
     # 4 B over PCIe per step); a cudaMemcpyAsync D2H on the compute stream instead costs 7 us/step
     # (profiles/micro/e2e_variants.py: 193.6 -> 186.6 us/step).
-    from splitlearning_b200.io import iterate_host_batches
+    from splitlearning_b200.io import HostBatchPrefetcher, iterate_host_batches
     hx, hy = synthetic_batches(torch, nb, pin=True)
     hloss = torch.zeros(K + W, dtype=torch.float32).pin_memory()
+    prefetcher = HostBatchPrefetcher(dev, B)          # side stream + staging buffers: set up once, like a DataLoader
 
     def e2e_run(first, count):
         host = ((hx[i % nb], hy[i % nb]) for i in range(first, first + count))
-        for j, (dx, dy) in enumerate(iterate_host_batches(host, dev, B)):
+        for j, (dx, dy) in enumerate(iterate_host_batches(host, dev, B, prefetcher)):
             step(first + j, dx, dy, hloss[first + j])
 
     e2e_run(0, W)

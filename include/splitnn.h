@@ -59,6 +59,15 @@ int sn_get_matmul_precision(void);
  * (No counterpart in the reference.) */
 int sn_set_skinny_tensor_forward(int on);
 int sn_get_skinny_tensor_forward(void);
+/* Run the small middle of a batch <= 16 training step of a three-layer server (first layer's
+ * epilogue, second layer forward, its epilogue, last layer forward, loss, last layer backward, second
+ * layer backward + update, its input-gradient reduction) as ONE persistent kernel whose phases meet
+ * at grid-wide barriers (1), or as seven dependent launches (0, default).  Results are bit-identical.
+ * north_star asked for "a persistent whole-MLP kernel"; built and MEASURED SLOWER on B200: 76-83 us
+ * against 51 us for the seven launches (profiles/r2e_trace_vanilla_tail.txt).  Kept
+ * selectable, with its parity tests, as that measured answer.  (No counterpart in the reference.) */
+int sn_set_persistent_tail(int on);
+int sn_get_persistent_tail(void);
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 uint64_t sn_launch_count(void);
 
@@ -68,6 +77,12 @@ uint64_t sn_launch_count(void);
  * (index c*169+h*13+w).  Replaces model1_sisa.forward / model1.forward, models.py:27-30,11-14. */
 int sn_conv_pool_forward(const float* x, const float* w, const float* b, int B, float* act,
                          void* stream);
+
+/* dst <- src for one conv block's parameters (w [32,1,3,3], b [32]; device pointers on the current
+ * device, or peer-accessible): the Alice -> Alice weight hand-off of the vanilla / U-shape protocol,
+ * `self.model.load_state_dict(last_alice_rref.rpc_sync().give_weights())`, data_entities_vanilla.py:59-64,
+ * as one small launch in the stream's kernel chain. */
+int sn_conv_weights_copy(float* dst_w, float* dst_b, const float* src_w, const float* src_b, void* stream);
 
 /* Weight/bias gradient of the block above given dL/dact [B,5408]; no input gradient (the input
  * is data).  dw [32*9], db [32].  `scratch` >= sn_conv_pool_backward_scratch_bytes(B) bytes.

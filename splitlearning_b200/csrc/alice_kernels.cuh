@@ -83,7 +83,8 @@ __global__ void __launch_bounds__(256) conv_pool_fwd_kernel(const float* __restr
 // Lanes are consecutive pooled positions: a warp's store is one contiguous run of a channel row.
 constexpr int kStreamThreads = 352;
 
-__global__ void __launch_bounds__(kStreamThreads, 2) conv_pool_stream_kernel(const float* __restrict__ x,
+template <int CTAS_PER_SM>
+__global__ void __launch_bounds__(kStreamThreads, CTAS_PER_SM) conv_pool_stream_kernel(const float* __restrict__ x,
                                                                              const float* __restrict__ w,
                                                                              const float* __restrict__ bias, int B,
                                                                              float* __restrict__ act, size_t ld_act) {
@@ -156,6 +157,17 @@ __global__ void __launch_bounds__(kStreamThreads, 2) conv_pool_stream_kernel(con
     }
   }
   asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+
+// The Alice -> Alice weight hand-off: 288 + 32 floats, one small CTA in the step's launch chain (two
+// cudaMemcpyAsync device copies in its place cost ~40 us per hand-off: copy-engine latency, and the
+// chain of dependent launches is broken twice).
+__global__ void __launch_bounds__(128) conv_weights_copy_kernel(float* __restrict__ dw, float* __restrict__ db,
+                                                                const float* __restrict__ sw, const float* __restrict__ sb) {
+  pdl_wait();
+  pdl_launch();
+  for (int t = threadIdx.x; t < 288; t += 128) dw[t] = sw[t];
+  if (threadIdx.x < 32) db[threadIdx.x] = sb[threadIdx.x];
 }
 
 // Weight gradient.  grid (gx, 4): CTA (bx, cg) loops over samples bx, bx+gx, ...; warp = one

@@ -10,6 +10,26 @@
 
 namespace sn {
 
+// How a kernel body meets the work it depends on.  As its own launch: programmatic dependent launch
+// (wait for the previous kernel, then let the next one start its prologue).  As one phase of the
+// persistent tail kernel (tail_kernel.cuh): a grid-wide barrier.
+struct PdlSync {
+  static constexpr bool kCoherent = false;
+  __device__ __forceinline__ void operator()() const {
+    pdl_wait();
+    pdl_launch();
+  }
+};
+// Load of a value that an EARLIER PHASE may have produced.  Across kernel launches the read-only path
+// (ld.global.nc) is fine: the producer is another kernel.  Inside the persistent tail kernel the
+// producer is another CTA of the same launch, the non-coherent path and L1 are off limits, and the
+// load goes to L2 (ld.global.cg).
+template <class Sync, class T>
+__device__ __forceinline__ T ld_dep(const T* p) {
+  if constexpr (Sync::kCoherent) return __ldcg(p);
+  else return __ldg(p);
+}
+
 // ------------------------------------------------------------------------------------------
 // Forward, skinny: P[ks][b][n] = sum_{k in chunk ks} X[b][k] * W[n][k]
 //   grid (nx, ksplit, batch tiles), 256 threads.  The CTA stages its X chunk [16][kc] in
@@ -103,19 +123,19 @@ __device__ __forceinline__ void cp_async16_zfill(void* smem, const void* gmem, b
 // R = weight rows per tile (8 or 4), WPC = 64 / R warps per CTA: the same 128 KB of W rings and the
 // same FMAs per SM either way; R = 4 halves the accumulators per thread (64 instead of 128
 // registers), which lets 16 warps instead of 8 be resident to hide the FMA / LDS latencies.
-template <int R>
-__global__ void __launch_bounds__(32 * (64 / R), 1)
-fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N,
-                  int K, int kc, float* __restrict__ P, int Bpad, int ksplit, int prefetch_early, int l2_keep_w) {
-  extern __shared__ float4 smem4[];
+template <int R, class Sync>
+__device__ __forceinline__ void
+fwd_skinny_body(float4* smem4, const dim3 bid, const int gdx, Sync sync,
+                const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N,
+                int K, int kc, float* __restrict__ P, int Bpad, int ksplit, int prefetch_early, int l2_keep_w) {
   // rows below l2_keep_w are tagged evict_last (see l2_policy), the others stream
   const uint64_t pol_keep = l2_policy(1);
   constexpr int WPC = 64 / R, NT = 32 * WPC;        // warps, threads per CTA
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int ks = blockIdx.y, k0 = ks * kc;
+  const int ks = bid.y, k0 = ks * kc;
   const int klen = min(kc, K - k0);
   const int iters = (klen + 127) >> 7;
-  const int b0 = blockIdx.z * kBT, nb = min(kBT, B - b0);
+  const int b0 = bid.z * kBT, nb = min(kBT, B - b0);
   const int kc4 = kc >> 2;
   float4* wring = smem4 + kBT * kc4 + warp * (kFwdRing * R * 32);   // after the X chunk
 #ifdef SN_TIMING
@@ -129,7 +149,7 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
   // a warp's range must be at least one row group long, or a group could be cut into three or more
   // pieces and two of them would share partial slot 1: with fewer groups than warps (a narrow layer)
   // only the first `groups` warps take work
-  const int gw = blockIdx.x * WPC + warp, nw = min((int)gridDim.x * WPC, groups);
+  const int gw = bid.x * WPC + warp, nw = min(gdx * WPC, groups);
   const int t0 = gw < nw ? (int)(T * gw / nw) : (int)T, t1 = gw < nw ? (int)(T * (gw + 1) / nw) : (int)T;
 
   const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -167,8 +187,7 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
 #pragma unroll
     for (int d = 0; d < kFwdRing - 1; ++d) issue(d);
   }
-  pdl_wait();
-  pdl_launch();
+  sync();
   if (!prefetch_early) {
 #pragma unroll
     for (int d = 0; d < kFwdRing - 1; ++d) issue(d);
@@ -194,7 +213,7 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
             const int b = bq * 4 + r;
             v[u][bq][r] = zero;
             if (k4 < kc4 && k4 * 4 < klen && b < nb)
-              v[u][bq][r] = __ldg(reinterpret_cast<const float4*>(X + (size_t)(b0 + b) * ldx + k0) + k4);
+              v[u][bq][r] = ld_dep<Sync>(reinterpret_cast<const float4*>(X + (size_t)(b0 + b) * ldx + k0) + k4);
           }
       }
 #pragma unroll
@@ -288,27 +307,39 @@ fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __re
   cp_async_wait<0>();
   SN_T(4);
 #ifdef SN_TIMING
-  if (lane == 0 && blockIdx.z == 0) {
-    long long* o = g_fwd_timing + ((blockIdx.y * gridDim.x + blockIdx.x) * WPC + warp) * 8;
+  if (lane == 0 && bid.z == 0) {
+    long long* o = g_fwd_timing + ((bid.y * gdx + bid.x) * WPC + warp) * 8;
     o[0] = tstamp[1] - tstamp[0]; o[1] = tstamp[2] - tstamp[1]; o[2] = tstamp[3] - tstamp[2];
     o[3] = tstamp[4] - tstamp[3]; o[4] = t_red; o[5] = t1 - t0; o[6] = tstamp[0]; o[7] = tstamp[4];
   }
 #endif
 }
 
+template <int R>
+__global__ void __launch_bounds__(32 * (64 / R), 1)
+fwd_skinny_kernel(const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N,
+                  int K, int kc, float* __restrict__ P, int Bpad, int ksplit, int prefetch_early, int l2_keep_w) {
+  extern __shared__ float4 smem4[];
+  fwd_skinny_body<R>(smem4, blockIdx, (int)gridDim.x, PdlSync{}, X, ldx, B, W, ldw, N, K, kc, P, Bpad, ksplit, prefetch_early,
+                     l2_keep_w);
+}
+
 // H[b][n] = act(sum_ks P[ks][b][n] + bias[n]) * dropout.   One thread per element.
 // mask (nullable) is [B][N] keep-bytes with row stride N; otherwise, when keep_prob < 1, Philox.
-__global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int Bpad, int B, int N,
-                                    const float* __restrict__ bias, int relu, const uint8_t* __restrict__ mask,
-                                    float keep_prob, float scale, uint64_t seed, uint64_t offset, int layer,
-                                    float* __restrict__ H, int ldh, float* __restrict__ out2, int idx_ld, int idx_off) {
+template <class Sync>
+__device__ __forceinline__ void
+fwd_epilogue_body(const unsigned bx, const unsigned gdx, Sync sync, const float* __restrict__ P, int ksplit, int Bpad, int B,
+                  int N, const float* __restrict__ bias, int relu, const uint8_t* __restrict__ mask, float keep_prob,
+                  float scale, uint64_t seed, uint64_t offset, int layer, float* __restrict__ H, int ldh,
+                  float* __restrict__ out2, int idx_ld, int idx_off) {
   // idx_ld > 0: this launch computes rows [idx_off, idx_off+N) of a layer that is idx_ld rows wide
   // (a tensor-parallel shard): the dropout decision of an element must not depend on the sharding,
   // so the mask / Philox index is the element's index in the FULL [B, idx_ld] activation.
-  pdl_wait();
-  pdl_launch();
+  sync();
   const size_t total = (size_t)B * N;
-  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+  const size_t stride = (size_t)gdx * blockDim.x;
+  size_t idx = bx * (size_t)blockDim.x + threadIdx.x;
+  for (; idx < total; idx += stride) {
     const int b = (int)(idx / N), n = (int)(idx - (size_t)b * N);
     const size_t gidx = idx_ld > 0 ? (size_t)b * idx_ld + idx_off + n : idx;
     const float bn = bias[n];                    // requested before the partials, not after them
@@ -322,14 +353,14 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
       for (; ks + 16 <= ksplit; ks += 16) {
         float t[16];
 #pragma unroll
-        for (int q = 0; q < 16; ++q) t[q] = pp[(size_t)(ks + q) * pstride];
+        for (int q = 0; q < 16; ++q) t[q] = ld_dep<Sync>(pp + (size_t)(ks + q) * pstride);
 #pragma unroll
         for (int q = 0; q < 16; ++q) s += t[q];
       }
       if (ks < ksplit) {
         float t[16];
 #pragma unroll
-        for (int q = 0; q < 16; ++q) t[q] = ks + q < ksplit ? pp[(size_t)(ks + q) * pstride] : 0.f;
+        for (int q = 0; q < 16; ++q) t[q] = ks + q < ksplit ? ld_dep<Sync>(pp + (size_t)(ks + q) * pstride) : 0.f;
 #pragma unroll
         for (int q = 0; q < 16; ++q)
           if (ks + q < ksplit) s += t[q];
@@ -337,11 +368,11 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
       }
     }
     for (; ks + 4 <= ksplit; ks += 4) {          // four independent loads in flight, fixed add order
-      const float p0 = pp[(size_t)ks * pstride], p1 = pp[(size_t)(ks + 1) * pstride];
-      const float p2 = pp[(size_t)(ks + 2) * pstride], p3 = pp[(size_t)(ks + 3) * pstride];
+      const float p0 = ld_dep<Sync>(pp + (size_t)ks * pstride), p1 = ld_dep<Sync>(pp + (size_t)(ks + 1) * pstride);
+      const float p2 = ld_dep<Sync>(pp + (size_t)(ks + 2) * pstride), p3 = ld_dep<Sync>(pp + (size_t)(ks + 3) * pstride);
       s += p0; s += p1; s += p2; s += p3;
     }
-    for (; ks < ksplit; ++ks) s += pp[(size_t)ks * pstride];
+    for (; ks < ksplit; ++ks) s += ld_dep<Sync>(pp + (size_t)ks * pstride);
     s += bn;
     if (relu) s = fmaxf(s, 0.f);
     if (mask) {
@@ -352,6 +383,14 @@ __global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int
     H[(size_t)b * ldh + n] = s;
     if (out2) out2[idx] = s;
   }
+}
+
+__global__ void fwd_epilogue_kernel(const float* __restrict__ P, int ksplit, int Bpad, int B, int N,
+                                    const float* __restrict__ bias, int relu, const uint8_t* __restrict__ mask,
+                                    float keep_prob, float scale, uint64_t seed, uint64_t offset, int layer,
+                                    float* __restrict__ H, int ldh, float* __restrict__ out2, int idx_ld, int idx_off) {
+  fwd_epilogue_body(blockIdx.x, gridDim.x, PdlSync{}, P, ksplit, Bpad, B, N, bias, relu, mask, keep_prob, scale, seed, offset,
+                    layer, H, ldh, out2, idx_ld, idx_off);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -412,6 +451,51 @@ __device__ __forceinline__ float ce_row_reg(const float (&zc)[NC], int64_t lab, 
         dzr[c] = p * invB;
       }
     }
+  }
+  return loss;
+}
+
+// The same with the gradient returned in registers (dzv[i] for class gl + GW*i) instead of stored.
+template <int NC, int GW = 32>
+__device__ __forceinline__ float ce_row_reg_vals(const float (&zc)[NC], int64_t lab, int C, float invB, float (&dzv)[NC],
+                                                 int gl) {
+  float m = -INFINITY;
+  int arg = 0x7fffffff;
+#pragma unroll
+  for (int i = 0; i < NC; ++i) {
+    const int c = gl + GW * i;
+    if (c < C && zc[i] > m) { m = zc[i]; arg = c; }
+  }
+#pragma unroll
+  for (int o = GW / 2; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, m, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
+  }
+  float s1 = 0.f, zl = 0.f, ex[NC];
+#pragma unroll
+  for (int i = 0; i < NC; ++i) {
+    const int c = gl + GW * i;
+    ex[i] = 1.f;
+    if (c < C) {
+      if (c != arg) { ex[i] = expf(zc[i] - m); s1 += ex[i]; }
+      if (c == lab) zl = zc[i];
+    }
+  }
+#pragma unroll
+  for (int o = GW / 2; o > 0; o >>= 1) {
+    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    zl += __shfl_xor_sync(0xffffffffu, zl, o);
+  }
+  const bool ok = lab >= 0 && lab < C;
+  const float loss = ok ? (log1pf(s1) - (zl - m)) : NAN;
+  const float invs = 1.f / (1.f + s1);
+#pragma unroll
+  for (int i = 0; i < NC; ++i) {
+    const int c = gl + GW * i;
+    float p = ex[i] * invs;
+    if (c == lab) p -= 1.f;
+    dzv[i] = c < C ? p * invB : 0.f;
   }
   return loss;
 }
@@ -494,17 +578,19 @@ struct CeTail {
 // computes the cross-entropy of all rows and the logit gradient in the same launch.
 constexpr int kHeadRows = 2;
 
-__global__ void __launch_bounds__(256)
-fwd_small_kernel(const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N, int K,
-                 const float* __restrict__ bias, int relu, const uint8_t* __restrict__ mask, float keep_prob,
-                 float scale, uint64_t seed, uint64_t offset, int layer, float* __restrict__ H, int ldh,
-                 float* __restrict__ out2, int prefetch_early, CeTail ce) {
+template <class Sync>
+__device__ __forceinline__ void
+fwd_small_body(const dim3 bid, const unsigned ncta, Sync sync,
+               const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N, int K,
+               const float* __restrict__ bias, int relu, const uint8_t* __restrict__ mask, float keep_prob,
+               float scale, uint64_t seed, uint64_t offset, int layer, float* __restrict__ H, int ldh,
+               float* __restrict__ out2, int prefetch_early, CeTail ce) {
   __shared__ float part[8][kHeadRows * kBT];
   __shared__ float rl[256];                          // row losses of the tail (rows beyond 256: global scratch)
   __shared__ unsigned is_last;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int n0 = blockIdx.x * kHeadRows;
-  const int b0 = blockIdx.y * kBT, nb = min(kBT, B - b0);
+  const int n0 = bid.x * kHeadRows;
+  const int b0 = bid.y * kBT, nb = min(kBT, B - b0);
   const int K4 = (K + 3) >> 2;
   const bool wvec = (K & 3) == 0 && (ldw & 3) == 0 && (reinterpret_cast<uintptr_t>(W) & 15) == 0;
   const bool xvec = (K & 3) == 0 && (ldx & 3) == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0;
@@ -522,6 +608,16 @@ fwd_small_kernel(const float* __restrict__ X, int ldx, int B, const float* __res
     v.w = k + 3 < K ? __ldg(row + k + 3) : 0.f;
     return v;
   };
+  auto load4x = [&](const float* row, int k4, bool vec) {        // X may come from an earlier phase
+    if (vec) return ld_dep<Sync>(reinterpret_cast<const float4*>(row) + k4);
+    const int k = k4 * 4;
+    float4 v;
+    v.x = k < K ? ld_dep<Sync>(row + k) : 0.f;
+    v.y = k + 1 < K ? ld_dep<Sync>(row + k + 1) : 0.f;
+    v.z = k + 2 < K ? ld_dep<Sync>(row + k + 2) : 0.f;
+    v.w = k + 3 < K ? ld_dep<Sync>(row + k + 3) : 0.f;
+    return v;
+  };
   auto load_w = [&](int k4, float4* w) {
 #pragma unroll
     for (int r = 0; r < kHeadRows; ++r)
@@ -531,11 +627,11 @@ fwd_small_kernel(const float* __restrict__ X, int ldx, int B, const float* __res
   // when the host says the previous kernel cannot be writing W or the bias (prefetch_early), the
   // first pass's W values are fetched before the PDL wait; otherwise right after it
   float4 w[kHeadRows];
-  if (!prefetch_early) { pdl_wait(); pdl_launch(); }
+  if (!prefetch_early) sync();
   load_w(warp * 32 + lane, w);
   float bv = 0.f;
   if (tid < kHeadRows * kBT && n0 + (tid >> 4) < N) bv = __ldg(bias + n0 + (tid >> 4));
-  if (prefetch_early) { pdl_wait(); pdl_launch(); }
+  if (prefetch_early) sync();
   SN_TP(1);
 
   float acc[kHeadRows * kBT];
@@ -546,7 +642,7 @@ fwd_small_kernel(const float* __restrict__ X, int ldx, int B, const float* __res
     if (kb > 0) load_w(k4, w);
     float4 x[kBT];
 #pragma unroll
-    for (int b = 0; b < kBT; ++b) x[b] = (k4 < K4 && b < nb) ? load4(X + (size_t)(b0 + b) * ldx, k4, xvec) : zero4;
+    for (int b = 0; b < kBT; ++b) x[b] = (k4 < K4 && b < nb) ? load4x(X + (size_t)(b0 + b) * ldx, k4, xvec) : zero4;
 #pragma unroll
     for (int r = 0; r < kHeadRows; ++r)
 #pragma unroll
@@ -592,7 +688,7 @@ fwd_small_kernel(const float* __restrict__ X, int ldx, int B, const float* __res
   __threadfence();
   __syncthreads();
   SN_TP(4);
-  if (tid == 0) is_last = (atomicAdd(ce.ticket, 1u) == gridDim.x * gridDim.y - 1);
+  if (tid == 0) is_last = (atomicAdd(ce.ticket, 1u) == ncta - 1);
   __syncthreads();
   SN_TP(5);
   if (!is_last) return;
@@ -639,6 +735,15 @@ fwd_small_kernel(const float* __restrict__ X, int ldx, int B, const float* __res
       *ce.ticket = 0u;
     }
   }
+}
+
+__global__ void __launch_bounds__(256)
+fwd_small_kernel(const float* __restrict__ X, int ldx, int B, const float* __restrict__ W, int ldw, int N, int K,
+                 const float* __restrict__ bias, int relu, const uint8_t* __restrict__ mask, float keep_prob,
+                 float scale, uint64_t seed, uint64_t offset, int layer, float* __restrict__ H, int ldh,
+                 float* __restrict__ out2, int prefetch_early, CeTail ce) {
+  fwd_small_body(blockIdx, gridDim.x * gridDim.y, PdlSync{}, X, ldx, B, W, ldw, N, K, bias, relu, mask, keep_prob, scale, seed,
+                 offset, layer, H, ldh, out2, prefetch_early, ce);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -829,29 +934,35 @@ constexpr int kRing = SN_KRING;   // rows in flight per thread (W + optimizer st
 // across the warp's 128-wide k slice, and the per-slice partials PF[slice][b][n] are summed by
 // fwd_epilogue_kernel at the start of the next step.  W is then read once per step instead of
 // twice (28*P -> 24*P bytes with Adam).
-template <int OPT, bool NEED_DA, bool FUSE_FWD = false>
-__global__ void __launch_bounds__(256, 1)
-bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict__ bias, float* __restrict__ s1,
-                  float* __restrict__ s2, float* __restrict__ bs1, float* __restrict__ bs2,
-                  const float* __restrict__ dZ, int ldz, const float* __restrict__ A, int lda, int B,
-                  float* __restrict__ PA, int kw, int rows_per_cta, OptParams op,
-                  const float* __restrict__ Xn, int Bn, float* __restrict__ PF, int l2_keep_w,
-                  const float* __restrict__ gate, float gscale) {
+template <int OPT, bool NEED_DA, bool FUSE_FWD, bool PFS, class Sync>
+__device__ __forceinline__ void
+bwd_update_body(float4* smem4, const dim3 bid, Sync sync,
+                float* __restrict__ W, int ldw, int N, int K, float* __restrict__ bias, float* __restrict__ s1,
+                float* __restrict__ s2, float* __restrict__ bs1, float* __restrict__ bs2,
+                const float* __restrict__ dZ, int ldz, const float* __restrict__ A, int lda, int B,
+                float* __restrict__ PA, int kw, int rows_per_cta, OptParams op,
+                const float* __restrict__ Xn, int Bn, float* __restrict__ PF, int l2_keep_w,
+                const float* __restrict__ gate, float gscale) {
+  constexpr bool pf_smem = PFS;
   // gate != nullptr (tensor-parallel shard): dZ arrives UNGATED (it is the head GPU's cut gradient
   // w.r.t. this layer's output); the ReLU/dropout gate is this shard's own dense activation
   // gate[b][N]: dZ <- dZ * (gate > 0 ? gscale : 0), applied while the tile is staged.
-  extern __shared__ float4 smem4[];
   // rows below l2_keep_w: weights tagged evict_last, their optimizer state evict_first
   const uint64_t pol_keep = l2_policy(1), pol_norm = l2_policy(0), pol_s = l2_policy(l2_keep_w ? 2 : 0);
   float* dzs = reinterpret_cast<float*>(smem4);                  // [rows_per_cta][16]
   // per-thread ring of the next kRing rows' float4s: [array][slot][thread]; a thread only ever
   // reads what it copied itself, so cp.async.wait_group is the only synchronisation needed
   float4* ring = smem4 + ((rows_per_cta * kBT + 3) >> 2);
+  // FUSE_FWD with pf_smem: the next-forward partials of this CTA's rows are collected in shared memory
+  // ([k slice of the CTA][row][16 batch values, padded to 17]) and written out once at the end, summed
+  // over the CTA's kw slices: kgroups partials per output instead of one per 128-wide k slice, and
+  // coalesced stores instead of sixteen scattered 4-byte stores per row and warp
+  float* pfs = reinterpret_cast<float*>(ring + (OPT == 2 ? 3 : 2) * kRing * 256);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int wk = warp % kw, wr = warp / kw, rw = 8 / kw;
-  const int nb0 = blockIdx.y * rows_per_cta, nb1 = min(N, nb0 + rows_per_cta);
+  const int nb0 = bid.y * rows_per_cta, nb1 = min(N, nb0 + rows_per_cta);
   const int nrows = nb1 - nb0;
-  const int k0 = (blockIdx.x * kw + wk) * 128 + lane * 4;
+  const int k0 = (bid.x * kw + wk) * 128 + lane * 4;
   const bool kok = k0 < K;
 
   auto issue = [&](int slot, int row) {
@@ -868,8 +979,8 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
 #pragma unroll
     for (int d = 0; d < kRing - 1; ++d) issue(d, n + d * rw);    // start streaming before anything else
   }
-  pdl_wait();        // W / optimizer state are never written by the kernel just before this one;
-  pdl_launch();      // dZ (and A) are, so everything below waits for it
+  sync();            // W / optimizer state are never written by the kernel (phase) just before this one;
+                     // dZ (and A) are, so everything below waits for it
   if (OPT == 3) {    // ... except the gradient buffer of an accumulation launch (the previous tile's launch wrote it)
 #pragma unroll
     for (int d = 0; d < kRing - 1; ++d) issue(d, n + d * rw);
@@ -884,8 +995,8 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
       for (int q = 0; q < SB; ++q) {
         const int idx = base_idx + q * 256;
         const int b = idx / nrows, j = idx - b * nrows;
-        v[q] = (idx < total && b < B) ? __ldg(dZ + (size_t)b * ldz + nb0 + j) : 0.f;
-        if (gate && idx < total && b < B) v[q] = __ldg(gate + (size_t)b * N + nb0 + j) > 0.f ? v[q] * gscale : 0.f;
+        v[q] = (idx < total && b < B) ? ld_dep<Sync>(dZ + (size_t)b * ldz + nb0 + j) : 0.f;
+        if (gate && idx < total && b < B) v[q] = ld_dep<Sync>(gate + (size_t)b * N + nb0 + j) > 0.f ? v[q] * gscale : 0.f;
       }
 #pragma unroll
       for (int q = 0; q < SB; ++q) {
@@ -905,8 +1016,8 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
 #pragma unroll
     for (int p = 0; p < kBP; ++p) {
       const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-      const float4 e = (kok && 2 * p < rows) ? __ldg(reinterpret_cast<const float4*>(base + (size_t)(2 * p) * ld + k0)) : zero;
-      const float4 o = (kok && 2 * p + 1 < rows) ? __ldg(reinterpret_cast<const float4*>(base + (size_t)(2 * p + 1) * ld + k0)) : zero;
+      const float4 e = (kok && 2 * p < rows) ? ld_dep<Sync>(reinterpret_cast<const float4*>(base + (size_t)(2 * p) * ld + k0)) : zero;
+      const float4 o = (kok && 2 * p + 1 < rows) ? ld_dep<Sync>(reinterpret_cast<const float4*>(base + (size_t)(2 * p + 1) * ld + k0)) : zero;
       dst[p][0] = make_float2(e.x, o.x);
       dst[p][1] = make_float2(e.y, o.y);
       dst[p][2] = make_float2(e.z, o.z);
@@ -924,7 +1035,7 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
   }
   float2 xn2[kBP][4];                               // dead (and removed) unless FUSE_FWD
   if (FUSE_FWD) load_pairs(Xn, lda, Bn, xn2);
-  const int kslice = blockIdx.x * kw + wk;
+  const int kslice = bid.x * kw + wk;
   const bool slice_ok = kslice * 128 < K;
   __syncthreads();
 
@@ -993,16 +1104,32 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
         y[2 * p] = t.x;
         y[2 * p + 1] = t.y;
       }
+      // (Sharing one 32-value butterfly between two consecutive rows - same five shuffle stages, twice
+      // the independent work per stage - was built and measured SLOWER: 122.8 -> 134 us for this
+      // traversal, 228 registers instead of 185.)
       butterfly_reduce<kBT>(y, lane);               // lanes 2b, 2b+1 hold batch row b
-      if (slice_ok && !(lane & 1)) PF[((size_t)kslice * kBT + (lane >> 1)) * N + n] = y[0];
+      if (pf_smem) {
+        if (!(lane & 1)) pfs[((size_t)wk * rows_per_cta + (n - nb0)) * (kBT + 1) + (lane >> 1)] = slice_ok ? y[0] : 0.f;
+      } else if (slice_ok && !(lane & 1)) {
+        PF[((size_t)kslice * kBT + (lane >> 1)) * N + n] = y[0];
+      }
     }
   }
   cp_async_wait<0>();
+  if (FUSE_FWD && pf_smem) {
+    __syncthreads();
+    for (int idx = tid; idx < nrows * kBT; idx += 256) {
+      const int b = idx / nrows, j = idx - b * nrows;
+      float t = pfs[(size_t)j * (kBT + 1) + b];
+      for (int q = 1; q < kw; ++q) t += pfs[((size_t)q * rows_per_cta + j) * (kBT + 1) + b];   // fixed order
+      PF[((size_t)bid.x * kBT + b) * N + nb0 + j] = t;
+    }
+  }
 
   // bias: db[n] = sum_b dZ[b][n].  One thread per row AFTER the streaming loop (a per-row
   // load->update->store chain inside the loop made the k-group-0 CTAs latency-bound and the
   // whole grid wait for them).
-  if (OPT != 3 && blockIdx.x == 0) {
+  if (OPT != 3 && bid.x == 0) {
     for (int j = tid; j < nrows; j += 256) {
       float db = 0.f;
 #pragma unroll
@@ -1034,10 +1161,23 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
         const float4 u = red[((r * kw + s) * kBT + b) * 32 + l];
         t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
       }
-      const int k = (blockIdx.x * kw + s) * 128 + l * 4;
-      if (k < K && b < B) *reinterpret_cast<float4*>(PA + ((size_t)blockIdx.y * kBT + b) * K + k) = t;
+      const int k = (bid.x * kw + s) * 128 + l * 4;
+      if (k < K && b < B) *reinterpret_cast<float4*>(PA + ((size_t)bid.y * kBT + b) * K + k) = t;
     }
   }
+}
+
+template <int OPT, bool NEED_DA, bool FUSE_FWD = false, bool PFS = false>
+__global__ void __launch_bounds__(256, 1)
+bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict__ bias, float* __restrict__ s1,
+                  float* __restrict__ s2, float* __restrict__ bs1, float* __restrict__ bs2,
+                  const float* __restrict__ dZ, int ldz, const float* __restrict__ A, int lda, int B,
+                  float* __restrict__ PA, int kw, int rows_per_cta, OptParams op,
+                  const float* __restrict__ Xn, int Bn, float* __restrict__ PF, int l2_keep_w,
+                  const float* __restrict__ gate, float gscale) {
+  extern __shared__ float4 smem4[];
+  bwd_update_body<OPT, NEED_DA, FUSE_FWD, PFS>(smem4, blockIdx, PdlSync{}, W, ldw, N, K, bias, s1, s2, bs1, bs2, dZ, ldz, A, lda, B,
+                                               PA, kw, rows_per_cta, op, Xn, Bn, PF, l2_keep_w, gate, gscale);
 }
 
 // Backward + optimizer for tiny layers (fc3 100x1000: 400 KB, L2-resident, pure latency).  The
@@ -1052,16 +1192,21 @@ bwd_update_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restric
 //   a hidden layer) and written to dst[b][k].
 constexpr int kSmallBwdRows = 16;   // rows per warp held in registers => N <= 128
 
-template <int OPT, bool NEED_DA>
-__global__ void __launch_bounds__(256)
-bwd_small_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict__ bias, float* __restrict__ s1,
-                 float* __restrict__ s2, float* __restrict__ bs1, float* __restrict__ bs2,
-                 const float* __restrict__ dZ, int ldz, const float* __restrict__ A, int lda, int B, OptParams op,
-                 int gate, float gscale, float* __restrict__ dst, int ldd) {
+// `ce` (tail kernel only, labels != nullptr): dZ is not read - the CTA first computes the cross-entropy
+// of the logits ce.dz-shaped [rows][C] held in `logits` itself (every CTA does, redundantly: 16 rows of
+// 100 classes cost less than a grid barrier) and block 0 also stores the loss and the logit gradient.
+template <int OPT, bool NEED_DA, class Sync>
+__device__ __forceinline__ void
+bwd_small_body(const unsigned bx, Sync sync,
+               float* __restrict__ W, int ldw, int N, int K, float* __restrict__ bias, float* __restrict__ s1,
+               float* __restrict__ s2, float* __restrict__ bs1, float* __restrict__ bs2,
+               const float* __restrict__ dZ, int ldz, const float* __restrict__ A, int lda, int B, OptParams op,
+               int gate, float gscale, float* __restrict__ dst, int ldd, const float* __restrict__ logits = nullptr,
+               CeTail ce = CeTail{}) {
   __shared__ float dzs[128 * kBT];                 // [row][16]
   __shared__ float red[8][kBT][32];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int k = blockIdx.x * 32 + lane;
+  const int k = bx * 32 + lane;
   const bool kok = k < K;
   float w[kSmallBwdRows], m1[kSmallBwdRows], m2[OPT == 2 ? kSmallBwdRows : 1];
 #pragma unroll
@@ -1073,15 +1218,53 @@ bwd_small_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict
     m1[i] = ok ? s1[o] : 0.f;
     if (OPT == 2) m2[i] = ok ? s2[o] : 0.f;
   }
-  pdl_wait();        // W / optimizer state are never written by the kernel just before this one;
-  pdl_launch();      // dZ (and A) are
-  for (int idx = tid; idx < N * kBT; idx += 256) {
-    const int b = idx / N, j = idx - b * N;
-    dzs[j * kBT + b] = b < B ? __ldg(dZ + (size_t)b * ldz + j) : 0.f;
+  sync();            // W / optimizer state are never written by the kernel (phase) just before this one;
+                     // dZ (and A) are
+  if (ce.labels && logits) {
+    // cross-entropy in place: warp w takes rows 2w, 2w+1 (16 lanes each), the logit gradient lands in
+    // dzs[class][row]; rows beyond B stay zero
+    for (int idx = tid; idx < N * kBT; idx += 256) dzs[idx] = 0.f;
+    __syncthreads();
+    __shared__ float rl_s[kBT];
+    const int gl = lane & 15, r = warp * 2 + (lane >> 4);
+    const bool live = r < ce.rows;
+    float zc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = gl + 16 * i;
+      zc[i] = (live && c < ce.C) ? __ldcg(logits + (size_t)r * ce.C + c) : -INFINITY;
+    }
+    const int64_t lab = live ? ce.labels[r] : 0;
+    // ce_row_reg writes (softmax - onehot)/rows for class c to dzr[c]: aim it at column r of dzs
+    float dzr[8];
+    const float l = ce_row_reg_vals<8, 16>(zc, lab, live ? ce.C : 0, 1.f / (float)ce.rows, dzr, gl);
+    if (live) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int c = gl + 16 * i;
+        if (c < ce.C) {
+          dzs[c * kBT + r] = dzr[i];
+          if (bx == 0 && ce.dz) ce.dz[(size_t)r * ce.C + c] = dzr[i];
+        }
+      }
+      if (gl == 0) rl_s[r] = l;
+    }
+    __syncthreads();
+    if (bx == 0 && warp == 0) {
+      float sl = 0.f;
+      for (int q = lane; q < ce.rows; q += 32) sl += rl_s[q];
+      sl = warp_sum(sl);
+      if (lane == 0 && ce.loss) *ce.loss = sl / (float)ce.rows;
+    }
+  } else {
+    for (int idx = tid; idx < N * kBT; idx += 256) {
+      const int b = idx / N, j = idx - b * N;
+      dzs[j * kBT + b] = b < B ? ld_dep<Sync>(dZ + (size_t)b * ldz + j) : 0.f;
+    }
   }
   float a[kBT];
 #pragma unroll
-  for (int b = 0; b < kBT; ++b) a[b] = (kok && b < B) ? __ldg(A + (size_t)b * lda + k) : 0.f;
+  for (int b = 0; b < kBT; ++b) a[b] = (kok && b < B) ? ld_dep<Sync>(A + (size_t)b * lda + k) : 0.f;
   float acc[NEED_DA ? kBT : 1];
   if (NEED_DA) {
 #pragma unroll
@@ -1115,7 +1298,7 @@ bwd_small_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict
       }
     }
   }
-  if (blockIdx.x == 0) {                            // bias: db[n] = sum_b dZ[b][n]
+  if (bx == 0) {                                    // bias: db[n] = sum_b dZ[b][n]
     for (int j = tid; j < N; j += 256) {
       float db = 0.f;
 #pragma unroll
@@ -1136,42 +1319,61 @@ bwd_small_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict
       float t = 0.f;
 #pragma unroll
       for (int r = 0; r < 8; ++r) t += red[r][b][l];
-      const int kk = blockIdx.x * 32 + l;
+      const int kk = bx * 32 + l;
       if (kk < K && b < B) {
-        if (gate) t = __ldg(A + (size_t)b * lda + kk) > 0.f ? t * gscale : 0.f;
+        if (gate) t = ld_dep<Sync>(A + (size_t)b * lda + kk) > 0.f ? t * gscale : 0.f;
         dst[(size_t)b * ldd + kk] = t;
       }
     }
   }
 }
 
+template <int OPT, bool NEED_DA>
+__global__ void __launch_bounds__(256)
+bwd_small_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict__ bias, float* __restrict__ s1,
+                 float* __restrict__ s2, float* __restrict__ bs1, float* __restrict__ bs2,
+                 const float* __restrict__ dZ, int ldz, const float* __restrict__ A, int lda, int B, OptParams op,
+                 int gate, float gscale, float* __restrict__ dst, int ldd) {
+  bwd_small_body<OPT, NEED_DA>(blockIdx.x, PdlSync{}, W, ldw, N, K, bias, s1, s2, bs1, bs2, dZ, ldz, A, lda, B, op, gate, gscale,
+                               dst, ldd);
+}
+
 // dst[b][k] = (sum_s PA[s][b][k]) * gate, gate = (H[b][k] > 0 ? scale : 0) for hidden layers
 // (H is the post-ReLU, post-dropout activation so H>0 <=> ReLU active and kept), 1 at the cut.
 // dst_table != nullptr (tensor-parallel head): column k goes to dst_table[k / cols_per_dst] instead of
 // dst - each consumer GPU gets its column range pushed into its own memory over NVLink.
-__global__ void bwd_epilogue_kernel(const float* __restrict__ PA, int nsplit, int B, int K,
-                                    const float* __restrict__ H, int ldh, float scale, float* __restrict__ dst,
-                                    int ldd, float* const* __restrict__ dst_table, int cols_per_dst) {
-  pdl_wait();
-  pdl_launch();
+template <class Sync>
+__device__ __forceinline__ void
+bwd_epilogue_body(const unsigned bx, const unsigned gdx, Sync sync, const float* __restrict__ PA, int nsplit, int B, int K,
+                  const float* __restrict__ H, int ldh, float scale, float* __restrict__ dst, int ldd,
+                  float* const* __restrict__ dst_table, int cols_per_dst) {
+  sync();
   const size_t total = (size_t)B * K;
-  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+  const size_t stride = (size_t)gdx * blockDim.x;
+  size_t idx = bx * (size_t)blockDim.x + threadIdx.x;
+  for (; idx < total; idx += stride) {
     const int b = (int)(idx / K), k = (int)(idx - (size_t)b * K);
-    const float hv = H ? H[(size_t)b * ldh + k] : 1.f;   // requested before the partials
+    const float hv = H ? ld_dep<Sync>(H + (size_t)b * ldh + k) : 1.f;   // requested before the partials
     float s = 0.f;
     const float* pp = PA + (size_t)b * K + k;
     const size_t pstride = (size_t)kBT * K;
     int p = 0;
     for (; p + 4 <= nsplit; p += 4) {            // four independent loads in flight, fixed add order
-      const float p0 = pp[(size_t)p * pstride], p1 = pp[(size_t)(p + 1) * pstride];
-      const float p2 = pp[(size_t)(p + 2) * pstride], p3 = pp[(size_t)(p + 3) * pstride];
+      const float p0 = ld_dep<Sync>(pp + (size_t)p * pstride), p1 = ld_dep<Sync>(pp + (size_t)(p + 1) * pstride);
+      const float p2 = ld_dep<Sync>(pp + (size_t)(p + 2) * pstride), p3 = ld_dep<Sync>(pp + (size_t)(p + 3) * pstride);
       s += p0; s += p1; s += p2; s += p3;
     }
-    for (; p < nsplit; ++p) s += pp[(size_t)p * pstride];
+    for (; p < nsplit; ++p) s += ld_dep<Sync>(pp + (size_t)p * pstride);
     if (H) s = hv > 0.f ? s * scale : 0.f;
     float* d = dst_table ? dst_table[k / cols_per_dst] : dst;
     d[(size_t)b * ldd + k] = s;
   }
+}
+
+__global__ void bwd_epilogue_kernel(const float* __restrict__ PA, int nsplit, int B, int K,
+                                    const float* __restrict__ H, int ldh, float scale, float* __restrict__ dst,
+                                    int ldd, float* const* __restrict__ dst_table, int cols_per_dst) {
+  bwd_epilogue_body(blockIdx.x, gridDim.x, PdlSync{}, PA, nsplit, B, K, H, ldh, scale, dst, ldd, dst_table, cols_per_dst);
 }
 
 // dst = src * (out > 0)  (ReLU on the last layer, U-shape model2)

@@ -14,6 +14,7 @@
 #include "common.cuh"
 #include "gemm_tc.cuh"
 #include "mlp_kernels.cuh"
+#include "tail_kernel.cuh"
 
 namespace sn {
 thread_local std::string g_last_error;
@@ -101,6 +102,10 @@ static BwdPlan plan_bwd(int N, int K, int sms, bool need_da, bool adam) {
   }
   return best;
 }
+
+constexpr size_t kMaxSmemPerCta = 232448;    // 227 KB
+// shared-memory collection of the fused next-forward partials (bwd_update_kernel, pf_smem): fits?
+static size_t bwd_pf_smem_bytes(const BwdPlan& p) { return (size_t)p.kw * p.rows_per_cta * (kBT + 1) * 4; }
 
 static size_t bwd_smem_bytes(const BwdPlan& p, bool need_da, bool adam) {
   // dZ tile + max(per-thread cp.async ring, dA cross-warp reduction buffer) which alias
@@ -257,6 +262,15 @@ static bool sk_enabled() {
   }
   return v == 1 && g_matmul_precision.load() != 2;
 }
+std::atomic<int> g_persistent_tail{-1};             // -1: not set yet (SN_TAIL=1 in the environment turns it on)
+static bool tail_enabled() {
+  int v = g_persistent_tail.load();
+  if (v < 0) {
+    v = (getenv("SN_TAIL") && atoi(getenv("SN_TAIL")) != 0) ? 1 : 0;
+    g_persistent_tail.store(v);
+  }
+  return v == 1;
+}
 static SkPlan plan_sk(int K, int N, int sms) {
   const long long KB = ceil_div(K, tc::BK), RT = ceil_div(N, tc::BM), U = KB * RT;
   long long G = std::min<long long>(sms, U);
@@ -388,6 +402,10 @@ struct sn_bob {
   Profiler prof;
   float* PF = nullptr;         // fused next-forward partials of layer 0 [k slices][16][dims[1]] (lazy)
   bool pf_valid = false;       // PF holds layer 0's pre-activation partials for the coming step
+  int pf_parts = 0;            // how many partials per output PF holds (k groups, or 128-wide k slices)
+  float* Ptail = nullptr;      // tail kernel: the second layer's split-K partials (lazy)
+  unsigned* tail_bar = nullptr;   // tail kernel: grid-barrier arrival counter (never reset)
+  unsigned tail_arrivals = 0;     // arrivals all earlier launches have added to it
   std::vector<int> l2_keep;    // per layer: tag the weight lines evict_last in L2 (see l2_policy)
 };
 
@@ -418,6 +436,7 @@ struct sn_shard {
   float* PF = nullptr;       // fused next-forward partials [k slices][16][n_rows]
   float* Hloc = nullptr;     // dense copy of the slice's activation [16][n_rows] (the backward's gate)
   bool pf_valid = false, h_valid = false;
+  int pf_parts = 0;
   int l2_keep = 0;
 };
 
@@ -432,7 +451,14 @@ static int conv_stream_min() {
 static int launch_conv_fwd(const float* x, const float* w, const float* b, int B, float* act, size_t ld_act, int sms,
                            cudaStream_t st) {
   if (B >= conv_stream_min()) {
-    launch_k(conv_pool_stream_kernel, dim3(std::min(B, sms * 2)), dim3(kStreamThreads), 0, st, x, w, b, B, act, ld_act);
+    // resident CTAs per SM: 3 (54 registers) by default; SN_CONV_CTAS=2|4 for A/B timing
+    static const int ctas = getenv("SN_CONV_CTAS") ? atoi(getenv("SN_CONV_CTAS")) : 3;
+    if (ctas == 2)
+      launch_k(conv_pool_stream_kernel<2>, dim3(std::min(B, sms * 2)), dim3(kStreamThreads), 0, st, x, w, b, B, act, ld_act);
+    else if (ctas == 4)
+      launch_k(conv_pool_stream_kernel<4>, dim3(std::min(B, sms * 4)), dim3(kStreamThreads), 0, st, x, w, b, B, act, ld_act);
+    else
+      launch_k(conv_pool_stream_kernel<3>, dim3(std::min(B, sms * 3)), dim3(kStreamThreads), 0, st, x, w, b, B, act, ld_act);
   } else {
     launch_k(conv_pool_fwd_kernel, dim3(std::min(B, sms * 4), 4), dim3(256), 0, st, x, w, b, B, act, ld_act);
   }
@@ -454,6 +480,11 @@ int sn_set_skinny_tensor_forward(int on) {
   return 0;
 }
 int sn_get_skinny_tensor_forward(void) { return sk_enabled() ? 1 : 0; }
+int sn_set_persistent_tail(int on) {
+  g_persistent_tail.store(on ? 1 : 0);
+  return 0;
+}
+int sn_get_persistent_tail(void) { return tail_enabled() ? 1 : 0; }
 const char* sn_last_error(void) { return g_last_error.c_str(); }
 uint64_t sn_launch_count(void) { return g_launches.load(); }
 
@@ -463,6 +494,14 @@ int sn_conv_pool_forward(const float* x, const float* w, const float* b, int B, 
   int dev = 0;
   SN_CUDA(cudaGetDevice(&dev));
   return launch_conv_fwd(x, w, b, B, act, kD0, sm_count(dev), (cudaStream_t)stream);
+}
+
+int sn_conv_weights_copy(float* dst_w, float* dst_b, const float* src_w, const float* src_b, void* stream) {
+  SN_REQUIRE(dst_w && dst_b && src_w && src_b, "sn_conv_weights_copy: bad arguments");
+  launch_k(conv_weights_copy_kernel, dim3(1), dim3(128), 0, (cudaStream_t)stream, dst_w, dst_b, src_w, src_b);
+  SN_LAUNCH_CHECK();
+  mark_written(dst_w, 288 * 4);
+  return 0;
 }
 
 size_t sn_conv_pool_backward_scratch_bytes(int B) {
@@ -695,6 +734,8 @@ int sn_bob_destroy(sn_bob* h) {
   cudaFree(h->PA);
   cudaFree(h->dWbuf);
   cudaFree(h->PF);
+  cudaFree(h->Ptail);
+  cudaFree(h->tail_bar);
   cudaFree(h->row_loss);
   cudaFree(h->ticket);
   h->prof.clear();
@@ -830,7 +871,7 @@ static int bob_forward_impl(sn_bob* h, const float* act, int B, int train, const
     if (l == 0 && h->pf_valid) {
       // layer 0 of this step was already multiplied out by the previous step's fused traversal
       h->pf_valid = false;
-      launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, h->sms)), dim3(256), 0, st, h->PF, ceil_div(K, 128), kBT, B, N,
+      launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, h->sms)), dim3(256), 0, st, h->PF, h->pf_parts, kBT, B, N,
                h->b[l], relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N, last ? out : nullptr, 0, 0);
       SN_LAUNCH_CHECK();
     } else if (launch_linear_fwd(X, ldx, B, h->W[l], h->b[l], K, N, relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N,
@@ -845,14 +886,17 @@ static int bob_forward_impl(sn_bob* h, const float* act, int B, int train, const
 }
 
 }  // extern "C" (templates need C++ linkage)
+// l_top: the highest layer to process (the tail kernel has already done the layers above 0);
+// op_in: the step's optimizer scalars when the caller has already advanced the step counter.
 template <int OPT>
 static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float* cut_grad, cudaStream_t st,
-                             const float* next_act = nullptr, int next_B = 0) {
+                             const float* next_act = nullptr, int next_B = 0, int l_top = -1,
+                             const OptParams* op_in = nullptr) {
   auto& s = h->slots[slot];
-  s.step += 1;
-  const OptParams op = make_opt(h->hyper, s.step);
+  if (!op_in) s.step += 1;
+  const OptParams op = op_in ? *op_in : make_opt(h->hyper, s.step);
   const float scale = 1.f / (1.f - h->dropout_p);
-  for (int l = h->L - 1; l >= 0; --l) {
+  for (int l = (l_top >= 0 ? l_top : h->L - 1); l >= 0; --l) {
     const int K = h->dims[l], N = h->dims[l + 1];
     const float* A = l == 0 ? act : h->H[l];
     const float* dZ = h->dZ[l + 1];
@@ -893,11 +937,23 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
       } else if (l == 0 && next_act && next_B > 0 && next_B <= kBT && (size_t)N * K > kSmallLayerElems) {
         // SISA: fuse the next step's layer-0 forward into this traversal
         if (!h->PF) SN_CUDA(cudaMalloc(&h->PF, (size_t)ceil_div(K, 128) * kBT * N * 4));
-        if (set_smem(bwd_update_kernel<OPT, false, true>, smem)) return 1;
+        // the partials are collected in shared memory when they fit next to the ring (one partial per
+        // k GROUP then, not per 128-wide slice)
+        const int pf_smem = smem + bwd_pf_smem_bytes(p) <= kMaxSmemPerCta && !getenv("SN_NO_PF_SMEM") ? 1 : 0;
+        const size_t smem_f = smem + (pf_smem ? bwd_pf_smem_bytes(p) : 0);
+        h->pf_parts = pf_smem ? p.kgroups : ceil_div(K, 128);
         cudaEvent_t pe = h->prof.begin(st, 1, l);
-        launch_k(bwd_update_kernel<OPT, false, true>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, h->b[l],
-                 s.s1[2 * l], s.s2[2 * l], s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, h->PA, p.kw, p.rows_per_cta, op,
-                 next_act, next_B, h->PF, h->l2_keep[l], (const float*)nullptr, 1.f);
+        if (pf_smem) {
+          if (set_smem(bwd_update_kernel<OPT, false, true, true>, smem_f)) return 1;
+          launch_k(bwd_update_kernel<OPT, false, true, true>, dim3(grid), dim3(256), smem_f, st, h->W[l], K, N, K, h->b[l],
+                   s.s1[2 * l], s.s2[2 * l], s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, h->PA, p.kw, p.rows_per_cta, op,
+                   next_act, next_B, h->PF, h->l2_keep[l], (const float*)nullptr, 1.f);
+        } else {
+          if (set_smem(bwd_update_kernel<OPT, false, true, false>, smem_f)) return 1;
+          launch_k(bwd_update_kernel<OPT, false, true, false>, dim3(grid), dim3(256), smem_f, st, h->W[l], K, N, K, h->b[l],
+                   s.s1[2 * l], s.s2[2 * l], s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, h->PA, p.kw, p.rows_per_cta, op,
+                   next_act, next_B, h->PF, h->l2_keep[l], (const float*)nullptr, 1.f);
+        }
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
         mark_written(h->W[l], wbytes);
@@ -1010,6 +1066,94 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
   return 0;
 }
 
+// ---------------------------------------------------------------- persistent tail (tail_kernel.cuh)
+// Applies to the reference's server shape class: three layers, a big first layer, a second layer on
+// the weight-stream path and a small last layer with at most 128 classes, batch <= 16.
+static bool tail_applies(const sn_bob* h, int B, const float* act) {
+  if (!tail_enabled() || h->prof.on || h->L != 3 || B > kBT || h->relu_last || h->heads != 1 || fwd_rows() != 8) return false;
+  if (h->hyper.type != SN_OPT_SGD_MOMENTUM && h->hyper.type != SN_OPT_ADAM) return false;
+  const int d0 = h->dims[0], n1 = h->dims[1], n2 = h->dims[2], n3 = h->dims[3];
+  auto small = [](int K, int N) { return (size_t)N * K <= kSmallLayerElems && K <= kSmallLayerMaxK; };
+  if (small(d0, n1) || (d0 % 4) != 0) return false;                            // layer 0 must leave split-K partials
+  if (small(n1, n2) || (n1 % 4) != 0 || sk_applies(B, n1, n2, act, n1, h->W[1])) return false;
+  if (!small(n2, n3) || n3 > 8 * kSmallBwdRows || n3 > 128) return false;
+  const FwdPlan f1 = plan_fwd(n1, n2, h->sms);
+  const BwdPlan b1 = plan_bwd(n2, n1, h->sms, true, h->hyper.type == SN_OPT_ADAM);
+  return f1.nx * f1.ksplit <= h->sms && b1.kgroups * b1.nsplit <= h->sms && ceil_div(n3, kHeadRows) <= h->sms &&
+         ceil_div(n2, 32) <= h->sms;
+}
+
+template <int OPT>
+static int bob_train_step_tail(sn_bob* h, int slot, const float* act, const int64_t* labels, int B,
+                               const uint8_t* const* drop_masks, uint64_t seed, uint64_t offset, float* cut_grad,
+                               float* logits_out, float* loss_out, cudaStream_t st, const float* next_act, int next_B) {
+  const int d0 = h->dims[0], n1 = h->dims[1], n2 = h->dims[2], n3 = h->dims[3];
+  const bool drop = h->dropout_p > 0.f;
+  TailParams tp{};
+  tp.B = B;
+  tp.keep = (drop && !drop_masks) ? 1.f - h->dropout_p : 1.f;
+  tp.scale = 1.f / (1.f - h->dropout_p);
+  tp.seed = seed;
+  tp.offset = offset;
+  // ---- first layer: leave its split-K partials for the tail's first phase
+  if (h->pf_valid) {                     // multiplied out by the previous step's fused traversal
+    h->pf_valid = false;
+    tp.P0 = h->PF; tp.parts0 = h->pf_parts; tp.bpad0 = kBT;
+  } else if (sk_applies(B, d0, n1, act, d0, h->W[0])) {
+    const SkPlan p = plan_sk(d0, n1, h->sms);
+    CUtensorMap mw, mx;
+    if (tc::make_map(&mw, h->W[0], n1, d0, d0, tc::BM) || tc::make_map(&mx, act, B, d0, d0, tc::kSkNB)) return 1;
+    if (set_smem(tc::skinny_fwd_x3_kernel, tc::sk_smem_bytes())) return 1;
+    launch_k(tc::skinny_fwd_x3_kernel, dim3(p.grid), dim3(tc::kThreads), tc::sk_smem_bytes(), st, mw, mx, n1, d0, B, h->P, kBT, p.qmax,
+             just_written(h->W[0], (size_t)n1 * d0 * 4) ? 0 : 1, h->l2_keep[0]);
+    SN_LAUNCH_CHECK();
+    tp.P0 = h->P; tp.parts0 = p.qmax; tp.bpad0 = kBT;
+  } else {
+    const FwdPlan p = plan_fwd(d0, n1, h->sms);
+    const size_t smem = (size_t)kBT * p.kc * 4 + (size_t)8 * kFwdRing * 8 * 32 * 16;
+    if (set_smem(fwd_skinny_kernel<8>, smem)) return 1;
+    const int early = just_written(h->W[0], (size_t)n1 * d0 * 4) ? 0 : 1;
+    launch_k(fwd_skinny_kernel<8>, dim3(p.nx, p.ksplit, 1), dim3(256), smem, st, act, d0, B, h->W[0], d0, n1, d0, p.kc, h->P, kBT,
+             p.ksplit, early, h->l2_keep[0]);
+    SN_LAUNCH_CHECK();
+    tp.P0 = h->P; tp.parts0 = kFwdSlots * p.ksplit; tp.bpad0 = kBT;
+  }
+  auto& s = h->slots[slot];
+  s.step += 1;
+  const OptParams op = make_opt(h->hyper, s.step);
+  tp.op = op;
+  if (!h->tail_bar) {
+    SN_CUDA(cudaMalloc(&h->tail_bar, 256));
+    SN_CUDA(cudaMemsetAsync(h->tail_bar, 0, 256, st));
+    h->tail_arrivals = 0;
+  }
+  const FwdPlan f1 = plan_fwd(n1, n2, h->sms);
+  const BwdPlan b1 = plan_bwd(n2, n1, h->sms, true, OPT == 2);
+  if (!h->Ptail) SN_CUDA(cudaMalloc(&h->Ptail, (size_t)kFwdSlots * f1.ksplit * kBT * n2 * 4));
+  SN_REQUIRE((size_t)b1.nsplit * kBT * n1 <= h->PA_floats, "internal: tail kernel input-gradient partials exceed the scratch");
+  const int grid = h->sms;
+  tp.bar = h->tail_bar;
+  tp.bar_base = h->tail_arrivals;
+  h->tail_arrivals += (unsigned)kTailBarriers * (unsigned)grid;
+  tp.b0 = h->b[0]; tp.mask0 = drop_masks ? drop_masks[0] : nullptr; tp.H1 = h->H[1]; tp.n1 = n1;
+  tp.W1 = h->W[1]; tp.n2 = n2; tp.kc1 = f1.kc; tp.ksplit1 = f1.ksplit; tp.nx1 = f1.nx; tp.l2_keep1 = h->l2_keep[1]; tp.P1 = h->Ptail;
+  tp.b1 = h->b[1]; tp.mask1 = drop_masks ? drop_masks[1] : nullptr; tp.H2 = h->H[2];
+  tp.W2 = h->W[2]; tp.b2 = h->b[2]; tp.n3 = n3; tp.H3 = h->H[3]; tp.logits_out = logits_out;
+  tp.ce = CeTail{labels, h->dZ[3], h->row_loss, h->ticket, loss_out, B, n3};
+  tp.W2m = h->W[2]; tp.b2m = h->b[2]; tp.s1_2 = s.s1[4]; tp.s2_2 = s.s2[4]; tp.bs1_2 = s.s1[5]; tp.bs2_2 = s.s2[5];
+  tp.gscale = drop ? tp.scale : 1.f;
+  tp.dZ2 = h->dZ[2];
+  tp.W1m = h->W[1]; tp.b1m = h->b[1]; tp.s1_1 = s.s1[2]; tp.s2_1 = s.s2[2]; tp.bs1_1 = s.s1[3]; tp.bs2_1 = s.s2[3];
+  tp.kw1 = b1.kw; tp.rows1 = b1.rows_per_cta; tp.kgroups1 = b1.kgroups; tp.nsplit1 = b1.nsplit; tp.PA = h->PA;
+  tp.dZ1 = h->dZ[1];
+  const size_t smem = std::max((size_t)kBT * f1.kc * 4 + (size_t)8 * kFwdRing * 8 * 32 * 16, bwd_smem_bytes(b1, true, OPT == 2));
+  if (set_smem(tail_kernel<OPT>, smem)) return 1;
+  launch_k(tail_kernel<OPT>, dim3(grid), dim3(256), smem, st, tp);
+  SN_LAUNCH_CHECK();
+  // ---- first layer's backward + update (and the cut-layer gradient): the ordinary launches
+  return bob_backward_impl<OPT>(h, slot, act, B, cut_grad, st, next_act, next_B, 0, &op);
+}
+
 extern "C" {
 static int bob_backward_dispatch(sn_bob* h, int slot, const float* act, int B, float* cut_grad, cudaStream_t st,
                                  const float* next_act = nullptr, int next_B = 0) {
@@ -1029,6 +1173,15 @@ static int bob_train_step_impl(sn_bob* h, int slot, const float* act, const int6
   h->stashed = true;
   h->stashed_B = B;
   if (h->relu_last) return fail_msg("libsplitnn: sn_bob_train_step needs a linear last layer (relu_last=0)");
+  if (tail_applies(h, B, act)) {
+    const int rc = h->hyper.type == SN_OPT_ADAM
+                       ? bob_train_step_tail<2>(h, slot, act, labels, B, drop_masks, seed, offset, cut_grad, logits_out, loss_out, st,
+                                                next_act, next_B)
+                       : bob_train_step_tail<1>(h, slot, act, labels, B, drop_masks, seed, offset, cut_grad, logits_out, loss_out, st,
+                                                next_act, next_B);
+    h->stashed = false;
+    return rc;
+  }
   const int C = h->dims[h->L];
   float* z = h->H[h->L];
   // [B][heads*Ch] row-major is [B*heads][Ch]: multi-head CE is the same kernel over more rows
@@ -1433,7 +1586,7 @@ int sn_shard_forward(sn_shard* h, const float* X, int B, int train_mode, const u
   int nparts = 0;
   if (h->pf_valid) {                 // the previous backward traversal already multiplied this batch out
     P = h->PF;
-    nparts = ceil_div(K, 128);
+    nparts = h->pf_parts;
     h->pf_valid = false;
   } else {
     FwdPlan p = plan_fwd(K, N, h->sms);
@@ -1470,10 +1623,20 @@ static int shard_backward_impl(sn_shard* h, const float* X, const float* dH, int
   dim3 grid(p.kgroups, p.nsplit);
   const float* dZ = dH + h->n_off;
   if (X_next && B_next > 0) {
-    if (set_smem(bwd_update_kernel<OPT, false, true>, smem)) return 1;
-    launch_k(bwd_update_kernel<OPT, false, true>, dim3(grid), dim3(256), smem, st, h->W, K, N, K, h->b, h->s1, h->s2, h->bs1, h->bs2,
-             dZ, ld_dh, X, K, B, (float*)nullptr, p.kw, p.rows_per_cta, op, X_next, B_next, h->PF, h->l2_keep,
-             (const float*)h->Hloc, gscale);
+    const int pf_smem = smem + bwd_pf_smem_bytes(p) <= kMaxSmemPerCta && !getenv("SN_NO_PF_SMEM") ? 1 : 0;
+    const size_t smem_f = smem + (pf_smem ? bwd_pf_smem_bytes(p) : 0);
+    h->pf_parts = pf_smem ? p.kgroups : ceil_div(K, 128);
+    if (pf_smem) {
+      if (set_smem(bwd_update_kernel<OPT, false, true, true>, smem_f)) return 1;
+      launch_k(bwd_update_kernel<OPT, false, true, true>, dim3(grid), dim3(256), smem_f, st, h->W, K, N, K, h->b, h->s1, h->s2, h->bs1,
+               h->bs2, dZ, ld_dh, X, K, B, (float*)nullptr, p.kw, p.rows_per_cta, op, X_next, B_next, h->PF, h->l2_keep,
+               (const float*)h->Hloc, gscale);
+    } else {
+      if (set_smem(bwd_update_kernel<OPT, false, true, false>, smem_f)) return 1;
+      launch_k(bwd_update_kernel<OPT, false, true, false>, dim3(grid), dim3(256), smem_f, st, h->W, K, N, K, h->b, h->s1, h->s2, h->bs1,
+               h->bs2, dZ, ld_dh, X, K, B, (float*)nullptr, p.kw, p.rows_per_cta, op, X_next, B_next, h->PF, h->l2_keep,
+               (const float*)h->Hloc, gscale);
+    }
     h->pf_valid = true;
   } else {
     if (set_smem(bwd_update_kernel<OPT, false, false>, smem)) return 1;

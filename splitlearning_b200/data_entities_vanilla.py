@@ -98,7 +98,8 @@ class alice(object):
             self.logger.info(f"Alice-{self.client_id} is first client to train")
         else:
             self.logger.info(f"Alice-{self.client_id} receiving weights from Alice-{last_alice_id}")
-            self.model.load_state_dict(last_alice_rref.give_weights())
+            # same effect as load_state_dict(last_alice.give_weights()) without the host-side clone
+            self.model.copy_weights_from(last_alice_rref.model)
         for epoch in range(self.epochs):
             self._run_batches(self.train_data)
 

@@ -336,6 +336,13 @@ def linear_forward(x, W, bias, relu=False, keep_mask=None, mask_scale=1.0):
     return y
 
 
+def conv_weights_copy(dst_w, dst_b, src_w, src_b):
+    """`sn_conv_weights_copy`: dst <- src for a conv block's weight and bias, enqueued on dst's stream."""
+    with torch.cuda.device(dst_w.device):
+        check(_lib.load().sn_conv_weights_copy(ptr(_f32c(dst_w)), ptr(_f32c(dst_b)), ptr(_f32c(src_w)), ptr(_f32c(src_b)),
+                                               _stream(dst_w.device)))
+
+
 def linear_forward_noalloc(x, W, bias, relu=False, keep_mask=None, mask_scale=1.0, out=None):
     """`sn_linear_forward_noalloc`: same result as `linear_forward`, but the library uses its own
     built-in 4 MiB scratch and allocates nothing.  Pass `out` to keep this wrapper allocation-free

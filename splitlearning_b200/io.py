@@ -41,9 +41,11 @@ class HostBatchPrefetcher:
         self.free[slot].record(torch.cuda.current_stream(self.device))
 
 
-def iterate_host_batches(batches, device, batch_size):
-    """Yield (x_dev, y_dev) for an iterable of pinned (hx, hy) host batches, prefetching one ahead."""
-    pf = HostBatchPrefetcher(device, batch_size)
+def iterate_host_batches(batches, device, batch_size, prefetcher=None):
+    """Yield (x_dev, y_dev) for an iterable of pinned (hx, hy) host batches, prefetching one ahead.
+    `prefetcher`: a HostBatchPrefetcher to reuse (its stream, events and staging buffers are set-up
+    costs; build it once per loader, not once per epoch)."""
+    pf = prefetcher or HostBatchPrefetcher(device, batch_size)
     it = iter(batches)
     nxt = next(it, None)
     slot = 0

@@ -61,6 +61,18 @@ class _ConvBlock(nn.Module):
         w, b = self._wb()
         return E.AliceEngine(w.data, b.data, **opt)
 
+    def copy_weights_from(self, other):
+        """The Alice -> Alice weight hand-off (`give_weights` + `load_state_dict`,
+        `data_entities_vanilla.py:59-64`) as a stream-ordered device copy of 288 + 32 floats: no
+        host-side state_dict clone; across GPUs two peer copies."""
+        (w, b), (ow, ob) = self._wb(), other._wb()
+        if w.device == ow.device:
+            E.conv_weights_copy(w.data, b.data, ow.data, ob.data)      # one small launch in the stream's chain
+        else:
+            with torch.no_grad():
+                w.copy_(ow, non_blocking=True)
+                b.copy_(ob, non_blocking=True)
+
 
 class model1(_ConvBlock):
     """U-shape client head (`models.py:5-14`): keys `conv1.weight`, `conv1.bias`."""

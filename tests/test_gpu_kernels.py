@@ -172,6 +172,46 @@ def test_vanilla_step_vs_oracle_and_golden(eng, B):
         assert rel_err(p.cpu().numpy() - p0, p_ref.numpy() - p0) <= 2e-3, n
 
 
+@pytest.mark.parametrize("opt", ["sgd", "adam"])
+def test_persistent_tail_kernel_is_bit_identical_to_the_launch_chain(eng, opt):
+    """sn_set_persistent_tail(1): the middle of the step (fc1 epilogue .. fc2 backward) runs as one
+    persistent kernel with grid barriers instead of seven launches.  Same kernel bodies, same order of
+    every sum: logits, loss, cut gradient and all updated weights must be EQUAL bit for bit, over
+    three steps, with given masks and with in-kernel Philox dropout, full and ragged batches.  (Both
+    forms are separately checked against the oracle by the tests around this one.)"""
+    from splitlearning_b200 import _lib
+    lib = _lib.load()
+    kw = (dict(optimizer=eng.SN_OPT_SGD_MOMENTUM, lr=1e-3, momentum=0.9) if opt == "sgd"
+          else dict(optimizer=eng.SN_OPT_ADAM, lr=1e-3, weight_decay=1e-5))
+    a = T(seeded_weights(A_SHAPES, 11))
+    results = []
+    was = lib.sn_get_persistent_tail()
+    try:
+        for tail in (0, 1):
+            _lib.check(lib.sn_set_persistent_tail(tail))
+            assert lib.sn_get_persistent_tail() == tail
+            bob, gp = _bob(eng, T(seeded_weights(B_SHAPES, 12)), **kw)
+            out = []
+            n0 = lib.sn_launch_count()
+            for step, B in enumerate((16, 16, 5)):
+                x, y = seeded_batch(B, 100 + step)
+                act = cu(R.alice_forward(torch.from_numpy(x), a[0], a[1]).numpy())
+                masks = [cu(m) for m in seeded_masks(B, (5000, 1000), 200 + step)] if step != 1 else None
+                loss, cut, logits = bob.train_step(act, cu(y), masks=masks, seed=3, offset=step + 1, want_logits=True,
+                                                   want_cut_grad=opt == "sgd")
+                out += [loss.clone(), logits.clone()] + ([cut.clone()] if cut is not None else [])
+            torch.cuda.synchronize()
+            out += [p.clone() for p in gp]
+            results.append((out, lib.sn_launch_count() - n0))
+    finally:
+        _lib.check(lib.sn_set_persistent_tail(was))
+    (chain, n_chain), (tail, n_tail) = results
+    assert n_tail < n_chain                               # six launches per step fewer
+    assert len(chain) == len(tail)
+    for u, v in zip(chain, tail):
+        assert torch.equal(u, v)
+
+
 def test_sisa_server_steps_vs_oracle_and_golden(eng):
     g = load_golden("modules_sisa_server.npz")
     a, b = T(seeded_weights(A_SHAPES, 11)), T(seeded_weights(B_SHAPES, 12))

@@ -373,6 +373,26 @@ static size_t fwd_partial_floats(int B, int K, int N, int sms, int skinny_max = 
 
 using namespace sn;
 
+// A handle's calls run on the handle's device and leave the caller's current device as it was (the
+// host program - torch - keeps its own idea of the current device).
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess) { cudaGetLastError(); cur = -1; }
+    if (cur != dev) {
+      cudaSetDevice(dev);
+      prev = cur;
+    }
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+  DeviceGuard(const DeviceGuard&) = delete;
+  DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+
+
 // =============================================================================== handles
 struct sn_bob {
   int device = 0, L = 0, relu_last = 0, n_slots = 1, max_batch = 16, Bpad = 16, sms = 148;
@@ -637,7 +657,7 @@ int sn_bob_create(sn_bob** out, int device, const int* dims, int n_layers, int r
   int ndev = 0;
   SN_CUDA(cudaGetDeviceCount(&ndev));
   SN_REQUIRE(device >= 0 && device < ndev, "sn_bob_create: no such CUDA device (a B200 is required; there is no CPU path)");
-  SN_CUDA(cudaSetDevice(device));
+  DeviceGuard device_guard_(device);
   sn_bob* h = new sn_bob();
   h->device = device;
   h->L = n_layers;
@@ -727,7 +747,7 @@ int sn_bob_create(sn_bob** out, int device, const int* dims, int n_layers, int r
 
 int sn_bob_destroy(sn_bob* h) {
   if (!h) return 0;
-  cudaSetDevice(h->device);
+  DeviceGuard device_guard_(h->device);
   for (auto p : h->H) cudaFree(p);
   for (auto p : h->dZ) cudaFree(p);
   cudaFree(h->P);
@@ -749,7 +769,7 @@ int sn_bob_destroy(sn_bob* h) {
 
 #define SN_BOB_ENTER(h)                                     \
   SN_REQUIRE(h != nullptr, "null sn_bob handle");           \
-  SN_CUDA(cudaSetDevice(h->device));
+  DeviceGuard device_guard_(h->device);
 
 int sn_bob_reset_opt_slot(sn_bob* h, int slot, void* stream) {
   SN_BOB_ENTER(h);
@@ -1282,7 +1302,7 @@ int sn_alice_create(sn_alice** out, int device, int optimizer, double lr, double
   int ndev = 0;
   SN_CUDA(cudaGetDeviceCount(&ndev));
   SN_REQUIRE(device >= 0 && device < ndev, "sn_alice_create: no such CUDA device (a B200 is required; there is no CPU path)");
-  SN_CUDA(cudaSetDevice(device));
+  DeviceGuard device_guard_(device);
   sn_alice* h = new sn_alice();
   h->device = device;
   h->max_batch = max_batch;
@@ -1313,7 +1333,7 @@ int sn_alice_create(sn_alice** out, int device, int optimizer, double lr, double
 
 int sn_alice_destroy(sn_alice* h) {
   if (!h) return 0;
-  cudaSetDevice(h->device);
+  DeviceGuard device_guard_(h->device);
   cudaFree(h->s1);
   cudaFree(h->s2);
   cudaFree(h->partial);
@@ -1327,7 +1347,7 @@ int sn_alice_destroy(sn_alice* h) {
 
 #define SN_ALICE_ENTER(h)                                   \
   SN_REQUIRE(h != nullptr, "null sn_alice handle");         \
-  SN_CUDA(cudaSetDevice(h->device));
+  DeviceGuard device_guard_(h->device);
 
 int sn_alice_reset_opt(sn_alice* h, void* stream) {
   SN_ALICE_ENTER(h);
@@ -1486,11 +1506,11 @@ int sn_p2p_copy(void* dst, int dst_device, const void* src, int src_device, size
 // ------------------------------------------------------------------ tensor-parallel layer slices
 #define SN_SHARD_ENTER(h)                                              \
   SN_REQUIRE((h) != nullptr, "null sn_shard handle");                  \
-  SN_CUDA(cudaSetDevice((h)->device))
+  DeviceGuard device_guard_((h)->device)
 
 int sn_shard_destroy(sn_shard* h) {
   if (!h) return 0;
-  cudaSetDevice(h->device);
+  DeviceGuard device_guard_(h->device);
   cudaFree(h->s1); cudaFree(h->s2); cudaFree(h->bs1); cudaFree(h->bs2);
   cudaFree(h->P); cudaFree(h->PF); cudaFree(h->Hloc);
   delete h;
@@ -1509,7 +1529,7 @@ int sn_shard_create(sn_shard** out, int device, int K, int n_total, int n_off, i
   int ndev = 0;
   SN_CUDA(cudaGetDeviceCount(&ndev));
   SN_REQUIRE(device >= 0 && device < ndev, "sn_shard_create: no such CUDA device");
-  SN_CUDA(cudaSetDevice(device));
+  DeviceGuard device_guard_(device);
   sn_shard* h = new sn_shard();
   h->device = device; h->K = K; h->n_total = n_total; h->n_off = n_off; h->n_rows = n_rows; h->relu = relu;
   h->dropout_p = (float)dropout_p;
@@ -1714,7 +1734,6 @@ int sn_tp_server_epoch(sn_shard* shard, sn_bob* head, int rank, int world, const
       }
       if (drop_masks)
         for (int l = 0; l < nm; ++l) hm[l] = drop_masks[l + 1] + (size_t)r0 * head->dims[l + 1];
-      SN_CUDA(cudaSetDevice(head->device));
       head->pf_valid = false;
       // the head's cut-gradient reduction pushes every rank's column range into that rank's own
       // memory (reading it from here over NVLink made the remote traversals 19 us slower)

@@ -309,7 +309,8 @@ def _view_f32(address, count, device):
 def conv_pool_forward(x, w, b):
     lib = _lib.load()
     out = torch.empty(x.shape[0], D0, device=x.device)
-    check(lib.sn_conv_pool_forward(ptr(_f32c(x)), ptr(_f32c(w)), ptr(_f32c(b)), x.shape[0], ptr(out), _stream(x.device)))
+    with torch.cuda.device(x.device):          # the stateless entry points launch on the CURRENT device
+        check(lib.sn_conv_pool_forward(ptr(_f32c(x)), ptr(_f32c(w)), ptr(_f32c(b)), x.shape[0], ptr(out), _stream(x.device)))
     return out
 
 
@@ -318,9 +319,10 @@ def conv_pool_backward(x, w, b, dact):
     B = x.shape[0]
     dw = torch.empty(32, 1, 3, 3, device=x.device)
     db = torch.empty(32, device=x.device)
-    scratch = torch.empty(lib.sn_conv_pool_backward_scratch_bytes(B), dtype=torch.uint8, device=x.device)
-    check(lib.sn_conv_pool_backward(ptr(_f32c(x)), ptr(_f32c(w)), ptr(_f32c(b)), ptr(_f32c(dact)), B, ptr(dw), ptr(db),
-                                    ptr(scratch), _stream(x.device)))
+    with torch.cuda.device(x.device):
+        scratch = torch.empty(lib.sn_conv_pool_backward_scratch_bytes(B), dtype=torch.uint8, device=x.device)
+        check(lib.sn_conv_pool_backward(ptr(_f32c(x)), ptr(_f32c(w)), ptr(_f32c(b)), ptr(_f32c(dact)), B, ptr(dw), ptr(db),
+                                        ptr(scratch), _stream(x.device)))
     return dw, db
 
 
@@ -329,10 +331,11 @@ def linear_forward(x, W, bias, relu=False, keep_mask=None, mask_scale=1.0):
     B, K = x.shape
     N = W.shape[0]
     y = torch.empty(B, N, device=x.device)
-    nbytes = lib.sn_linear_forward_scratch_bytes(B, K, N)
-    scratch = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
-    check(lib.sn_linear_forward(ptr(_f32c(x)), ptr(_f32c(W)), ptr(_f32c(bias)), B, K, N, int(bool(relu)),
-                                ptr(keep_mask), float(mask_scale), ptr(y), ptr(scratch), nbytes, _stream(x.device)))
+    with torch.cuda.device(x.device):
+        nbytes = lib.sn_linear_forward_scratch_bytes(B, K, N)
+        scratch = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+        check(lib.sn_linear_forward(ptr(_f32c(x)), ptr(_f32c(W)), ptr(_f32c(bias)), B, K, N, int(bool(relu)),
+                                    ptr(keep_mask), float(mask_scale), ptr(y), ptr(scratch), nbytes, _stream(x.device)))
     return y
 
 
@@ -351,8 +354,9 @@ def linear_forward_noalloc(x, W, bias, relu=False, keep_mask=None, mask_scale=1.
     B, K = x.shape
     N = W.shape[0]
     y = out if out is not None else torch.empty(B, N, device=x.device)
-    check(lib.sn_linear_forward_noalloc(ptr(_f32c(x)), ptr(_f32c(W)), ptr(_f32c(bias)), B, K, N, int(bool(relu)),
-                                        ptr(keep_mask), float(mask_scale), ptr(_f32c(y)), _stream(x.device)))
+    with torch.cuda.device(x.device):
+        check(lib.sn_linear_forward_noalloc(ptr(_f32c(x)), ptr(_f32c(W)), ptr(_f32c(bias)), B, K, N, int(bool(relu)),
+                                            ptr(keep_mask), float(mask_scale), ptr(_f32c(y)), _stream(x.device)))
     return y
 
 
@@ -361,7 +365,8 @@ def cross_entropy(logits, labels, want_grad=True):
     B, Cn = logits.shape
     loss = torch.empty((), device=logits.device)
     d = torch.empty_like(logits) if want_grad else None
-    check(lib.sn_cross_entropy(ptr(_f32c(logits)), ptr(labels), B, Cn, ptr(loss), ptr(d), _stream(logits.device)))
+    with torch.cuda.device(logits.device):
+        check(lib.sn_cross_entropy(ptr(_f32c(logits)), ptr(labels), B, Cn, ptr(loss), ptr(d), _stream(logits.device)))
     return loss, d
 
 
@@ -370,6 +375,7 @@ def eval_counts(logits, labels, omit_label, counters=None):
     B, Cn = logits.shape
     if counters is None:
         counters = torch.zeros(6, dtype=torch.int64, device=logits.device)
-    check(lib.sn_eval_counts(ptr(_f32c(logits)), ptr(labels), B, Cn, int(omit_label), ptr(counters),
-                             _stream(logits.device)))
+    with torch.cuda.device(logits.device):
+        check(lib.sn_eval_counts(ptr(_f32c(logits)), ptr(labels), B, Cn, int(omit_label), ptr(counters),
+                                 _stream(logits.device)))
     return counters

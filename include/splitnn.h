@@ -267,7 +267,9 @@ int sn_alice_local_epoch(sn_alice* h, const float* x, const int64_t* labels, int
 
 /* One whole vanilla split step on one device in one call: sn_alice_forward -> sn_bob_train_step
  * (Philox dropout) -> sn_alice_backward_update, i.e. the body of alice.train's batch loop,
- * data_entities_vanilla.py:70-76.  act and cut_grad are caller scratch [B,5408]. */
+ * data_entities_vanilla.py:70-76.  act and cut_grad are caller scratch [B,5408]; cut_grad may be left
+ * unwritten (for batches <= 16 the conv backward adds the server's partial sums itself instead of
+ * reading a reduced copy). */
 int sn_vanilla_step(sn_alice* alice, sn_bob* bob, int slot, const float* x, const int64_t* labels,
                     int B, uint64_t seed, uint64_t offset, float* act, float* cut_grad,
                     float* loss_out, void* stream);
@@ -360,7 +362,12 @@ int sn_shard_backward_update(sn_shard* h, const float* X, const float* dH, int l
  * layer sharded over `world` ranks: the tensor-parallel form of sn_bob_server_epoch, i.e. of the
  * epoch body of bob.train_and_backward, data_entities_vanilla_sisa.py:298-313.  Every rank calls it
  * with its shard and the same cache (replicated); rank 0 also passes `head` (an sn_bob over the
- * remaining layers, input width = the sharded layer's width) and the labels.  H1 is the [16, n_total]
+ * remaining layers, input width = the sharded layer's width) and the labels; rank 0 of a multi-rank
+ * run may come WITHOUT a shard (shard = NULL, cache unused: it is then the head only).  Column
+ * ownership of H1/dH1: rank 0's shard rows first (possibly none), then equal ranges for ranks 1.. .
+ * The head forms its input gradient with a read-only pass over its first layer, pushes every rank's
+ * columns into that rank's memory and releases the flags BEFORE its own first-layer update
+ * traversal, which then overlaps the shards' traversals.  H1 is the [16, n_total]
  * activation buffer in rank 0's mailbox (a peer pointer elsewhere) and h_ready_flags the base of the
  * per-rank flags next to it (rank r's at +128*r bytes); dH1 [16, n_total] and dh_ready_flag are THIS
  * rank's own gradient buffer and flag.  Rank 0 also passes two DEVICE arrays: dH1_table_dev[world]

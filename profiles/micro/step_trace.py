@@ -130,6 +130,8 @@ KNOWN = {6: ["conv_fwd", "fwd_fc1", "tail(epi1,fc2,epi2,fc3,ce+bwd3,bwd2,bepi2)"
               "tail:bepi_fc2", "bwd_fc1", "bepi_fc1", "conv_bwd"] if os.environ.get("SN_TAIL") else
              ["conv_fwd", "fwd_fc1", "epi_fc1", "fwd_fc2", "epi_fc2", "fc3+ce", "bwd_fc3", "bwd_fc2", "bepi_fc2",
               "bwd_fc1", "bepi_fc1", "conv_bwd"],
+         11: ["conv_fwd", "fwd_fc1", "epi_fc1", "fwd_fc2", "epi_fc2", "fc3+ce", "bwd_fc3", "bwd_fc2", "bepi_fc2", "bwd_fc1",
+              "conv_bwd(+cut partial sums)"],
          10: ["conv_fwd", "fwd_fc1+epi", "fwd_fc2+epi", "fc3+ce", "bwd_fc3", "bwd_fc2", "bepi_fc2", "bwd_fc1", "bepi_fc1",
               "conv_bwd"],
          14: ["conv_fwd", "fwd_fc1", "epi_fc1", "fwd_fc2", "epi_fc2", "fwd_fc3", "ce", "bwd_fc3", "bepi_fc3", "bwd_fc2",

@@ -969,7 +969,7 @@ bwd_update_body(float4* smem4, const dim3 bid, Sync sync,
     if (kok && row < nb1) {
       const size_t o = (size_t)row * ldw + k0;
       if (OPT != 3 || NEED_DA) cp_async16_hint(ring + (0 * kRing + slot) * 256 + tid, W + o, row < l2_keep_w ? pol_keep : pol_norm);
-      if (OPT != 3 || !op.acc_first) cp_async16_hint(ring + (1 * kRing + slot) * 256 + tid, s1 + o, pol_s);
+      if (OPT != 4 && (OPT != 3 || !op.acc_first)) cp_async16_hint(ring + (1 * kRing + slot) * 256 + tid, s1 + o, pol_s);
       if (OPT == 2) cp_async16_hint(ring + (2 * kRing + slot) * 256 + tid, s2 + o, pol_s);
     }
     cp_async_commit();
@@ -1046,7 +1046,7 @@ bwd_update_body(float4* smem4, const dim3 bid, Sync sync,
     float4 w = make_float4(0.f, 0.f, 0.f, 0.f), m1 = w, m2 = w;
     if (kok) {
       if (OPT != 3 || NEED_DA) w = ring[(0 * kRing + slot) * 256 + tid];
-      if (OPT != 3 || !op.acc_first) m1 = ring[(1 * kRing + slot) * 256 + tid];
+      if (OPT != 4 && (OPT != 3 || !op.acc_first)) m1 = ring[(1 * kRing + slot) * 256 + tid];
       if (OPT == 2) m2 = ring[(2 * kRing + slot) * 256 + tid];
     }
     slot = (slot + 1) & (kRing - 1);
@@ -1070,7 +1070,10 @@ bwd_update_body(float4* smem4, const dim3 bid, Sync sync,
       }
     }
     float4 g = make_float4(g2[0].x + g2[0].y, g2[1].x + g2[1].y, g2[2].x + g2[2].y, g2[3].x + g2[3].y);
-    if (OPT == 3) {
+    if (OPT == 4) {
+      // input-gradient-only launch (tensor-parallel head: dA goes out to the shards before the update
+      // traversal starts): the weights are read, nothing is written per row
+    } else if (OPT == 3) {
       // accumulation launch (batches of 17..64 rows go through in tiles of 16): the gradient of this
       // tile is added into the buffer behind `s1`; the weights are only read (for dA)
       if (kok) {
@@ -1129,7 +1132,7 @@ bwd_update_body(float4* smem4, const dim3 bid, Sync sync,
   // bias: db[n] = sum_b dZ[b][n].  One thread per row AFTER the streaming loop (a per-row
   // load->update->store chain inside the loop made the k-group-0 CTAs latency-bound and the
   // whole grid wait for them).
-  if (OPT != 3 && bid.x == 0) {
+  if (OPT != 3 && OPT != 4 && bid.x == 0) {
     for (int j = tid; j < nrows; j += 256) {
       float db = 0.f;
 #pragma unroll
@@ -1340,13 +1343,13 @@ bwd_small_kernel(float* __restrict__ W, int ldw, int N, int K, float* __restrict
 
 // dst[b][k] = (sum_s PA[s][b][k]) * gate, gate = (H[b][k] > 0 ? scale : 0) for hidden layers
 // (H is the post-ReLU, post-dropout activation so H>0 <=> ReLU active and kept), 1 at the cut.
-// dst_table != nullptr (tensor-parallel head): column k goes to dst_table[k / cols_per_dst] instead of
+// dst_table != nullptr (tensor-parallel head): column k goes to dst_table[owner of column k] instead of
 // dst - each consumer GPU gets its column range pushed into its own memory over NVLink.
 template <class Sync>
 __device__ __forceinline__ void
 bwd_epilogue_body(const unsigned bx, const unsigned gdx, Sync sync, const float* __restrict__ PA, int nsplit, int B, int K,
                   const float* __restrict__ H, int ldh, float scale, float* __restrict__ dst, int ldd,
-                  float* const* __restrict__ dst_table, int cols_per_dst) {
+                  float* const* __restrict__ dst_table, int cols_per_dst, int first_cols = -1) {
   sync();
   const size_t total = (size_t)B * K;
   const size_t stride = (size_t)gdx * blockDim.x;
@@ -1365,15 +1368,19 @@ bwd_epilogue_body(const unsigned bx, const unsigned gdx, Sync sync, const float*
     }
     for (; p < nsplit; ++p) s += ld_dep<Sync>(pp + (size_t)p * pstride);
     if (H) s = hv > 0.f ? s * scale : 0.f;
-    float* d = dst_table ? dst_table[k / cols_per_dst] : dst;
+    // first_cols >= 0: consumer 0 owns the first `first_cols` columns (possibly none), the others
+    // cols_per_dst each after that (the tensor-parallel head keeps a smaller slice for its own GPU)
+    float* d = dst_table ? dst_table[first_cols < 0 ? k / cols_per_dst : (k < first_cols ? 0 : 1 + (k - first_cols) / cols_per_dst)]
+                         : dst;
     d[(size_t)b * ldd + k] = s;
   }
 }
 
 __global__ void bwd_epilogue_kernel(const float* __restrict__ PA, int nsplit, int B, int K,
                                     const float* __restrict__ H, int ldh, float scale, float* __restrict__ dst,
-                                    int ldd, float* const* __restrict__ dst_table, int cols_per_dst) {
-  bwd_epilogue_body(blockIdx.x, gridDim.x, PdlSync{}, PA, nsplit, B, K, H, ldh, scale, dst, ldd, dst_table, cols_per_dst);
+                                    int ldd, float* const* __restrict__ dst_table, int cols_per_dst, int first_cols) {
+  bwd_epilogue_body(blockIdx.x, gridDim.x, PdlSync{}, PA, nsplit, B, K, H, ldh, scale, dst, ldd, dst_table, cols_per_dst,
+                    first_cols);
 }
 
 // dst = src * (out > 0)  (ReLU on the last layer, U-shape model2)

@@ -7,6 +7,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <functional>
 #include <mutex>
 #include <vector>
 
@@ -415,6 +416,12 @@ struct sn_bob {
   unsigned* ticket = nullptr;
   float* const* cut_table = nullptr;   // tensor-parallel head: per-consumer destinations of the cut gradient's columns
   int cut_cols = 1;
+  bool defer_cut = false;              // sn_vanilla_step: leave the cut gradient as n-split partials in PA ...
+  int deferred_nsplit = 0;             // ... (this many) for the conv backward kernel to add up itself
+  int cut_first = -1;                  // >= 0: consumer 0 owns this many leading columns, the others cut_cols each
+  // tensor-parallel head: produce and hand out the cut gradient BEFORE the first layer's update
+  // traversal (a read-only pass over its weights), then call this (the flag release), then update
+  std::function<int(cudaStream_t)> after_cut;
   bool stashed = false;
   int stashed_B = 0;
   int heads = 1;
@@ -539,7 +546,7 @@ int sn_conv_pool_backward(const float* x, const float* w, const float* b, const 
   SN_CUDA(cudaMemsetAsync(ticket, 0, 256, st));
   OptParams op{};
   launch_k(conv_pool_bwd_kernel<0>, dim3(gx, 4), dim3(256), 0, st, x, const_cast<float*>(w), const_cast<float*>(b), dact, B,
-                                                      partial, ticket, dw, db, nullptr, nullptr, op, 0);
+                                                      partial, ticket, dw, db, nullptr, nullptr, op, 0, 1, (size_t)0);
   SN_LAUNCH_CHECK();
   return 0;
 }
@@ -942,7 +949,32 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
       BwdPlan p = plan_bwd(N, K, h->sms, need_da, OPT == 2);
       size_t smem = bwd_smem_bytes(p, need_da, OPT == 2);
       dim3 grid(p.kgroups, p.nsplit);
-      if (need_da) {
+      if (need_da && l == 0 && h->after_cut) {
+        // Tensor-parallel head: the shards wait for this layer's input gradient and for nothing else,
+        // and it depends only on dZ and the OLD weights.  So: a read-only pass forms it (4*N*K bytes),
+        // its reduction pushes each consumer's columns into that consumer's memory, the flags are
+        // released - and only then does the update traversal (16-24 bytes per weight) run, while the
+        // shards are already streaming their slices.
+        if (set_smem(bwd_update_kernel<4, true>, smem)) return 1;
+        launch_k(bwd_update_kernel<4, true>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
+                 s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, h->PA, p.kw, p.rows_per_cta, op, (const float*)nullptr, 0,
+                 (float*)nullptr, 0, (const float*)nullptr, 1.f);
+        SN_LAUNCH_CHECK();
+        launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, p.nsplit, B, K, gateH, K,
+                 gscale, dst, K, h->cut_table, h->cut_cols, h->cut_first);
+        SN_LAUNCH_CHECK();
+        if (int rc = h->after_cut(st)) return rc;
+        const BwdPlan pu = plan_bwd(N, K, h->sms, false, OPT == 2);
+        const size_t smem_u = bwd_smem_bytes(pu, false, OPT == 2);
+        if (set_smem(bwd_update_kernel<OPT, false>, smem_u)) return 1;
+        cudaEvent_t pe = h->prof.begin(st, 1, l);
+        launch_k(bwd_update_kernel<OPT, false>, dim3(pu.kgroups, pu.nsplit), dim3(256), smem_u, st, h->W[l], K, N, K, h->b[l],
+                 s.s1[2 * l], s.s2[2 * l], s.s1[2 * l + 1], s.s2[2 * l + 1], dZ, N, A, K, B, h->PA, pu.kw, pu.rows_per_cta, op,
+                 (const float*)nullptr, 0, (float*)nullptr, h->l2_keep[l], (const float*)nullptr, 1.f);
+        Profiler::end(pe, st);
+        SN_LAUNCH_CHECK();
+        mark_written(h->W[l], wbytes);
+      } else if (need_da) {
         if (set_smem(bwd_update_kernel<OPT, true>, smem)) return 1;
         cudaEvent_t pe = h->prof.begin(st, 1, l);
         launch_k(bwd_update_kernel<OPT, true>, dim3(grid), dim3(256), smem, st, h->W[l], K, N, K, h->b[l], s.s1[2 * l], s.s2[2 * l],
@@ -951,8 +983,14 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
                                                               h->l2_keep[l], (const float*)nullptr, 1.f);
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
+        if (l == 0 && h->defer_cut && K == kD0 && !h->cut_table) {
+          // the consumer (Alice's conv backward, next in the same call) adds the partials itself
+          h->deferred_nsplit = p.nsplit;
+          mark_written(h->W[l], wbytes);
+          continue;
+        }
         launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, p.nsplit, B, K, gateH, K,
-                 gscale, dst, K, l == 0 ? h->cut_table : (float* const*)nullptr, h->cut_cols);
+                 gscale, dst, K, l == 0 ? h->cut_table : (float* const*)nullptr, h->cut_cols, h->cut_first);
         SN_LAUNCH_CHECK();
       } else if (l == 0 && next_act && next_B > 0 && next_B <= kBT && (size_t)N * K > kSmallLayerElems) {
         // SISA: fuse the next step's layer-0 forward into this traversal
@@ -1016,7 +1054,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
           SN_LAUNCH_CHECK();
           launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)nt * K, h->sms)), dim3(256), 0, st, h->PA, p.nsplit, nt, K,
                    gateH ? gateH + (size_t)r0 * K : (const float*)nullptr, K, gscale, dst + (size_t)r0 * K, K,
-                   (float* const*)nullptr, 1);
+                   (float* const*)nullptr, 1, -1);
           SN_LAUNCH_CHECK();
         } else {
           if (set_smem(bwd_update_kernel<3, false>, smem)) return 1;
@@ -1078,7 +1116,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
       if (need_da) {
         // PA holds one dense [B][K] "split"; bwd_epilogue indexes splits with a 16-row stride
         launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, 1, B, K, gateH, K, gscale, dst, K,
-                 l == 0 ? h->cut_table : (float* const*)nullptr, h->cut_cols);
+                 l == 0 ? h->cut_table : (float* const*)nullptr, h->cut_cols, h->cut_first);
         SN_LAUNCH_CHECK();
       }
     }
@@ -1387,7 +1425,8 @@ int sn_alice_forward_ld(sn_alice* h, const float* x, int B, float* act, size_t l
   return launch_conv_fwd(x, h->w, h->b, B, act, ld_act, h->sms, (cudaStream_t)stream);
 }
 
-static int alice_bwd(sn_alice* h, const float* x, const float* dact, int B, cudaStream_t st) {
+static int alice_bwd(sn_alice* h, const float* x, const float* dact, int B, cudaStream_t st, int nsplit = 1,
+                     size_t pstride = 0) {
   SN_REQUIRE(B <= h->max_batch, "batch larger than max_batch given to sn_alice_create");
   h->step += 1;
   const OptParams op = make_opt(h->hyper, h->step);
@@ -1399,11 +1438,11 @@ static int alice_bwd(sn_alice* h, const float* x, const float* dact, int B, cuda
   switch (h->hyper.type) {
     case SN_OPT_SGD_MOMENTUM:
       launch_k(conv_pool_bwd_kernel<1>, dim3(grid), dim3(256), 0, st, x, h->w, h->b, dact, B, h->partial, h->ticket, nullptr, nullptr,
-                                                   h->s1, h->s2, op, early);
+                                                   h->s1, h->s2, op, early, nsplit, pstride);
       break;
     case SN_OPT_ADAM:
       launch_k(conv_pool_bwd_kernel<2>, dim3(grid), dim3(256), 0, st, x, h->w, h->b, dact, B, h->partial, h->ticket, nullptr, nullptr,
-                                                   h->s1, h->s2, op, early);
+                                                   h->s1, h->s2, op, early, nsplit, pstride);
       break;
     default:
       return fail_msg("libsplitnn: this sn_alice was created without an optimizer");
@@ -1452,8 +1491,19 @@ int sn_vanilla_step(sn_alice* alice, sn_bob* bob, int slot, const float* x, cons
   SN_REQUIRE(alice->device == bob->device, "sn_vanilla_step: Alice and Bob must share a device (use the separate calls across GPUs)");
   int rc = sn_alice_forward(alice, x, B, act, stream);
   if (rc) return rc;
+  // Both halves of the step are in this one call, so the cut-layer gradient need not be materialised:
+  // Bob's first-layer backward leaves its n-split partial sums and Alice's conv backward adds them
+  // while it loads them (one reduction launch less; cut_grad stays untouched then).
+  static const bool fold = getenv("SN_NO_CUT_FOLD") == nullptr;
+  bob->defer_cut = fold && B <= kBT;
+  bob->deferred_nsplit = 0;
   rc = sn_bob_train_step(bob, slot, act, labels, B, nullptr, seed, offset, cut_grad, nullptr, loss_out, stream);
+  bob->defer_cut = false;
   if (rc) return rc;
+  if (bob->deferred_nsplit > 0) {
+    SN_ALICE_ENTER(alice);
+    return alice_bwd(alice, x, bob->PA, B, (cudaStream_t)stream, bob->deferred_nsplit, (size_t)kBT * kD0);
+  }
   return sn_alice_backward_update(alice, x, cut_grad, B, stream);
 }
 
@@ -1690,38 +1740,47 @@ int sn_tp_server_epoch(sn_shard* shard, sn_bob* head, int rank, int world, const
                        uint64_t offset, float* H1, float* dH1, void* h_ready_flags, void* dh_ready_flag,
                        float* const* dH1_table_dev, const void* dh_flag_table_dev, uint32_t seq0, float* loss_per_step,
                        void* stream) {
-  SN_SHARD_ENTER(shard);
+  SN_REQUIRE(shard || (rank == 0 && head && world > 1), "sn_tp_server_epoch: only the head rank of a multi-rank run may come without a shard");
+  DeviceGuard device_guard_(shard ? shard->device : head->device);
   if (n_batches == 0) return 0;
-  SN_REQUIRE(cache && batch_offsets && n_batches > 0 && H1 && dH1 && world >= 1 && rank >= 0 && rank < world,
+  SN_REQUIRE(batch_offsets && n_batches > 0 && H1 && dH1 && world >= 1 && rank >= 0 && rank < world,
              "sn_tp_server_epoch: bad arguments");
+  SN_REQUIRE(cache || !shard, "sn_tp_server_epoch: a rank with a shard needs the cached activations");
   SN_REQUIRE((rank == 0) == (head != nullptr), "sn_tp_server_epoch: rank 0, and only rank 0, passes the head");
   SN_REQUIRE(rank != 0 || labels, "sn_tp_server_epoch: the head needs the labels");
   SN_REQUIRE(world == 1 || (h_ready_flags && dh_ready_flag), "sn_tp_server_epoch: flags are required with more than one rank");
   SN_REQUIRE(world == 1 || rank != 0 || (dH1_table_dev && dh_flag_table_dev),
              "sn_tp_server_epoch: the head needs the per-rank gradient destinations and flags");
-  SN_REQUIRE(!head || (head->dims[0] == shard->n_total && head->device == shard->device),
+  SN_REQUIRE(!head || !shard || (head->dims[0] == shard->n_total && head->device == shard->device),
              "sn_tp_server_epoch: the head's input width must be the sharded layer's width");
   cudaStream_t st = (cudaStream_t)stream;
-  const int K = shard->K, n1 = shard->n_total;
+  const int n1 = shard ? shard->n_total : head->dims[0];
+  const int K = shard ? shard->K : 0;
   const int nm = head ? head->L - 1 : 0;
   std::vector<const uint8_t*> hm(std::max(nm, 1), nullptr);
   char* flags = reinterpret_cast<char*>(h_ready_flags);
+  // column ownership of H1 / dH1: rank 0 owns the first r0 columns (its shard's rows; none without a
+  // shard), ranks 1..world-1 equal ranges after that
+  const int r0 = (rank == 0) ? (shard ? shard->n_rows : 0) : -1;
   for (int i = 0; i < n_batches; ++i) {
-    const int64_t r0 = batch_offsets[i], r1 = batch_offsets[i + 1];
-    SN_REQUIRE(r1 > r0 && r1 - r0 <= kBT, "sn_tp_server_epoch: batches of 1..16 rows");
-    const int n = (int)(r1 - r0);
-    const float* X = cache + (size_t)r0 * K;
+    const int64_t b0 = batch_offsets[i], b1 = batch_offsets[i + 1];
+    SN_REQUIRE(b1 > b0 && b1 - b0 <= kBT, "sn_tp_server_epoch: batches of 1..16 rows");
+    const int n = (int)(b1 - b0);
+    const float* X = shard ? cache + (size_t)b0 * K : nullptr;
     const float* Xn = nullptr;
     int Bn = 0;
-    if (i + 1 < n_batches) {
+    if (shard && i + 1 < n_batches) {
       Xn = cache + (size_t)batch_offsets[i + 1] * K;
       Bn = (int)(batch_offsets[i + 2] - batch_offsets[i + 1]);
       if (Bn <= 0 || Bn > kBT) { Xn = nullptr; Bn = 0; }
     }
     const uint32_t seq = seq0 + (uint32_t)i + 1;
-    const uint8_t* m1 = drop_masks ? drop_masks[0] + (size_t)r0 * n1 : nullptr;
-    int rc = sn_shard_forward(shard, X, n, 1, m1, seed, offset + (uint64_t)i, H1, n1, stream);
-    if (rc) return rc;
+    const uint8_t* m1 = drop_masks ? drop_masks[0] + (size_t)b0 * n1 : nullptr;
+    int rc = 0;
+    if (shard) {
+      rc = sn_shard_forward(shard, X, n, 1, m1, seed, offset + (uint64_t)i, H1, n1, stream);
+      if (rc) return rc;
+    }
     if (rank != 0) {
       rc = sn_flag_signal(flags + 128 * rank, seq, nullptr, nullptr, 0, stream);
       if (rc) return rc;
@@ -1733,23 +1792,32 @@ int sn_tp_server_epoch(sn_shard* shard, sn_bob* head, int rank, int world, const
         if (rc) return rc;
       }
       if (drop_masks)
-        for (int l = 0; l < nm; ++l) hm[l] = drop_masks[l + 1] + (size_t)r0 * head->dims[l + 1];
+        for (int l = 0; l < nm; ++l) hm[l] = drop_masks[l + 1] + (size_t)b0 * head->dims[l + 1];
       head->pf_valid = false;
       // the head's cut-gradient reduction pushes every rank's column range into that rank's own
-      // memory (reading it from here over NVLink made the remote traversals 19 us slower)
+      // memory (reading it from here over NVLink made the remote traversals 19 us slower), and
+      // it does so BEFORE the head's own first-layer update (bob_backward_impl, after_cut)
       head->cut_table = world > 1 ? dH1_table_dev : nullptr;
-      head->cut_cols = ceil_div(n1, world);
-      rc = bob_train_step_impl(head, 0, H1, labels + r0 * head->heads, n, drop_masks ? hm.data() : nullptr, seed + 1,
+      head->cut_first = r0;
+      head->cut_cols = world > 1 ? ceil_div(n1 - r0, world - 1) : n1;
+      if (world > 1 && !getenv("SN_TP_LATE_CUT"))
+        head->after_cut = [&](cudaStream_t) { return sn_flag_signal_many(dh_flag_table_dev, world - 1, seq, stream); };
+      rc = bob_train_step_impl(head, 0, H1, labels + b0 * head->heads, n, drop_masks ? hm.data() : nullptr, seed + 1,
                                offset + (uint64_t)i, dH1, nullptr, loss_per_step ? loss_per_step + i : nullptr, st, nullptr, 0);
+      const bool early = (bool)head->after_cut;
+      head->after_cut = nullptr;
       head->cut_table = nullptr;
+      head->cut_first = -1;
       if (rc) return rc;
-      if (world > 1) {
+      if (world > 1 && !early) {
         rc = sn_flag_signal_many(dh_flag_table_dev, world - 1, seq, stream);
         if (rc) return rc;
       }
     }
-    rc = sn_shard_backward_update(shard, X, dH1, n1, n, Xn, Bn, stream);
-    if (rc) return rc;
+    if (shard) {
+      rc = sn_shard_backward_update(shard, X, dH1, n1, n, Xn, Bn, stream);
+      if (rc) return rc;
+    }
   }
   return 0;
 }

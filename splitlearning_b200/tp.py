@@ -10,14 +10,14 @@ over the G ranks - each GPU streams 1/G of W1 and of its optimizer state - while
     previous traversal already multiplied this batch
     out) -> stores H1[:, rows_r] straight into the
     head's mailbox over NVLink; signal h_ready[r]
-                                                          wait for all h_ready; ordinary 2-layer Bob step
-                                                          on H1 (fc2, fc3, CE, backward, Adam); its cut
-                                                          gradient dH1 is pushed, column range by column
-                                                          range, into each rank's own mailbox, and each
-                                                          rank's dh_ready flag is set
-    wait dh_ready (own memory); slice backward: gates
-    dH1[:, rows_r] with its own activation, dW + Adam in
-    one traversal, fused with the next batch's forward
+                                                          wait for all h_ready; 2-layer Bob step on H1:
+                                                          fc2, fc3, CE, fc3 backward, then a READ-ONLY pass
+                                                          over fc2 forms dH1, which is pushed, column range
+                                                          by column range, into each rank's own mailbox,
+                                                          and each rank's dh_ready flag is set ...
+    wait dh_ready (own memory); slice backward: gates     ... and only then fc2's own dW + Adam traversal,
+    dH1[:, rows_r] with its own activation, dW + Adam in  overlapping the shards' (rank 0 therefore holds
+    one traversal, fused with the next batch's forward    fewer fc1 rows than the others: `row_split`)
 
 The cached activations are replicated on every rank (1.2 GB); labels live on the head.  The dropout
 decision of every element is that of the unsharded layer (global element index), so the sharded run
@@ -38,10 +38,31 @@ from .peer import _Raw, _View
 D0 = 5408
 
 
+def row_split(n1, K, head_first_layer_elems, world, min_rows=64):
+    """Row ranges [bounds[r], bounds[r+1]) of the sharded first layer.  Rank 0 also runs the head, whose
+    own first-layer update traversal (fc2: as many bytes as `head_first_layer_elems / K` rows of fc1)
+    starts when the shards start theirs, so rank 0 gets that many rows FEWER than the others - none at
+    all when its fair share would be tiny (8 GPUs: rank 0 is the head only, the other seven hold 5000/7
+    rows each).  Ranks 1.. take equal ranges."""
+    if world == 1:
+        return [0, n1]
+    head_rows = head_first_layer_elems / float(K)
+    other = (n1 + head_rows) / world
+    r0 = int(other - head_rows) // 8 * 8
+    if r0 < min_rows:
+        r0 = 0
+    per = -(-(n1 - r0) // (world - 1))
+    bounds = [0, r0]
+    for r in range(1, world):
+        bounds.append(min(n1, r0 + r * per))
+    return bounds
+
+
 class TPServer:
     """Collective object: construct on every rank with the SAME full weights (e.g. a model built
     under the same seed, or broadcast from rank 0).  `weights`/`biases`: fc1, fc2, fc3 tensors on this
-    rank's device; rank r trains rows [r*n1/G, (r+1)*n1/G) of fc1 in place, rank 0 also fc2, fc3."""
+    rank's device; rank r trains rows [bounds[r], bounds[r+1]) of fc1 in place (`row_split`: rank 0's
+    range is shorter, or empty, because it also trains fc2 and fc3)."""
 
     def __init__(self, rank, world, device, weights, biases, B=16, lr=1e-3, weight_decay=1e-5, dropout_p=0.5,
                  optimizer=E.SN_OPT_ADAM, momentum=0.0):
@@ -50,11 +71,13 @@ class TPServer:
         W1, b1 = weights[0], biases[0]
         n1, K = W1.shape
         self.n1 = n1
-        per = (n1 + world - 1) // world
-        self.lo, self.hi = min(n1, rank * per), min(n1, (rank + 1) * per)
+        self.bounds = row_split(n1, K, weights[1].shape[0] * weights[1].shape[1], world)
+        self.lo, self.hi = self.bounds[rank], self.bounds[rank + 1]
         kw = dict(optimizer=optimizer, lr=lr, momentum=momentum, weight_decay=weight_decay)
         self.W1s, self.b1s = W1[self.lo:self.hi], b1[self.lo:self.hi]          # contiguous row slices (views)
-        self.shard = E.ShardEngine(self.W1s, self.b1s, n1, self.lo, relu=True, dropout_p=dropout_p, **kw)
+        self.shard = None
+        if self.hi > self.lo:
+            self.shard = E.ShardEngine(self.W1s, self.b1s, n1, self.lo, relu=True, dropout_p=dropout_p, **kw)
         self.head = None
         if rank == 0:
             dims = [n1] + [w.shape[0] for w in weights[1:]]
@@ -119,7 +142,8 @@ class TPServer:
             marr = _lib.ptr_array(keep)
         # the loop itself runs in the library (sn_tp_server_epoch): from Python the six calls per step
         # made rank 0 host-bound (165 us/step at two GPUs)
-        check(self.lib.sn_tp_server_epoch(self.shard.h, self.head.h if self.head is not None else None, self.rank, self.world,
+        check(self.lib.sn_tp_server_epoch(self.shard.h if self.shard is not None else None,
+                                          self.head.h if self.head is not None else None, self.rank, self.world,
                                           _lib.ptr(acts), _lib.ptr(labels) if self.rank == 0 else None, offs, nb, marr,
                                           int(seed), int(self.offset), C.c_void_p(self.head_base + self.off_h),
                                           C.c_void_p(self.base + self.off_dh), C.c_void_p(self.head_base + self.off_flags),
@@ -132,9 +156,8 @@ class TPServer:
         """Collect the trained slices into rank 0's full fc1 tensors (state_dict interchange)."""
         if self.world == 1:
             return
-        per = (self.n1 + self.world - 1) // self.world
         for r in range(1, self.world):
-            lo, hi = min(self.n1, r * per), min(self.n1, (r + 1) * per)
+            lo, hi = self.bounds[r], self.bounds[r + 1]
             if self.rank == r:
                 dist.send(self.W1s.contiguous(), dst=0)
                 dist.send(self.b1s.contiguous(), dst=0)
@@ -146,7 +169,8 @@ class TPServer:
         torch.cuda.synchronize(self.device)
         if self.world > 1:
             dist.barrier()
-        self.shard.close()
+        if self.shard is not None:
+            self.shard.close()
         if self.head is not None:
             self.head.close()
         with torch.cuda.device(self.device):

@@ -172,6 +172,36 @@ def test_vanilla_step_vs_oracle_and_golden(eng, B):
         assert rel_err(p.cpu().numpy() - p0, p_ref.numpy() - p0) <= 2e-3, n
 
 
+@pytest.mark.parametrize("B", [16, 9])
+def test_single_call_vanilla_step_equals_the_three_calls(eng, B):
+    """sn_vanilla_step (one call: Alice forward, Bob's train step, Alice backward) lets the conv backward
+    add the server's input-gradient partials itself instead of reading a reduced cut gradient.  Same
+    sums in the same order: after three steps every weight on both sides must EQUAL the three-call form."""
+    a0, b0 = seeded_weights(A_SHAPES, 11), seeded_weights(B_SHAPES, 12)
+    kw = dict(optimizer=eng.SN_OPT_SGD_MOMENTUM, lr=1e-3, momentum=0.9)
+    finals = []
+    for single in (False, True):
+        gw, gb = cu(a0[0]), cu(a0[1])
+        bob, gp = _bob(eng, T(b0), **kw)
+        alice = eng.AliceEngine(gw, gb, **kw)
+        act, cut, loss = torch.empty(B, 5408, device="cuda"), torch.empty(B, 5408, device="cuda"), torch.zeros((), device="cuda")
+        losses = []
+        for step in range(3):
+            x, y = seeded_batch(B, 100 + step)
+            xg, yg = cu(x), cu(y)
+            if single:
+                eng.vanilla_step(alice, bob, xg, yg, 0, 5, step + 1, act, cut, loss)
+            else:
+                alice.forward(xg, out=act)
+                bob.train_step(act, yg, slot=0, masks=None, seed=5, offset=step + 1, loss_out=loss, cut_out=cut)
+                alice.backward_update(xg, cut)
+            losses.append(loss.clone())
+        torch.cuda.synchronize()
+        finals.append([gw.clone(), gb.clone()] + [p.clone() for p in gp] + losses)
+    for u, v in zip(*finals):
+        assert torch.equal(u, v)
+
+
 @pytest.mark.parametrize("opt", ["sgd", "adam"])
 def test_persistent_tail_kernel_is_bit_identical_to_the_launch_chain(eng, opt):
     """sn_set_persistent_tail(1): the middle of the step (fc1 epilogue .. fc2 backward) runs as one

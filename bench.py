@@ -307,6 +307,10 @@ def run_ours_single(args):
     from splitlearning_b200 import spmd
     sisa_concat = spmd.bench_sisa_concat(0, 1, dev, B, peak)
 
+    # ---- BASELINE.json configs[4]: a few representative points of the batch x width sweep (the full
+    # sweep is profiles/sweep.py -> profiles/r2_sweep.jsonl).  Reference precision unless marked.
+    sweep = run_sweep_points(torch)
+
     # ---- CPU baseline on the host cores (bounded sample)
     cpu, sisa_cpu = cpu_baselines()
     sisa.update(sisa_cpu)
@@ -318,9 +322,24 @@ def run_ours_single(args):
         "clocks": clk.summary(), "gpu_launches": int(launches),
         "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "h2d_bytes_per_step": B * 784 * 4 + B * 8,
                 "d2h_bytes_per_step": 4, "ms_per_step": round(e2e_ms / K, 5)},
-        "roofline": roofline, "cpu_baseline": cpu, "sisa": sisa, "sisa_concat": sisa_concat, "final_loss": final_loss,
+        "roofline": roofline, "cpu_baseline": cpu, "sisa": sisa, "sisa_concat": sisa_concat, "sweep": sweep, "final_loss": final_loss,
     }
     print(json.dumps(line))
+
+
+def run_sweep_points(torch):
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("sn_sweep", os.path.join(ROOT, "profiles", "sweep.py"))
+    sw = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(sw)
+    out = []
+    for (b, h, mode) in [(16, 8192, 0), (64, 8192, 0), (256, 8192, 0), (4096, 4096, 0), (4096, 4096, 1)]:
+        try:
+            out.append(sw.point_record(b, h, mode, steps=8))
+        except Exception as e:
+            out.append({"B": b, "H": h, "mode": mode, "error": f"{type(e).__name__}: {e}"[:200]})
+        torch.cuda.empty_cache()
+    return out
 
 
 def cpu_baselines():

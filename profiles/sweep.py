@@ -1,11 +1,17 @@
 """BASELINE.json config 5: synthetic scaling sweep of Bob's training step (forward, CE, backward,
-optimizer) over batch and hidden width, Bob dims [5408, H, H/5 (rounded to 4), 100], on one B200.
-fp32 mode for every batch (parity path), TF32 tcgen05 mode for B >= 128.  Prints one JSON line per
-point with time per step, samples/s, model TFLOP/s (6*P_w*B) and the fraction of the
-relevant roofline: HBM (16*P bytes per step, SGD) for the weight-streaming regime, TF32 tensor
-peak (measured bf16 peak / 2) for the tensor regime.
+optimizer) over batch and hidden width, Bob dims [5408, H, H/5 (rounded to 4), 100].
 
-    python profiles/sweep.py [--quick] > profiles/r1_sweep.jsonl
+One GPU:   python profiles/sweep.py [--quick] > profiles/r2_sweep.jsonl
+    Every batch size is run at REFERENCE PRECISION - the credited column ("credited": true): the fp32
+    weight-stream kernels up to 64 rows, 3xTF32 on tcgen05 above (fp32-accurate, inside the 1e-4
+    parity bound).  Batches >= 128 are also run in one-pass TF32 ("credited": false: 5e-4 on the
+    logits, outside the bound; shown as the tensor-pipe ceiling only).
+    Per point: time per step, samples/s, model TFLOP/s (6*P_w*B) and the fraction of the
+    relevant roofline: HBM (16*P bytes per step, SGD) for the weight-streaming regime, TF32 tensor
+    peak (measured bf16 peak / 2) for the tensor regime.
+world_size axis (2/4/8 GPUs; the only part of the step that shards is the SISA server step, B = 16):
+    python -m torch.distributed.run --nproc-per-node G ... profiles/sweep.py --tp >> profiles/r2_sweep_tp.jsonl
+    runs tp.TPServer (first layer's rows split over the ranks) for H in 2048/4096/8192.
 """
 import json
 import os
@@ -62,7 +68,7 @@ def main():
     Bs = [16, 64, 256, 1024, 4096] if quick else [16, 64, 256, 1024, 4096, 16384, 65536]
     for H in Hs:
         for B in Bs:
-            for mode in ([0] if B < 128 else [1]):
+            for mode in ([0] if B < 128 else [0, 1]):
                 if B * max(H, 5408) * 4 > 6e9:
                     continue
                 steps = max(2, min(50, int(2e11 / (6.0 * 5408 * H * B + 1e9))))
@@ -74,7 +80,8 @@ def main():
                 flops = 6.0 * pw * B
                 tfl = flops / (ms * 1e-3) / 1e12
                 gbs = 16.0 * pw / (ms * 1e-3) / 1e9
-                print(json.dumps({"B": B, "H": H, "dims": dims, "precision": "tf32-tcgen05" if mode else "fp32",
+                prec = "tf32-tcgen05" if mode else ("fp32" if B <= 64 else "3xtf32-tcgen05")
+                print(json.dumps({"B": B, "H": H, "dims": dims, "precision": prec, "credited": mode == 0,
                                   "ms_per_step": round(ms, 4), "samples_per_s": round(B / (ms * 1e-3), 1),
                                   "tflops": round(tfl, 2), "frac_tf32_peak": round(tfl / tf32_peak, 4),
                                   "weight_stream_gbs": round(gbs, 1), "frac_hbm": round(gbs / hbm, 4),
@@ -82,5 +89,64 @@ def main():
                 torch.cuda.empty_cache()
 
 
+def point_record(B, H, mode, steps=None):
+    """One sweep point as a dict (bench.py's `sweep` extra uses this)."""
+    hbm, tf32_peak, src = peaks()
+    steps = steps or max(2, min(50, int(2e11 / (6.0 * 5408 * H * B + 1e9))))
+    dims, pw, ms, loss = run_point(B, H, mode, steps)
+    tfl = 6.0 * pw * B / (ms * 1e-3) / 1e12
+    gbs = 16.0 * pw / (ms * 1e-3) / 1e9
+    return {"B": B, "H": H, "precision": "tf32-tcgen05" if mode else ("fp32" if B <= 64 else "3xtf32-tcgen05"),
+            "credited": mode == 0, "ms_per_step": round(ms, 4), "samples_per_s": round(B / (ms * 1e-3), 1),
+            "tflops": round(tfl, 2), "frac_tf32_peak": round(tfl / tf32_peak, 4), "frac_hbm": round(gbs / hbm, 4)}
+
+
+def main_tp():
+    """world_size axis: SISA server steps (B = 16, Adam) with the first layer sharded over the ranks."""
+    import torch.distributed as dist
+    from splitlearning_b200 import tp
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank)))
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    hbm, _, src = peaks()
+    B, nbat = 16, 400
+    for H in (2048, 4096, 8192):
+        dims = [5408, H, max(4, (H // 5) // 4 * 4), 100]
+        g = torch.Generator(device="cpu").manual_seed(H)
+        Ws = [(torch.randn(dims[i + 1], dims[i], generator=g) / dims[i] ** 0.5).to(dev) for i in range(3)]
+        bs = [torch.zeros(dims[i + 1], device=dev) for i in range(3)]
+        acts = ((torch.rand(nbat * B, 5408, generator=g) * 100) * (torch.rand(nbat * B, 5408, generator=g) < 0.6)).to(dev)
+        labels = torch.randint(0, 10, (nbat * B,), generator=g).to(dev)
+        offs = list(range(0, nbat * B + 1, B))
+        srv = tp.TPServer(rank, world, dev, Ws, bs, B=B, lr=1e-4, weight_decay=1e-5, dropout_p=0.5)
+        srv.server_epoch(acts, labels, offs[:41])
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        srv.server_epoch(acts, labels, offs)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        us = 1e3 * float(t.item()) / nbat
+        pw = sum(dims[i] * dims[i + 1] for i in range(3))
+        if rank == 0:
+            print(json.dumps({"B": B, "H": H, "dims": dims, "world_size": world, "precision": "fp32", "credited": True,
+                              "workload": "SISA server step, Adam, first layer's rows split over the ranks",
+                              "us_per_step": round(us, 2), "samples_per_s": round(B / (us * 1e-6), 1),
+                              "aggregate_weight_stream_gbs": round(24.0 * pw / (us * 1e-6) / 1e9, 1),
+                              "frac_hbm_one_gpu": round(24.0 * pw / (us * 1e-6) / 1e9 / hbm, 4), "peaks": src}), flush=True)
+        srv.close()
+        del Ws, bs, acts
+        torch.cuda.empty_cache()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
 if __name__ == "__main__":
-    main()
+    if "--tp" in sys.argv:
+        main_tp()
+    else:
+        main()

@@ -304,7 +304,40 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(r[j]);     // lane holds row q*32+lane
       __syncwarp();
       const int n = n0 + c0 + lane;                                                // now lane = column
-      if (n < N) {
+      if (EPI == EPI_UPDATE) {
+        // dW + optimizer: the tile's weights and optimizer state are a pure read-modify-write stream
+        // (16-24 bytes per element against 2*B flops), so what matters is bytes in flight.  All 32 rows'
+        // loads of a chunk are issued before the first update (the row-at-a-time form kept ~5 KB in
+        // flight per SM and ran the batch-256 step 17x off its HBM floor).
+        if (n < N) {
+          constexpr int RB = 16;                                   // rows per batch of loads
+          const int rows = min(32, M - (m0 + q * 32));
+#pragma unroll 1
+          for (int r0 = 0; r0 < 32; r0 += RB) {
+            float pv[RB], av[RB], bv[OPT == 2 ? RB : 1];
+            float* cp = C + (size_t)(m0 + q * 32 + r0) * ldc + n;
+            float* s1p = ep.s1 + (size_t)(m0 + q * 32 + r0) * ldc + n;
+            float* s2p = (OPT == 2) ? ep.s2 + (size_t)(m0 + q * 32 + r0) * ldc + n : nullptr;
+#pragma unroll
+            for (int rr = 0; rr < RB; ++rr) {
+              const bool ok = r0 + rr < rows;
+              pv[rr] = ok ? cp[(size_t)rr * ldc] : 0.f;
+              av[rr] = ok ? s1p[(size_t)rr * ldc] : 0.f;
+              if (OPT == 2) bv[OPT == 2 ? rr : 0] = ok ? s2p[(size_t)rr * ldc] : 0.f;
+            }
+#pragma unroll
+            for (int rr = 0; rr < RB; ++rr) {
+              if (r0 + rr < rows) {
+                float b2 = (OPT == 2) ? bv[OPT == 2 ? rr : 0] : 0.f;
+                opt_update<OPT>(ep.op, pv[rr], tile[(r0 + rr) * 33 + lane], av[rr], b2);
+                cp[(size_t)rr * ldc] = pv[rr];
+                s1p[(size_t)rr * ldc] = av[rr];
+                if (OPT == 2) s2p[(size_t)rr * ldc] = b2;
+              }
+            }
+          }
+        }
+      } else if (n < N) {
         const float bias_v = (EPI == EPI_FWD && ep.bias) ? ep.bias[n] : 0.f;
 #pragma unroll 4
         for (int rr = 0; rr < 32; ++rr) {

@@ -55,6 +55,13 @@ static int fwd_rows() {
   return r;
 }
 
+// largest batch whose backward still goes through the fp32 traversal in tiles of 16 rows with a
+// gradient buffer (above it: tcgen05 GEMMs); SN_BWD_TILED_MAX overrides, for the config-5 sweep
+static int bwd_tiled_max() {
+  static const int v = getenv("SN_BWD_TILED_MAX") ? atoi(getenv("SN_BWD_TILED_MAX")) : kSkinnyFwdMaxB;
+  return std::min(v, kSkinnyFwdMaxB);
+}
+
 static FwdPlan plan_fwd(int K, int N, int sms) {
   // k-chunks of whole 128-float slices, as equal as possible; CTAs per chunk capped so that a
   // warp's tile range is at least one row group long (=> at most two partials per group)
@@ -1027,7 +1034,7 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         SN_LAUNCH_CHECK();
         mark_written(h->W[l], wbytes);
       }
-    } else if (B <= kSkinnyFwdMaxB && (K % 4) == 0 && g_matmul_precision.load() != 2) {
+    } else if (B <= bwd_tiled_max() && (K % 4) == 0 && g_matmul_precision.load() != 2) {
       // 17..64 rows (--batch_size 32/64): still a weight stream, far below the tensor ridge.  The
       // batch goes through the same fp32 traversal in tiles of 16 rows: each tile's launch forms its
       // dA rows and ADDS its dW into a gradient buffer (OPT=3); one elementwise pass then applies
@@ -1494,7 +1501,11 @@ int sn_vanilla_step(sn_alice* alice, sn_bob* bob, int slot, const float* x, cons
   // Both halves of the step are in this one call, so the cut-layer gradient need not be materialised:
   // Bob's first-layer backward leaves its n-split partial sums and Alice's conv backward adds them
   // while it loads them (one reduction launch less; cut_grad stays untouched then).
-  static const bool fold = getenv("SN_NO_CUT_FOLD") == nullptr;
+  // MEASURED SLOWER on B200 (conv backward 5.7 -> 12.7 us against the 4.5 us launch it saves: the three
+  // partial loads per value sit in front of the kernel's only long dependency chain), so it is off
+  // unless SN_CUT_FOLD=1; the results are bit-identical either way (tests/test_gpu_kernels.py).
+  const char* fold_env = getenv("SN_CUT_FOLD");
+  const bool fold = fold_env && atoi(fold_env) != 0;
   bob->defer_cut = fold && B <= kBT;
   bob->deferred_nsplit = 0;
   rc = sn_bob_train_step(bob, slot, act, labels, B, nullptr, seed, offset, cut_grad, nullptr, loss_out, stream);

@@ -38,19 +38,24 @@ from .peer import _Raw, _View
 D0 = 5408
 
 
-def row_split(n1, K, head_first_layer_elems, world, min_rows=64):
-    """Row ranges [bounds[r], bounds[r+1]) of the sharded first layer.  Rank 0 also runs the head, whose
-    own first-layer update traversal (fc2: as many bytes as `head_first_layer_elems / K` rows of fc1)
-    starts when the shards start theirs, so rank 0 gets that many rows FEWER than the others - none at
-    all when its fair share would be tiny (8 GPUs: rank 0 is the head only, the other seven hold 5000/7
-    rows each).  Ranks 1.. take equal ranges."""
+def row_split(n1, K, head_first_layer_elems, world, head_rows=None, min_rows=64):
+    """Row ranges [bounds[r], bounds[r+1]) of the sharded first layer: rank 0 holds `head_rows` rows
+    fewer than the others (none at all when that leaves it under `min_rows`), ranks 1.. equal ranges.
+    Default head_rows = 0, an even split.  Rank 0 also runs the head, whose own update traversal (fc2:
+    as many bytes as head_first_layer_elems / K rows of fc1) overlaps the shards' since the cut gradient
+    goes out first - but the other ranks pay about the same again in NVLink stores, flag launches and
+    flag latency before the head can start (profiles/r2h_tp_trace_2gpu.txt: rank 0 18 us of fc2 update
+    against 8 + 6 + ~6 us on rank 1), so taking rows away from rank 0 made the 2-GPU epoch SLOWER
+    (505 -> 532 ms with the late hand-out, and no better with the early one)."""
     if world == 1:
         return [0, n1]
-    head_rows = head_first_layer_elems / float(K)
+    if head_rows is None:
+        head_rows = 0.0
     other = (n1 + head_rows) / world
-    r0 = int(other - head_rows) // 8 * 8
+    r0 = (int(other - head_rows) + 7) // 8 * 8
     if r0 < min_rows:
         r0 = 0
+    r0 = min(r0, n1)
     per = -(-(n1 - r0) // (world - 1))
     bounds = [0, r0]
     for r in range(1, world):

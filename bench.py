@@ -379,18 +379,18 @@ def cpu_baselines():
 def ncu_traffic(kernel_key):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel_key` from the committed ncu
     capture (profiles/ncu_traffic.json, written by profiles/summarize.py from an `ncu --set full`
-    run), or None when the kernel sources have changed since that capture."""
+    run), or None when that kernel's source files have changed since the capture."""
     import hashlib
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            tab = json.load(f)
+            ent = json.load(f)["kernels"][kernel_key]
         h = hashlib.sha256()
-        for name in tab["sources"]:
+        for name in ent["sources"]:
             with open(os.path.join(ROOT, name), "rb") as f:
                 h.update(f.read())
-        if h.hexdigest()[:16] != tab["source_sha16"]:
+        if h.hexdigest()[:16] != ent["source_sha16"]:
             return None
-        return float(tab["kernels"][kernel_key]["dram_bytes_per_launch"])
+        return float(ent["dram_bytes_per_launch"])
     except Exception:
         return None
 

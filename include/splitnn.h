@@ -267,9 +267,7 @@ int sn_alice_local_epoch(sn_alice* h, const float* x, const int64_t* labels, int
 
 /* One whole vanilla split step on one device in one call: sn_alice_forward -> sn_bob_train_step
  * (Philox dropout) -> sn_alice_backward_update, i.e. the body of alice.train's batch loop,
- * data_entities_vanilla.py:70-76.  act and cut_grad are caller scratch [B,5408]; with SN_CUT_FOLD=1 in
- * the environment cut_grad is left unwritten (the conv backward then adds the server's partial sums
- * itself; same bits, measured slower, off by default). */
+ * data_entities_vanilla.py:70-76.  act and cut_grad are caller scratch [B,5408]. */
 int sn_vanilla_step(sn_alice* alice, sn_bob* bob, int slot, const float* x, const int64_t* labels,
                     int B, uint64_t seed, uint64_t offset, float* act, float* cut_grad,
                     float* loss_out, void* stream);

@@ -1,6 +1,6 @@
 """Turn gpurun_out ncu artefacts into the small tracked summaries under profiles/.
 usage: python profiles/summarize.py launches <launches.csv> | full <report.ncu-rep> | fullcsv <raw.csv>... |
-       traffic <out.json> key=<raw.csv>:<kernel substring>[:grid] ..."""
+       traffic <out.json> key=<family>:<raw.csv>:<kernel substring>[:grid] ..."""
 import collections
 import csv
 import re
@@ -47,8 +47,6 @@ def full(path):
 
 EXTRA = ["sm__inst_executed_pipe_fma.sum", "sm__inst_executed_pipe_lsu.sum", "sm__inst_executed_pipe_alu.sum",
          "sm__inst_executed_pipe_xu.sum", "sm__inst_executed.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum"]
-SOURCES = ["splitlearning_b200/csrc/mlp_kernels.cuh", "splitlearning_b200/csrc/alice_kernels.cuh",
-           "splitlearning_b200/csrc/gemm_tc.cuh", "splitlearning_b200/csrc/tail_kernel.cuh", "splitlearning_b200/csrc/common.cuh"]
 
 
 _SCALE = {"ns": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3, "s": 1e6, "second": 1e6,
@@ -90,22 +88,33 @@ def fullcsv(*paths):
             w.writerow([tag] + [re.sub(r"\(.*", "", r[h.index(k)])[:80] if k == "Kernel Name" else r[h.index(k)] for k in cols])
 
 
-def traffic(out_json, *specs):
-    """specs: key=csvpath:kernel-substring[:grid] ...  Writes the per-launch DRAM bytes of each named
-    kernel together with a hash of the kernel sources, so that bench.py can tell a stale figure."""
+def _src_hash(root, names):
     import hashlib
+    import os
+    hsh = hashlib.sha256()
+    for name in names:
+        with open(os.path.join(root, name), "rb") as f:
+            hsh.update(f.read())
+    return hsh.hexdigest()[:16]
+
+
+KERNEL_SOURCES = {"mlp": ["splitlearning_b200/csrc/mlp_kernels.cuh", "splitlearning_b200/csrc/common.cuh"],
+                  "alice": ["splitlearning_b200/csrc/alice_kernels.cuh", "splitlearning_b200/csrc/common.cuh"],
+                  "tc": ["splitlearning_b200/csrc/gemm_tc.cuh", "splitlearning_b200/csrc/common.cuh"]}
+
+
+def traffic(out_json, *specs):
+    """specs: key=family:csvpath:kernel-substring[:grid] ... (family = mlp | alice | tc: which source
+    files the kernel lives in).  Writes the per-launch DRAM bytes of each named kernel together with a
+    hash of those sources, so that bench.py can tell a stale figure (and then reports null)."""
     import json
     import os
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    hsh = hashlib.sha256()
-    for name in SOURCES:
-        with open(os.path.join(root, name), "rb") as f:
-            hsh.update(f.read())
-    table = {"sources": SOURCES, "source_sha16": hsh.hexdigest()[:16], "kernels": {}}
+    table = {"kernels": {}}
     for spec in specs:
         key, rest = spec.split("=", 1)
         parts = rest.split(":")
-        path, sub, grid = parts[0], parts[1], (parts[2] if len(parts) > 2 else None)
+        fam, path, sub, grid = parts[0], parts[1], parts[2], (parts[3] if len(parts) > 3 else None)
         h, data = _rows(path)
         hit = [r for r in data if sub in r[h.index("Kernel Name")] and (grid is None or r[h.index("launch__grid_size")] == grid)]
         if not hit:
@@ -115,7 +124,8 @@ def traffic(out_json, *specs):
         wr = float(r[h.index("dram__bytes_write.sum")]) * 1e6
         table["kernels"][key] = {"kernel": re.sub(r"\(.*", "", r[h.index("Kernel Name")]), "grid": r[h.index("launch__grid_size")],
                                  "dram_bytes_read": rd, "dram_bytes_write": wr, "dram_bytes_per_launch": rd + wr,
-                                 "us": float(r[h.index("gpu__time_duration.sum")]), "capture": os.path.basename(path)}
+                                 "us": float(r[h.index("gpu__time_duration.sum")]), "capture": os.path.basename(path),
+                                 "sources": KERNEL_SOURCES[fam], "source_sha16": _src_hash(root, KERNEL_SOURCES[fam])}
     with open(out_json, "w") as f:
         json.dump(table, f, indent=1)
     print("wrote", out_json)

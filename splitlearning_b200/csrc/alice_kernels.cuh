@@ -182,10 +182,10 @@ __global__ void __launch_bounds__(256) conv_pool_bwd_kernel(const float* __restr
                                                             float* __restrict__ partial, unsigned* __restrict__ ticket,
                                                             float* __restrict__ dw_out, float* __restrict__ db_out,
                                                             float* __restrict__ s1, float* __restrict__ s2,
-                                                            OptParams op, int prefetch_early, int nsplit, size_t pstride) {
-  // nsplit > 1: `dact` is not the cut-layer gradient itself but the server's first-layer backward's
-  // n-split partial sums [nsplit][..pstride floats..]: they are added here (same fixed order as
-  // bwd_epilogue_kernel, so the same bits) and the separate reduction launch is saved.
+                                                            OptParams op, int prefetch_early) {
+  // (Letting this kernel add the server's n-split input-gradient partials itself - one launch less in
+  // sn_vanilla_step - was built, bit-identical, and measured SLOWER: 5.7 -> 12.7 us here against the
+  // 4.5 us reduction launch it saved.  Removed.)
   __shared__ float img[28 * 28];
   __shared__ unsigned is_last;
   const int cg = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -217,16 +217,7 @@ __global__ void __launch_bounds__(256) conv_pool_bwd_kernel(const float* __restr
 #pragma unroll
     for (int q = 0; q < 6; ++q) {
       const int p = lane + 32 * q;
-      float v = 0.f;
-      if (p < kPooled) {
-        const float* src = dact + (size_t)b * kD0 + (size_t)c * kPooled + p;
-        v = __ldg(src);
-        if (nsplit > 1) {
-          v = 0.f + v;
-          for (int sp = 1; sp < nsplit; ++sp) v += __ldg(src + (size_t)sp * pstride);
-        }
-      }
-      dv[q] = v;
+      dv[q] = p < kPooled ? __ldg(dact + (size_t)b * kD0 + (size_t)c * kPooled + p) : 0.f;
     }
     if (b != blockIdx.x) {
       __syncthreads();

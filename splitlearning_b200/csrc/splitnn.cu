@@ -423,8 +423,6 @@ struct sn_bob {
   unsigned* ticket = nullptr;
   float* const* cut_table = nullptr;   // tensor-parallel head: per-consumer destinations of the cut gradient's columns
   int cut_cols = 1;
-  bool defer_cut = false;              // sn_vanilla_step: leave the cut gradient as n-split partials in PA ...
-  int deferred_nsplit = 0;             // ... (this many) for the conv backward kernel to add up itself
   int cut_first = -1;                  // >= 0: consumer 0 owns this many leading columns, the others cut_cols each
   // tensor-parallel head: produce and hand out the cut gradient BEFORE the first layer's update
   // traversal (a read-only pass over its weights), then call this (the flag release), then update
@@ -553,7 +551,7 @@ int sn_conv_pool_backward(const float* x, const float* w, const float* b, const 
   SN_CUDA(cudaMemsetAsync(ticket, 0, 256, st));
   OptParams op{};
   launch_k(conv_pool_bwd_kernel<0>, dim3(gx, 4), dim3(256), 0, st, x, const_cast<float*>(w), const_cast<float*>(b), dact, B,
-                                                      partial, ticket, dw, db, nullptr, nullptr, op, 0, 1, (size_t)0);
+                                                      partial, ticket, dw, db, nullptr, nullptr, op, 0);
   SN_LAUNCH_CHECK();
   return 0;
 }
@@ -990,12 +988,6 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
                                                               h->l2_keep[l], (const float*)nullptr, 1.f);
         Profiler::end(pe, st);
         SN_LAUNCH_CHECK();
-        if (l == 0 && h->defer_cut && K == kD0 && !h->cut_table) {
-          // the consumer (Alice's conv backward, next in the same call) adds the partials itself
-          h->deferred_nsplit = p.nsplit;
-          mark_written(h->W[l], wbytes);
-          continue;
-        }
         launch_k(bwd_epilogue_kernel, dim3(ew_grid((size_t)B * K, h->sms)), dim3(256), 0, st, h->PA, p.nsplit, B, K, gateH, K,
                  gscale, dst, K, l == 0 ? h->cut_table : (float* const*)nullptr, h->cut_cols, h->cut_first);
         SN_LAUNCH_CHECK();
@@ -1432,8 +1424,7 @@ int sn_alice_forward_ld(sn_alice* h, const float* x, int B, float* act, size_t l
   return launch_conv_fwd(x, h->w, h->b, B, act, ld_act, h->sms, (cudaStream_t)stream);
 }
 
-static int alice_bwd(sn_alice* h, const float* x, const float* dact, int B, cudaStream_t st, int nsplit = 1,
-                     size_t pstride = 0) {
+static int alice_bwd(sn_alice* h, const float* x, const float* dact, int B, cudaStream_t st) {
   SN_REQUIRE(B <= h->max_batch, "batch larger than max_batch given to sn_alice_create");
   h->step += 1;
   const OptParams op = make_opt(h->hyper, h->step);
@@ -1445,11 +1436,11 @@ static int alice_bwd(sn_alice* h, const float* x, const float* dact, int B, cuda
   switch (h->hyper.type) {
     case SN_OPT_SGD_MOMENTUM:
       launch_k(conv_pool_bwd_kernel<1>, dim3(grid), dim3(256), 0, st, x, h->w, h->b, dact, B, h->partial, h->ticket, nullptr, nullptr,
-                                                   h->s1, h->s2, op, early, nsplit, pstride);
+                                                   h->s1, h->s2, op, early);
       break;
     case SN_OPT_ADAM:
       launch_k(conv_pool_bwd_kernel<2>, dim3(grid), dim3(256), 0, st, x, h->w, h->b, dact, B, h->partial, h->ticket, nullptr, nullptr,
-                                                   h->s1, h->s2, op, early, nsplit, pstride);
+                                                   h->s1, h->s2, op, early);
       break;
     default:
       return fail_msg("libsplitnn: this sn_alice was created without an optimizer");
@@ -1498,23 +1489,8 @@ int sn_vanilla_step(sn_alice* alice, sn_bob* bob, int slot, const float* x, cons
   SN_REQUIRE(alice->device == bob->device, "sn_vanilla_step: Alice and Bob must share a device (use the separate calls across GPUs)");
   int rc = sn_alice_forward(alice, x, B, act, stream);
   if (rc) return rc;
-  // Both halves of the step are in this one call, so the cut-layer gradient need not be materialised:
-  // Bob's first-layer backward leaves its n-split partial sums and Alice's conv backward adds them
-  // while it loads them (one reduction launch less; cut_grad stays untouched then).
-  // MEASURED SLOWER on B200 (conv backward 5.7 -> 12.7 us against the 4.5 us launch it saves: the three
-  // partial loads per value sit in front of the kernel's only long dependency chain), so it is off
-  // unless SN_CUT_FOLD=1; the results are bit-identical either way (tests/test_gpu_kernels.py).
-  const char* fold_env = getenv("SN_CUT_FOLD");
-  const bool fold = fold_env && atoi(fold_env) != 0;
-  bob->defer_cut = fold && B <= kBT;
-  bob->deferred_nsplit = 0;
   rc = sn_bob_train_step(bob, slot, act, labels, B, nullptr, seed, offset, cut_grad, nullptr, loss_out, stream);
-  bob->defer_cut = false;
   if (rc) return rc;
-  if (bob->deferred_nsplit > 0) {
-    SN_ALICE_ENTER(alice);
-    return alice_bwd(alice, x, bob->PA, B, (cudaStream_t)stream, bob->deferred_nsplit, (size_t)kBT * kD0);
-  }
   return sn_alice_backward_update(alice, x, cut_grad, B, stream);
 }
 

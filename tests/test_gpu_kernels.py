@@ -172,13 +172,10 @@ def test_vanilla_step_vs_oracle_and_golden(eng, B):
         assert rel_err(p.cpu().numpy() - p0, p_ref.numpy() - p0) <= 2e-3, n
 
 
-@pytest.mark.parametrize("fold", ["0", "1"])
 @pytest.mark.parametrize("B", [16, 9])
-def test_single_call_vanilla_step_equals_the_three_calls(eng, B, fold, monkeypatch):
-    """sn_vanilla_step (one call: Alice forward, Bob's train step, Alice backward) lets the conv backward
-    add the server's input-gradient partials itself instead of reading a reduced cut gradient.  Same
-    sums in the same order: after three steps every weight on both sides must EQUAL the three-call form."""
-    monkeypatch.setenv("SN_CUT_FOLD", fold)       # 1: the conv backward adds the partial sums (off by default: slower)
+def test_single_call_vanilla_step_equals_the_three_calls(eng, B):
+    """sn_vanilla_step (one call: Alice forward, Bob's train step, Alice backward) against the three
+    separate calls: after three steps every weight on both sides and every loss must be EQUAL."""
     a0, b0 = seeded_weights(A_SHAPES, 11), seeded_weights(B_SHAPES, 12)
     kw = dict(optimizer=eng.SN_OPT_SGD_MOMENTUM, lr=1e-3, momentum=0.9)
     finals = []

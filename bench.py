@@ -225,7 +225,7 @@ def run_ours_single(args):
     # warm-up with a shorter turn, so that the hand-off path (its kernel is loaded lazily on first use)
     # has run before anything is timed
     for i in range(W):
-        step(i, xs[i % nb], ys[i % nb], loss_dev, turn=max(1, min(TURN, W // 2)))
+        step(i, xs[i % nb], ys[i % nb], loss_dev, turn=max(1, min(TURN, W // (N_ALICES + 1))))
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     l0 = lib.sn_launch_count()

@@ -363,9 +363,10 @@ int sn_shard_backward_update(sn_shard* h, const float* X, const float* dH, int l
  * remaining layers, input width = the sharded layer's width) and the labels; rank 0 of a multi-rank
  * run may come WITHOUT a shard (shard = NULL, cache unused: it is then the head only).  Column
  * ownership of H1/dH1: rank 0's shard rows first (possibly none), then equal ranges for ranks 1.. .
- * The head forms its input gradient with a read-only pass over its first layer, pushes every rank's
- * columns into that rank's memory and releases the flags BEFORE its own first-layer update
- * traversal, which then overlaps the shards' traversals.  H1 is the [16, n_total]
+ * The head's backward pushes every rank's columns of the input gradient into that rank's memory and
+ * then releases the flags.  (SN_TP_EARLY_CUT=1: the gradient is formed by a read-only pass and handed
+ * out BEFORE the head's own first-layer update; measured slower from 4 GPUs up, off by default.)
+ * H1 is the [16, n_total]
  * activation buffer in rank 0's mailbox (a peer pointer elsewhere) and h_ready_flags the base of the
  * per-rank flags next to it (rank r's at +128*r bytes); dH1 [16, n_total] and dh_ready_flag are THIS
  * rank's own gradient buffer and flag.  Rank 0 also passes two DEVICE arrays: dH1_table_dev[world]

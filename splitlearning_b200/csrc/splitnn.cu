@@ -1787,7 +1787,13 @@ int sn_tp_server_epoch(sn_shard* shard, sn_bob* head, int rank, int world, const
       head->cut_table = world > 1 ? dH1_table_dev : nullptr;
       head->cut_first = r0;
       head->cut_cols = world > 1 ? ceil_div(n1 - r0, world - 1) : n1;
-      if (world > 1 && !getenv("SN_TP_LATE_CUT"))
+      // SN_TP_EARLY_CUT=1: hand the cut gradient out BEFORE the head's first-layer update (a read-only
+      // pass, then the update on its own).  Measured (profiles/r2h_tp_trace_2gpu.txt, r2i_tp_trace_8gpu.txt):
+      // it takes 6 us off the shards' wait, but the two passes cost 32 us where the fused one costs 21,
+      // and from 4 GPUs up rank 0's own stream is the critical path - 8 GPUs: 106 us/step against 95.
+      // Off by default.
+      static const bool early_cut = getenv("SN_TP_EARLY_CUT") && atoi(getenv("SN_TP_EARLY_CUT")) != 0;
+      if (world > 1 && early_cut)
         head->after_cut = [&](cudaStream_t) { return sn_flag_signal_many(dh_flag_table_dev, world - 1, seq, stream); };
       rc = bob_train_step_impl(head, 0, H1, labels + b0 * head->heads, n, drop_masks ? hm.data() : nullptr, seed + 1,
                                offset + (uint64_t)i, dH1, nullptr, loss_per_step ? loss_per_step + i : nullptr, st, nullptr, 0);

@@ -713,9 +713,10 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # warm-up with a shorter turn: every hand-off route (local copy, NCCL send/recv) has run before the timed steps
-    run_vanilla_schedule(rank, world, bob, mine, lambda i: (xs[i % nb], ys[i % nb]), n_alices, max(1, min(turn, W // 2)), 0, W, B,
-                         device, None, link)
+    # warm-up with the shortest turn that still fits: every Alice (so every rank: kernels are loaded
+    # lazily, per process, on first launch) and every hand-off route has run before the timed steps
+    run_vanilla_schedule(rank, world, bob, mine, lambda i: (xs[i % nb], ys[i % nb]), n_alices,
+                         max(1, min(turn, W // (n_alices + 1))), 0, W, B, device, None, link)
     l0 = lib.sn_launch_count()
     import bench as bench_mod
     with bench_mod.ClockSampler(local) as clk:

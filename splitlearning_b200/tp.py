@@ -10,14 +10,18 @@ over the G ranks - each GPU streams 1/G of W1 and of its optimizer state - while
     previous traversal already multiplied this batch
     out) -> stores H1[:, rows_r] straight into the
     head's mailbox over NVLink; signal h_ready[r]
-                                                          wait for all h_ready; 2-layer Bob step on H1:
-                                                          fc2, fc3, CE, fc3 backward, then a READ-ONLY pass
-                                                          over fc2 forms dH1, which is pushed, column range
-                                                          by column range, into each rank's own mailbox,
-                                                          and each rank's dh_ready flag is set ...
-    wait dh_ready (own memory); slice backward: gates     ... and only then fc2's own dW + Adam traversal,
-    dH1[:, rows_r] with its own activation, dW + Adam in  overlapping the shards' (rank 0 therefore holds
-    one traversal, fused with the next batch's forward    fewer fc1 rows than the others: `row_split`)
+                                                          wait for all h_ready; ordinary 2-layer Bob step
+                                                          on H1 (fc2, fc3, CE, backward, Adam); its cut
+                                                          gradient dH1 is pushed, column range by column
+                                                          range, into each rank's own mailbox, and each
+                                                          rank's dh_ready flag is set
+    wait dh_ready (own memory); slice backward: gates
+    dH1[:, rows_r] with its own activation, dW + Adam in
+    one traversal, fused with the next batch's forward
+
+(SN_TP_EARLY_CUT=1 hands dH1 out before fc2's own update - a read-only pass over fc2, then the update -
+and `row_split(head_rows=...)` can give rank 0 fewer rows, or none: both built and measured, neither a
+win on this box; see `row_split` and profiles/r2h_tp_trace_2gpu.txt, r2i_tp_trace_8gpu.txt.)
 
 The cached activations are replicated on every rank (1.2 GB); labels live on the head.  The dropout
 decision of every element is that of the unsharded layer (global element index), so the sharded run
@@ -66,8 +70,8 @@ def row_split(n1, K, head_first_layer_elems, world, head_rows=None, min_rows=64)
 class TPServer:
     """Collective object: construct on every rank with the SAME full weights (e.g. a model built
     under the same seed, or broadcast from rank 0).  `weights`/`biases`: fc1, fc2, fc3 tensors on this
-    rank's device; rank r trains rows [bounds[r], bounds[r+1]) of fc1 in place (`row_split`: rank 0's
-    range is shorter, or empty, because it also trains fc2 and fc3)."""
+    rank's device; rank r trains rows [bounds[r], bounds[r+1]) of fc1 in place (`row_split`: an even
+    split by default), rank 0 also fc2 and fc3."""
 
     def __init__(self, rank, world, device, weights, biases, B=16, lr=1e-3, weight_decay=1e-5, dropout_p=0.5,
                  optimizer=E.SN_OPT_ADAM, momentum=0.0):

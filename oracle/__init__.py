@@ -17,7 +17,11 @@ torch 2.11.0 CPU is what both this container and the GPU box carry.
   protocol.py   single-process restatement of who-calls-whom (vanilla / U-shape / SISA), with
                 one RNG stream per logical process;
   partition.py  LDA partition + train/test split digests (integer-exact known answers);
-  gen_golden.py run HERE against `/root/reference` to write `tests/golden/*`.
+  gen_golden.py run HERE against `/root/reference` to write `tests/golden/*`;
+  fetch_ref.sh  copies the unmodified reference into oracle/_ref/ (git-ignored; travels to the GPU box);
+  ref_runner.py runs that copy - its alice/bob classes under torch.distributed.rpc, its SISA
+                `bob.train_and_backward` - as the timed CPU baseline (`bench.py --impl reference`);
+  cpu_baseline.py the single-process torch-CPU port, the labelled second figure / fallback.
 
 Parity pinning: the reference has no tests and no golden vectors.  The oracle is
 pinned by fixtures generated from the reference itself in this container (`gen_golden.py`:

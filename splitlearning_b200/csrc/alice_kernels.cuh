@@ -159,6 +159,98 @@ __global__ void __launch_bounds__(kStreamThreads, CTAS_PER_SM) conv_pool_stream_
   asm volatile("cp.async.wait_group 0;\n" ::: "memory");
 }
 
+// The same work with WARP-autonomous images: no CTA-wide barrier in the loop.  In the CTA-per-image
+// form above every image ends at a __syncthreads, all warps of a CTA hit the FP32 pipe in the same
+// phase and then all wait (ncu: `math_pipe_throttle` and `barrier` the two top stalls, FMA pipe 58 %
+// busy = half the FP32 peak, profiles/r2_ffma_rate.txt).  Here each warp stages ITS OWN image into a
+// private double buffer (cp.async, 7 x 16 B per lane), and its lanes walk the 338 (position, channel
+// half) items of that image in 11 rounds; warps drift apart and keep the pipe evenly fed.  Same
+// per-output operand order: bit-identical results.
+constexpr int kStreamWarps = 8;
+constexpr size_t kStreamWarpSmem = (size_t)kStreamWarps * 2 * 784 * 4 + 16 * 10 * 8;
+
+__global__ void __launch_bounds__(32 * kStreamWarps, 2) conv_pool_stream_warp_kernel(const float* __restrict__ x,
+                                                                                     const float* __restrict__ w,
+                                                                                     const float* __restrict__ bias, int B,
+                                                                                     float* __restrict__ act, size_t ld_act) {
+  extern __shared__ __align__(16) unsigned char conv_smem[];
+  float2(*wsm)[10] = reinterpret_cast<float2(*)[10]>(conv_smem);                       // [16][10]
+  float* imgs = reinterpret_cast<float*>(conv_smem + 16 * 10 * 8);                      // [warp][buf][784]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  float* mine = imgs + (size_t)warp * 2 * 784;
+  const int gw = blockIdx.x * kStreamWarps + warp, nw = gridDim.x * kStreamWarps;
+
+  auto stage = [&](int buf, int b) {
+    for (int t = lane; t < 196; t += 32) {
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(mine + buf * 784 + t * 4);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(x + (size_t)b * 784 + t * 4) : "memory");
+    }
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+  };
+  int b = gw;
+  if (b < B) stage(0, b);                              // x is an input: staged before the dependency wait
+  pdl_wait();
+  pdl_launch();
+  for (int t = tid; t < 16 * 10 * 2; t += 32 * kStreamWarps) {
+    const int odd = t & 1, q = (t >> 1) % 10, cp = t / 20;
+    const int c = 2 * cp + odd;
+    reinterpret_cast<float*>(&wsm[cp][q])[odd] = q < 9 ? w[c * 9 + q] : bias[c];
+  }
+  __syncthreads();                                     // the only CTA-wide barrier
+  int buf = 0;
+  for (; b < B; b += nw, buf ^= 1) {
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    __syncwarp();                                      // this image has landed; the other buffer is free
+    if (b + nw < B) stage(buf ^ 1, b + nw);
+    const float* img = mine + buf * 784;
+    float* outb = act + (size_t)b * ld_act;
+#pragma unroll 1
+    for (int item = lane; item < 2 * kPooled; item += 32) {
+      const int half = item >= kPooled, p = item - half * kPooled;
+      const int i = p / 13, j = p - i * 13;
+      float2 pt[4][4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const float2 a0 = *reinterpret_cast<const float2*>(&img[(2 * i + r) * 28 + 2 * j]);
+        const float2 a1 = *reinterpret_cast<const float2*>(&img[(2 * i + r) * 28 + 2 * j + 2]);
+        pt[r][0] = make_float2(a0.x, a0.x);
+        pt[r][1] = make_float2(a0.y, a0.y);
+        pt[r][2] = make_float2(a1.x, a1.x);
+        pt[r][3] = make_float2(a1.y, a1.y);
+      }
+      float* out = outb + p;
+#pragma unroll 2
+      for (int cc = 0; cc < 8; ++cc) {
+        const int cp = half * 8 + cc;
+        const float4* wq = reinterpret_cast<const float4*>(&wsm[cp][0]);
+        float2 wv[10];
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+          const float4 t = wq[q];
+          wv[2 * q] = make_float2(t.x, t.y);
+          wv[2 * q + 1] = make_float2(t.z, t.w);
+        }
+        float2 v[4];
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+          const int di = d >> 1, dj = d & 1;
+          float2 a = wv[9];
+#pragma unroll
+          for (int u = 0; u < 3; ++u)
+#pragma unroll
+            for (int q = 0; q < 3; ++q) a = __ffma2_rn(wv[u * 3 + q], pt[di + u][dj + q], a);
+          v[d] = a;
+        }
+        const float m0 = fmaxf(fmaxf(fmaxf(v[0].x, v[1].x), fmaxf(v[2].x, v[3].x)), 0.f);
+        const float m1 = fmaxf(fmaxf(fmaxf(v[0].y, v[1].y), fmaxf(v[2].y, v[3].y)), 0.f);
+        __stcs(out + (2 * cp) * kPooled, m0);
+        __stcs(out + (2 * cp + 1) * kPooled, m1);
+      }
+    }
+  }
+  asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+
 // The Alice -> Alice weight hand-off: 288 + 32 floats, one small CTA in the step's launch chain (two
 // cudaMemcpyAsync device copies in its place cost ~40 us per hand-off: copy-engine latency, and the
 // chain of dependent launches is broken twice).

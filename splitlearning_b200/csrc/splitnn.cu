@@ -483,9 +483,16 @@ static int conv_stream_min() {
 static int launch_conv_fwd(const float* x, const float* w, const float* b, int B, float* act, size_t ld_act, int sms,
                            cudaStream_t st) {
   if (B >= conv_stream_min()) {
-    // resident CTAs per SM: 3 (54 registers) by default; SN_CONV_CTAS=2|4 for A/B timing
+    // SN_CONV_STREAM=cta selects the CTA-per-image form (A/B timing); default: warp-autonomous images
+    static const bool warp_form = !(getenv("SN_CONV_STREAM") && !strcmp(getenv("SN_CONV_STREAM"), "cta"));
+    // resident CTAs per SM of the CTA form: 3 (54 registers) by default; SN_CONV_CTAS=2|4 for A/B timing
     static const int ctas = getenv("SN_CONV_CTAS") ? atoi(getenv("SN_CONV_CTAS")) : 3;
-    if (ctas == 2)
+    if (warp_form) {
+      if (set_smem(conv_pool_stream_warp_kernel, kStreamWarpSmem)) return 1;
+      static const int wctas = getenv("SN_CONV_WCTAS") ? std::max(1, atoi(getenv("SN_CONV_WCTAS"))) : 2;   // 2: 0.162 ms, 3: 0.172, 4: 0.168
+      launch_k(conv_pool_stream_warp_kernel, dim3(std::min(ceil_div(B, kStreamWarps), sms * wctas)), dim3(32 * kStreamWarps),
+               kStreamWarpSmem, st, x, w, b, B, act, ld_act);
+    } else if (ctas == 2)
       launch_k(conv_pool_stream_kernel<2>, dim3(std::min(B, sms * 2)), dim3(kStreamThreads), 0, st, x, w, b, B, act, ld_act);
     else if (ctas == 4)
       launch_k(conv_pool_stream_kernel<4>, dim3(std::min(B, sms * 4)), dim3(kStreamThreads), 0, st, x, w, b, B, act, ld_act);

@@ -713,12 +713,15 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # warm-up with the shortest turn that still fits: every Alice (so every rank: kernels are loaded
-    # lazily, per process, on first launch) and every hand-off route has run before the timed steps
+    # pre-heat (untimed; bench.PREHEAT, disclosed in config) + warm-up with the shortest turn that still
+    # fits: every Alice (so every rank: kernels are loaded lazily, per process, on first launch) and every
+    # hand-off route has run before the timed steps
+    import bench as bench_mod
+    run_vanilla_schedule(rank, world, bob, mine, lambda i: (xs[i % nb], ys[i % nb]), n_alices, 1, 0, bench_mod.PREHEAT, B,
+                         device, None, link)
     run_vanilla_schedule(rank, world, bob, mine, lambda i: (xs[i % nb], ys[i % nb]), n_alices,
                          max(1, min(turn, W // (n_alices + 1))), 0, W, B, device, None, link)
     l0 = lib.sn_launch_count()
-    import bench as bench_mod
     with bench_mod.ClockSampler(local) as clk:
         ms = timed(lambda i: (xs[i % nb], ys[i % nb]), W)
     launches = torch.tensor([lib.sn_launch_count() - l0], device=device, dtype=torch.int64)

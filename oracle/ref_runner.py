@@ -46,6 +46,23 @@ def _free_port():
     return port
 
 
+class _CleanLaunchEnv:
+    """The reference's processes must rendezvous among themselves: when bench.py itself runs under
+    torchrun, the launcher's variables (TORCHELASTIC_USE_AGENT_STORE makes env:// rendezvous a CLIENT of
+    the launcher's store; RANK / WORLD_SIZE / MASTER_*; OMP_NUM_THREADS=1) must not leak into them."""
+    NAMES = ("RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "GROUP_RANK", "GROUP_WORLD_SIZE", "ROLE_RANK",
+             "ROLE_WORLD_SIZE", "ROLE_NAME", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS", "NCCL_ASYNC_ERROR_HANDLING",
+             "TORCH_NCCL_ASYNC_ERROR_HANDLING")
+
+    def __enter__(self):
+        self.saved = {k: os.environ.pop(k) for k in list(os.environ) if k in self.NAMES or k.startswith("TORCHELASTIC_")}
+        return self
+
+    def __exit__(self, *exc):
+        os.environ.update(self.saved)
+        return False
+
+
 def _args(world, batch, epochs=1, server_epochs=1):
     return Namespace(world_size=world, epochs=epochs, iterations=1, batch_size=batch, partition_alpha=0.5,
                      datapath="data/mnist_flat", lr=1e-3, server_epochs=server_epochs, vanilla=True, sisa=False,
@@ -127,12 +144,8 @@ def time_vanilla_rpc(steps, warmup, world=5, batch=16, threads=None):
         sizes = write_loaders(d, n_samples, world - 1, batch)
         total = sum((n + batch - 1) // batch for n in sizes)
         out = os.path.join(d, "stamps.json")
-        env_keep = os.environ.pop("OMP_NUM_THREADS", None)
-        try:
+        with _CleanLaunchEnv():
             mp.spawn(_vanilla_worker, args=(world, d, _free_port(), batch, threads, out), nprocs=world, join=True)
-        finally:
-            if env_keep is not None:
-                os.environ["OMP_NUM_THREADS"] = env_keep
         with open(out) as f:
             stamps = json.load(f)
     n_steps = len(stamps) - 1                       # the last stamp closes the last step
@@ -179,12 +192,8 @@ def time_sisa_server(n_batches, batch=16, threads=None):
     threads = threads or host_threads()
     with tempfile.TemporaryDirectory() as d:
         out = os.path.join(d, "sisa.json")
-        env_keep = os.environ.pop("OMP_NUM_THREADS", None)
-        try:
+        with _CleanLaunchEnv():
             mp.spawn(_sisa_worker, args=(n_batches, batch, threads, _free_port(), out), nprocs=1, join=True)
-        finally:
-            if env_keep is not None:
-                os.environ["OMP_NUM_THREADS"] = env_keep
         with open(out) as f:
             r = json.load(f)
     r["ms_per_step"] = 1e3 * r["seconds"] / r["steps"]

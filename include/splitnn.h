@@ -242,6 +242,17 @@ int sn_alice_set_opt_step(sn_alice* h, int64_t step);
 
 /* act [B,5408] may live on another device (peer-mapped) — e.g. directly in Bob's HBM. */
 int sn_alice_forward(sn_alice* h, const float* x, int B, float* act, void* stream);
+/* The same for a batch that still lies in PINNED HOST memory (cudaHostAlloc / torch pin_memory: device-
+ * visible under UVA): the conv kernel reads host_x [B,1,28,28] and host_y [B] over PCIe itself, in its
+ * prologue - before its dependency wait, so the transfer overlaps the previous kernel of the stream -
+ * and leaves device copies in x_dev [B,784] / y_dev [B] for whoever needs the batch again (the conv
+ * backward, the server's loss).  Replaces the DataLoader -> model hand-off of a CPU batch,
+ * data_entities_vanilla.py:67-72, without a separate H2D copy, side stream or event in the step.  The
+ * caller alternates between two (x_dev, y_dev) pairs from step to step: this step's prologue may
+ * overwrite them while the previous step's backward still reads its own pair.  host_y/y_dev may both
+ * be NULL.  B < 512. */
+int sn_alice_forward_host(sn_alice* h, const float* host_x, const int64_t* host_y, int B, float* act,
+                          float* x_dev, int64_t* y_dev, void* stream);
 /* The same with a row stride: sample b's 5408 activations go to act + b*ld_act (ld_act >= 5408, in
  * floats).  With ld_act = 5408*K and act pointing at column 5408*k of the --concat server's
  * [rows, 5408*K] cache - normally a peer pointer into Bob's GPU - one launch per Alice fills her slot
@@ -271,6 +282,13 @@ int sn_alice_local_epoch(sn_alice* h, const float* x, const int64_t* labels, int
 int sn_vanilla_step(sn_alice* alice, sn_bob* bob, int slot, const float* x, const int64_t* labels,
                     int B, uint64_t seed, uint64_t offset, float* act, float* cut_grad,
                     float* loss_out, void* stream);
+
+/* sn_vanilla_step with the batch taken from pinned host memory (sn_alice_forward_host): the whole
+ * end-to-end step - host batch in, loss out (loss_out may be pinned host memory too) - is one call and
+ * one unbroken chain of dependent launches. */
+int sn_vanilla_step_host(sn_alice* alice, sn_bob* bob, int slot, const float* host_x, const int64_t* host_y,
+                         int B, uint64_t seed, uint64_t offset, float* x_dev, int64_t* y_dev, float* act,
+                         float* cut_grad, float* loss_out, void* stream);
 
 /* ------------------------------------------------------------------ NVLink plumbing */
 int sn_p2p_enable_all(int n_devices);

@@ -14,7 +14,7 @@ import bench
 from splitlearning_b200 import engine as E
 from splitlearning_b200.io import iterate_host_batches
 
-B, D0, N_ALICES, TURN = bench.B, bench.D0, bench.N_ALICES, bench.TURN
+B, D0, N_ALICES, TURN = bench.B, bench.D0, bench.N_ALICES, 64
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(dev)
 bob_model, bob, alices = bench.make_world(torch, dev)

@@ -58,6 +58,8 @@ SIGNATURES = {
     "sn_alice_set_opt_step": (_i, [_vp, _i64]),
     "sn_alice_forward": (_i, [_vp, _vp, _i, _vp, _vp]),
     "sn_alice_forward_ld": (_i, [_vp, _vp, _i, _vp, _sz, _vp]),
+    "sn_alice_forward_host": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _vp, _vp]),
+    "sn_vanilla_step_host": (_i, [_vp, _vp, _i, _vp, _vp, _i, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "sn_alice_backward_update": (_i, [_vp, _vp, _vp, _i, _vp]),
     "sn_alice_local_step": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "sn_alice_local_epoch": (_i, [_vp, _vp, _vp, _i64, _i, _vp, _vp]),

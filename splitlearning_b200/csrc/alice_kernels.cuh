@@ -35,9 +35,17 @@ __device__ __forceinline__ void conv4(const float* __restrict__ img, const float
 // grid (samples, 4 channel groups), 256 threads.  act index = b*ld_act + c*169 + i*13 + j
 // (ld_act = 5408 for a dense [B,5408] block; 5408*K when the rows are one Alice's slot of the
 // --concat server's [rows, 5408*K] cache).
+// x_mirror / y_src / y_dst (nullable; host-input form, sn_alice_forward_host): x and y_src are PINNED HOST
+// memory that the kernel reads over PCIe itself - in its prologue, before the dependency wait, so the
+// transfer overlaps the previous kernel - and it leaves device copies (x_mirror [B,784], y_dst [B]) for
+// the kernels that need the batch again (the conv backward, the server's loss).  No side stream, no
+// events, no break in the launch chain.
 __global__ void __launch_bounds__(256) conv_pool_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                             const float* __restrict__ bias, int B,
-                                                            float* __restrict__ act, size_t ld_act) {
+                                                            float* __restrict__ act, size_t ld_act,
+                                                            float* __restrict__ x_mirror,
+                                                            const long long* __restrict__ y_src,
+                                                            long long* __restrict__ y_dst) {
   __shared__ float img[28 * 28];
   __shared__ float ws[kConvCG * 9];
   __shared__ float bs[kConvCG];
@@ -46,8 +54,13 @@ __global__ void __launch_bounds__(256) conv_pool_fwd_kernel(const float* __restr
   // dependency wait.  The conv weights are NOT safe to touch early - the previous step's
   // conv_pool_bwd_kernel, which updates them, can be the launch right before this one.
   if (blockIdx.x < B)
-    for (int t = threadIdx.x; t < 196; t += 256)
-      reinterpret_cast<float4*>(img)[t] = reinterpret_cast<const float4*>(x + (size_t)blockIdx.x * 784)[t];
+    for (int t = threadIdx.x; t < 196; t += 256) {
+      const float4 v = reinterpret_cast<const float4*>(x + (size_t)blockIdx.x * 784)[t];
+      reinterpret_cast<float4*>(img)[t] = v;
+      if (x_mirror && cg == 0) reinterpret_cast<float4*>(x_mirror + (size_t)blockIdx.x * 784)[t] = v;
+    }
+  if (y_dst && blockIdx.x == 0 && cg == 0)
+    for (int t = threadIdx.x; t < B; t += 256) y_dst[t] = y_src[t];
   pdl_wait();
   pdl_launch();
   if (threadIdx.x < kConvCG * 9) ws[threadIdx.x] = w[cg * kConvCG * 9 + threadIdx.x];
@@ -55,8 +68,11 @@ __global__ void __launch_bounds__(256) conv_pool_fwd_kernel(const float* __restr
   for (int b = blockIdx.x; b < B; b += gridDim.x) {
     if (b != blockIdx.x) {
       __syncthreads();
-      for (int t = threadIdx.x; t < 196; t += 256)
-        reinterpret_cast<float4*>(img)[t] = reinterpret_cast<const float4*>(x + (size_t)b * 784)[t];
+      for (int t = threadIdx.x; t < 196; t += 256) {
+        const float4 v = reinterpret_cast<const float4*>(x + (size_t)b * 784)[t];
+        reinterpret_cast<float4*>(img)[t] = v;
+        if (x_mirror && cg == 0) reinterpret_cast<float4*>(x_mirror + (size_t)b * 784)[t] = v;
+      }
     }
     __syncthreads();
     for (int o = threadIdx.x; o < kConvCG * kPooled; o += 256) {

@@ -481,8 +481,9 @@ static int conv_stream_min() {
   return v;
 }
 static int launch_conv_fwd(const float* x, const float* w, const float* b, int B, float* act, size_t ld_act, int sms,
-                           cudaStream_t st) {
-  if (B >= conv_stream_min()) {
+                           cudaStream_t st, float* x_mirror = nullptr, const long long* y_src = nullptr,
+                           long long* y_dst = nullptr) {
+  if (B >= conv_stream_min() && !x_mirror && !y_dst) {
     // SN_CONV_STREAM=cta selects the CTA-per-image form (A/B timing); default: warp-autonomous images
     static const bool warp_form = !(getenv("SN_CONV_STREAM") && !strcmp(getenv("SN_CONV_STREAM"), "cta"));
     // resident CTAs per SM of the CTA form: 3 (54 registers) by default; SN_CONV_CTAS=2|4 for A/B timing
@@ -499,7 +500,7 @@ static int launch_conv_fwd(const float* x, const float* w, const float* b, int B
     else
       launch_k(conv_pool_stream_kernel<3>, dim3(std::min(B, sms * 3)), dim3(kStreamThreads), 0, st, x, w, b, B, act, ld_act);
   } else {
-    launch_k(conv_pool_fwd_kernel, dim3(std::min(B, sms * 4), 4), dim3(256), 0, st, x, w, b, B, act, ld_act);
+    launch_k(conv_pool_fwd_kernel, dim3(std::min(B, sms * 4), 4), dim3(256), 0, st, x, w, b, B, act, ld_act, x_mirror, y_src, y_dst);
   }
   SN_LAUNCH_CHECK();
   return 0;
@@ -1425,6 +1426,15 @@ int sn_alice_forward(sn_alice* h, const float* x, int B, float* act, void* strea
   return launch_conv_fwd(x, h->w, h->b, B, act, kD0, h->sms, (cudaStream_t)stream);
 }
 
+int sn_alice_forward_host(sn_alice* h, const float* host_x, const int64_t* host_y, int B, float* act, float* x_dev,
+                          int64_t* y_dev, void* stream) {
+  SN_ALICE_ENTER(h);
+  SN_REQUIRE(host_x && act && x_dev && B > 0 && (!host_y == !y_dev), "sn_alice_forward_host: bad arguments");
+  static_assert(sizeof(long long) == sizeof(int64_t), "int64 labels");
+  return launch_conv_fwd(host_x, h->w, h->b, B, act, kD0, h->sms, (cudaStream_t)stream, x_dev,
+                         reinterpret_cast<const long long*>(host_y), reinterpret_cast<long long*>(y_dev));
+}
+
 int sn_alice_forward_ld(sn_alice* h, const float* x, int B, float* act, size_t ld_act, void* stream) {
   SN_ALICE_ENTER(h);
   SN_REQUIRE(x && act && B > 0 && ld_act >= (size_t)kD0, "sn_alice_forward_ld: bad arguments (ld_act >= 5408)");
@@ -1499,6 +1509,18 @@ int sn_vanilla_step(sn_alice* alice, sn_bob* bob, int slot, const float* x, cons
   rc = sn_bob_train_step(bob, slot, act, labels, B, nullptr, seed, offset, cut_grad, nullptr, loss_out, stream);
   if (rc) return rc;
   return sn_alice_backward_update(alice, x, cut_grad, B, stream);
+}
+
+int sn_vanilla_step_host(sn_alice* alice, sn_bob* bob, int slot, const float* host_x, const int64_t* host_y, int B,
+                         uint64_t seed, uint64_t offset, float* x_dev, int64_t* y_dev, float* act, float* cut_grad,
+                         float* loss_out, void* stream) {
+  SN_REQUIRE(alice && bob && host_x && host_y && x_dev && y_dev && act && cut_grad && B > 0, "sn_vanilla_step_host: bad arguments");
+  SN_REQUIRE(alice->device == bob->device, "sn_vanilla_step_host: Alice and Bob must share a device");
+  int rc = sn_alice_forward_host(alice, host_x, host_y, B, act, x_dev, y_dev, stream);
+  if (rc) return rc;
+  rc = sn_bob_train_step(bob, slot, act, y_dev, B, nullptr, seed, offset, cut_grad, nullptr, loss_out, stream);
+  if (rc) return rc;
+  return sn_alice_backward_update(alice, x_dev, cut_grad, B, stream);
 }
 
 #ifdef SN_TRACE

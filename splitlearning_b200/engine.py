@@ -293,6 +293,18 @@ def vanilla_step(alice, bob, x, labels, slot, seed, offset, act, cut, loss):
                                   ptr(act), ptr(cut), ptr(loss), _stream(x.device)))
 
 
+def vanilla_step_host(alice, bob, host_x, host_y, slot, seed, offset, x_dev, y_dev, act, cut, loss):
+    """`sn_vanilla_step_host`: the same step with the batch still in PINNED host memory - the conv kernel
+    pulls it over PCIe in its prologue and leaves device copies in `x_dev` / `y_dev` (alternate between
+    two pairs from step to step)."""
+    if not (host_x.is_pinned() and host_y.is_pinned()):
+        raise ValueError("vanilla_step_host needs pinned host tensors (tensor.pin_memory())")
+    dev = act.device
+    with torch.cuda.device(dev):
+        check(bob.lib.sn_vanilla_step_host(alice.h, bob.h, int(slot), ptr(host_x), ptr(host_y), int(host_x.shape[0]), int(seed),
+                                           int(offset), ptr(x_dev), ptr(y_dev), ptr(act), ptr(cut), ptr(loss), _stream(dev)))
+
+
 class _RawCuda:
     """Minimal __cuda_array_interface__ carrier so torch can view library-owned memory."""
 

@@ -201,6 +201,38 @@ def test_single_call_vanilla_step_equals_the_three_calls(eng, B):
         assert torch.equal(u, v)
 
 
+@pytest.mark.parametrize("B", [16, 11])
+def test_host_input_step_equals_the_device_input_step(eng, B):
+    """sn_vanilla_step_host: the batch stays in pinned host memory, the conv kernel reads it over PCIe in its
+    prologue and leaves device copies for the backward and the loss.  Three steps (alternating the two
+    device-copy pairs) must EQUAL sn_vanilla_step on a device-resident batch: weights, losses, and the
+    copies themselves."""
+    a0, b0 = seeded_weights(A_SHAPES, 11), seeded_weights(B_SHAPES, 12)
+    kw = dict(optimizer=eng.SN_OPT_SGD_MOMENTUM, lr=1e-3, momentum=0.9)
+    finals = []
+    for host in (False, True):
+        gw, gb = cu(a0[0]), cu(a0[1])
+        bob, gp = _bob(eng, T(b0), **kw)
+        alice = eng.AliceEngine(gw, gb, **kw)
+        act, cut = torch.empty(B, 5408, device="cuda"), torch.empty(B, 5408, device="cuda")
+        loss = torch.zeros(3, dtype=torch.float32).pin_memory() if host else torch.zeros(3, device="cuda")
+        xd = [torch.empty(B, 1, 28, 28, device="cuda") for _ in range(2)]
+        yd = [torch.empty(B, dtype=torch.int64, device="cuda") for _ in range(2)]
+        for step in range(3):
+            x, y = seeded_batch(B, 100 + step)
+            if host:
+                hx, hy = torch.from_numpy(x).pin_memory(), torch.from_numpy(y).pin_memory()
+                eng.vanilla_step_host(alice, bob, hx, hy, 0, 5, step + 1, xd[step & 1], yd[step & 1], act, cut, loss[step])
+                torch.cuda.synchronize()                      # hx / hy go out of scope below
+                assert torch.equal(xd[step & 1].cpu(), torch.from_numpy(x)) and torch.equal(yd[step & 1].cpu(), torch.from_numpy(y))
+            else:
+                eng.vanilla_step(alice, bob, cu(x), cu(y), 0, 5, step + 1, act, cut, loss[step])
+        torch.cuda.synchronize()
+        finals.append([gw.clone(), gb.clone()] + [p.clone() for p in gp] + [loss.clone().cuda()])
+    for u, v in zip(*finals):
+        assert torch.equal(u, v)
+
+
 @pytest.mark.parametrize("opt", ["sgd", "adam"])
 def test_persistent_tail_kernel_is_bit_identical_to_the_launch_chain(eng, opt):
     """sn_set_persistent_tail(1): the middle of the step (fc1 epilogue .. fc2 backward) runs as one

@@ -9,10 +9,18 @@ Alice conv forward -> Bob forward / cross-entropy / backward / SGD-momentum (per
 -> cut-layer gradient -> Alice conv backward + SGD-momentum.  Workload at N=1 is
 BASELINE.json configs[1]: `--vanilla`, world_size=5 (1 Bob + 4 Alices taking turns), all on one
 B200.  Under torchrun (N>1): Bob on rank 0, the 4 Alices spread over ranks 1..N-1, activations and
-cut-layer gradients over NCCL send/recv; the protocol is strictly sequential, so
-total work is fixed: scaling = "strong".
+cut-layer gradients written by the producing kernels straight into the consumer GPU's mailbox over
+NVLink (peer.PeerLink; SN_LINK=nccl for send/recv); the protocol is strictly sequential
+(SURVEY.md 8e), so total work is fixed: scaling = "strong".
 
-Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+`--impl reference`: the UNMODIFIED reference (oracle/_ref) through its torch.distributed.rpc path on
+the host cores (oracle/ref_runner.py); under torchrun rank 0 alone runs it.
+
+Prints ONE JSON line (rank 0).  Besides the contract's fields: `roofline` (dominant kernel + whole
+step), `cpu_baseline` (reference over RPC on a bounded sample, the single-process port beside it),
+`sisa` (server epoch, cache fill, tensor-parallel epoch at N>1), `sisa_concat` (BASELINE.json
+configs[3]), `sweep` (five points of configs[4] at reference precision), `parity` (N>1: multi-GPU
+paths against the one-GPU path).  See DESIGN.md "Measurement".
 """
 import argparse
 import json

@@ -125,9 +125,14 @@ def run_reference(args):
     from oracle import ref_runner
     ncpu = ref_runner.host_threads()
     extra = {}
+    r = None
     if ref_runner.available():
         k = min(args.steps, REF_MAX_STEPS)
-        r = ref_runner.time_vanilla_rpc(k, args.warmup, world=N_ALICES + 1, batch=B, threads=ncpu)
+        try:
+            r = ref_runner.time_vanilla_rpc(k, args.warmup, world=N_ALICES + 1, batch=B, threads=ncpu)
+        except Exception as e:                      # the RPC harness could not run here: say so, time the port
+            extra = {"reference_error": f"{type(e).__name__}: {e}"[:300]}
+    if r is not None:
         value, dt, steps, threads = r["samples_per_s"], r["seconds"], r["steps"], r["threads"]
         kind = "reference"
         sample = (f"{steps} vanilla split steps of B={B} after {r['warmup']} warm-up steps through the UNMODIFIED reference: "
@@ -151,7 +156,8 @@ def run_reference(args):
         steps = args.steps
         dt = cb.time_steps(w, steps, args.warmup)
         value, threads, kind = steps * B / dt, best[1], "port"
-        sample = f"{steps} vanilla split steps of B={B} on torch-CPU, single process, no RPC (oracle/_ref absent)"
+        sample = (f"{steps} vanilla split steps of B={B} on torch-CPU, single process, no RPC "
+                  f"({'the RPC harness failed' if extra else 'oracle/_ref absent'})")
     line = {
         "impl": "reference", "metric": "split_nn_train_samples_per_sec", "value": value, "unit": "samples/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / steps,

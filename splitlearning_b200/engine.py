@@ -253,6 +253,19 @@ class AliceEngine:
             check(self.lib.sn_alice_forward_ld(self.h, ptr(x), B, C.c_void_p(out.data_ptr()), int(ld), _stream(x.device)))
         return out
 
+    def forward_host(self, host_x, host_y, x_dev, y_dev, out=None):
+        """`sn_alice_forward_host`: the batch is still in PINNED host memory; the conv kernel reads it over
+        PCIe in its prologue, writes the activations to `out` (a tensor or a raw peer address) and leaves
+        device copies in `x_dev` / `y_dev` (alternate between two pairs from step to step)."""
+        if not host_x.is_pinned() or (host_y is not None and not host_y.is_pinned()):
+            raise ValueError("forward_host needs pinned host tensors (tensor.pin_memory())")
+        B = host_x.shape[0]
+        out = out if out is not None else torch.empty(B, D0, device=self.device)
+        with torch.cuda.device(self.device):
+            check(self.lib.sn_alice_forward_host(self.h, ptr(host_x), ptr(host_y), B, C.c_void_p(out.data_ptr()), ptr(x_dev),
+                                                 ptr(y_dev) if host_y is not None else None, _stream(self.device)))
+        return out
+
     def backward_update(self, x, cut_grad):
         _f32c(x), _f32c(cut_grad)
         check(self.lib.sn_alice_backward_update(self.h, ptr(x), ptr(cut_grad), x.shape[0], _stream(x.device)))

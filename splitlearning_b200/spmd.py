@@ -77,17 +77,27 @@ def run_vanilla_schedule(rank, world, bob, alices, batch_fn, n_alices, turn, fir
         n = B if rows_fn is None else int(rows_fn(i))
         if not 1 <= n <= B:
             raise ValueError(f"step {i}: rows_fn gave {n} rows, mailboxes hold 1..{B}")
+        host_in = False
         if rank == own or world == 1:
             x, y = batch_fn(i)
             if x.shape[0] != n:
                 raise ValueError(f"step {i}: batch_fn returned {x.shape[0]} rows where every rank expects {n} "
                                  "(pass rows_fn for ragged batches)")
+            # a batch still in pinned host memory: Alice's conv kernel reads it over PCIe itself and
+            # leaves device copies for her backward and for the labels' way to Bob (no copy op, no event)
+            host_in = x.device.type == "cpu" and hasattr(alices[k], "forward_host")
         if world == 1:
-            act = alices[k].forward(x)
+            if host_in:
+                act, x, y = alices[k].forward_host(x, y, i)
+            else:
+                act = alices[k].forward(x)
             loss, g, _ = bob.train_step(act, y, slot=k)
             alices[k].backward_update(x, g)
         elif link is not None and rank == own:
-            alices[k].forward(x, out=link.alice_targets())       # the conv kernel stores into Bob's GPU
+            if host_in:
+                _, x, y = alices[k].forward_host(x, y, i, out=link.alice_targets())
+            else:
+                alices[k].forward(x, out=link.alice_targets())   # the conv kernel stores into Bob's GPU
             link.alice_publish(y, n)
             alices[k].backward_update(x, link.alice_wait_cut()[:n])
         elif link is not None and rank == 0:
@@ -96,7 +106,10 @@ def run_vanilla_schedule(rank, world, bob, alices, batch_fn, n_alices, turn, fir
             loss, g, _ = bob.train_step(act[:n], lab[:n], slot=k, cut_out=link.bob_cut_target(own))
             link.bob_publish_cut(own)
         elif rank == own:
-            alices[k].forward(x, out=act_view[:n])
+            if host_in:
+                _, x, y = alices[k].forward_host(x, y, i, out=act_view[:n])
+            else:
+                alices[k].forward(x, out=act_view[:n])
             lab_view[:n].copy_(y)
             dist.send(msg, dst=0)
             dist.recv(cut, src=0)
@@ -331,9 +344,20 @@ class _CudaAlice:
         self.model = M.model1_sisa(device)
         self.eng = self.model.make_engine(optimizer=E.SN_OPT_SGD_MOMENTUM, lr=lr, momentum=0.9, max_batch=64)
         self.w, self.b = self.model._wb()
+        self._mirrors = None
 
     def forward(self, x, out=None):
         return self.eng.forward(x, out=out)
+
+    def forward_host(self, hx, hy, step, out=None):
+        """(act, x_dev, y_dev) for a pinned host batch; the device copies alternate between two pairs."""
+        if self._mirrors is None:
+            dev, mb = self.eng.device, self.eng.max_batch
+            self._mirrors = [(torch.empty(mb, 1, 28, 28, device=dev), torch.empty(mb, dtype=torch.int64, device=dev)) for _ in range(2)]
+        n = hx.shape[0]
+        xd, yd = self._mirrors[step & 1]
+        act = self.eng.forward_host(hx, hy, xd, yd, out=out)
+        return act, xd[:n], yd[:n]
 
     def backward_update(self, x, cut):
         self.eng.backward_update(x, cut)
@@ -738,7 +762,11 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
     owned = [i for i in range(first, last) if owner_rank((i // turn) % n_alices, world) == rank]
     pos = {i: j for j, i in enumerate(owned)}
 
+    zero_copy = os.environ.get("SN_E2E", "zerocopy") != "copy"
+
     def host_batch(i):
+        if zero_copy:                                     # pinned tensors straight into the schedule
+            return phx[i % nb], phy[i % nb]
         j = pos[i]
         if j == 0:
             pf.submit(0, phx[i % nb], phy[i % nb])

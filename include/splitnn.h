@@ -399,6 +399,23 @@ int sn_tp_server_epoch(sn_shard* shard, sn_bob* head, int rank, int world, const
                        float* const* dH1_table_dev, const void* dh_flag_table_dev, uint32_t seq0,
                        float* loss_per_step, void* stream);
 
+/* ---- host-side data preparation (no GPU work; these two run on the calling thread) ----
+ * LDA (Dirichlet) non-IID partition of n labelled samples over client_num clients: the classification
+ * branch of non_iid_partition_with_dirichlet_distribution, /root/reference/data/noniid_partition.py:6-91,
+ * as one native call that consumes numpy's LEGACY MT19937 stream exactly as the reference's
+ * np.random.shuffle / np.random.dirichlet calls do.  The caller passes the generator state
+ * (np.random.get_state(): key[624], pos, has_gauss, cached_gaussian); it is advanced in place, so handing
+ * it back with np.random.set_state() leaves the stream where the reference would have left it.
+ * out_idx[n] receives the clients' sample ids back to back, out_offsets[client_num+1] the boundaries
+ * (samples whose label is outside [0, classes) belong to nobody, as in the reference).  Returns 0, or 2
+ * on a NULL/invalid argument. */
+int sn_lda_partition(const int64_t* labels, int64_t n, int client_num, int classes, double alpha,
+                     uint32_t* mt_key624, int* mt_pos, int* has_gauss, double* cached_gauss,
+                     int64_t* out_idx, int64_t* out_offsets);
+/* Python's random.shuffle(ids) for the state of random.getstate() (key[624], pos): the shuffle in front
+ * of the 80/20 train/test split, /root/reference/data/relational_table_preprocessor.py:83. */
+int sn_py_random_shuffle(int64_t* ids, int64_t n, uint32_t* mt_key624, int* mt_pos);
+
 #ifdef __cplusplus
 }
 #endif

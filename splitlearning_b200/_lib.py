@@ -88,6 +88,8 @@ SIGNATURES = {
     "sn_flag_signal_many": (_i, [_vp, _i, C.c_uint32, _vp]),
     "sn_flag_status": (_i, []),
     "sn_flag_status_clear": (_i, []),
+    "sn_lda_partition": (_i, [_vp, _i64, _i, _i, _d, _vp, C.POINTER(_i), C.POINTER(_i), C.POINTER(_d), _vp, _vp]),
+    "sn_py_random_shuffle": (_i, [_vp, _i64, _vp, C.POINTER(_i)]),
 }
 
 _lib = None

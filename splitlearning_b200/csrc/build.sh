@@ -6,5 +6,5 @@ OUT=${SN_OUT:-"$HERE/../libsplitnn.so"}
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 $NVCC -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
   -Xcompiler -fPIC -shared ${SN_NVCC_EXTRA} \
-  -o "$OUT" "$HERE/splitnn.cu" -lcudart
+  -o "$OUT" "$HERE/splitnn.cu" "$HERE/lda_partition.cpp" -lcudart
 echo "built $OUT"

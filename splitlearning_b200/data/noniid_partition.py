@@ -11,8 +11,39 @@ Bit-exactness depends on consuming numpy's *legacy global* MT19937 stream in exa
     for client i in 0..client_num-1:  shuffle(python list)
 Shuffling an ndarray and shuffling a python list of the same length draw different numbers of
 variates, so the container types below are part of the contract.
+
+Two implementations, equal bit for bit (tests/test_host_logic.py): the numpy one below, and the
+native routine `sn_lda_partition` (csrc/lda_partition.cpp) that takes numpy's MT19937 state in and
+hands it back advanced.  `native=None` picks the native one when libsplitnn.so is there.
 """
+import ctypes as C
+
 import numpy as np
+
+
+def _native_lib():
+    from .. import _lib
+    try:
+        return _lib.load()
+    except (_lib.SplitNNError, OSError):
+        return None
+
+
+def _partition_native(lib, labels, client_num, classes, alpha, rng):
+    """The whole partition in one library call; numpy's generator state goes in and comes back."""
+    name, key, pos, has_gauss, cached = rng.get_state()
+    key = np.ascontiguousarray(key, dtype=np.uint32).copy()
+    labels = np.ascontiguousarray(labels, dtype=np.int64)
+    n = labels.shape[0]
+    ids = np.empty(n, dtype=np.int64)
+    offsets = np.empty(client_num + 1, dtype=np.int64)
+    c_pos, c_has, c_gauss = C.c_int(int(pos)), C.c_int(int(has_gauss)), C.c_double(float(cached))
+    rc = lib.sn_lda_partition(labels.ctypes.data, n, int(client_num), int(classes), float(alpha), key.ctypes.data,
+                              C.byref(c_pos), C.byref(c_has), C.byref(c_gauss), ids.ctypes.data, offsets.ctypes.data)
+    if rc != 0:
+        raise ValueError("sn_lda_partition: invalid argument")
+    rng.set_state((name, key, c_pos.value, c_has.value, c_gauss.value))
+    return {i: ids[offsets[i]:offsets[i + 1]].tolist() for i in range(client_num)}
 
 
 def _split_one_class(n_total, alpha, client_num, shards, class_idx, rng):
@@ -30,17 +61,25 @@ def _split_one_class(n_total, alpha, client_num, shards, class_idx, rng):
 
 
 def non_iid_partition_with_dirichlet_distribution(label_list, client_num, classes, alpha,
-                                                  task='classification', rng=None):
+                                                  task='classification', rng=None, native=None):
     """Return {client: [sample ids]}; same name/arguments as the reference (`:6-10`).
 
     `rng` defaults to numpy's global legacy generator (what the reference uses); pass a
-    `np.random.RandomState` to keep the global stream untouched.
+    `np.random.RandomState` to keep the global stream untouched.  `native`: True = the library
+    routine, False = numpy, None = the library when it loads.
     """
     if task == 'segmentation':
         raise NotImplementedError("segmentation partition is outside the split-NN hot path")
     rng = np.random if rng is None else rng
     labels = np.asarray(label_list)
     n_total = labels.shape[0]
+    integral = n_total > 0 and labels.ndim == 1 and np.issubdtype(labels.dtype, np.integer) and hasattr(rng, "get_state")
+    if native is not False and integral:
+        lib = _native_lib()
+        if lib is not None:
+            return _partition_native(lib, labels, client_num, classes, alpha, rng)
+    if native:
+        raise RuntimeError("native LDA partition needs libsplitnn.so, 1-D integer labels and a legacy numpy generator")
 
     smallest = 0
     while smallest < 10:                                     # min-size guarantee (:43-44)

@@ -5,14 +5,36 @@ and `:8-55` (`relational_table_preprocess_dl`, the flat-784 twin).  The two diff
 rows are indexed, so both go through `_split_clients`.  RNG call order that must be preserved
 for a bit-exact split: the LDA partition first (numpy legacy global stream), then one
 `random.shuffle(list)` per client in ascending client order (`:83`), `N_train = int(N*(1-test))`
-(`:80`).  The returned list has the reference's 8 positions (`:103-104`).
+(`:80`).  The returned list has the reference's 8 positions (`:103-104`).  Both shuffles run in the
+library when it is there (`sn_lda_partition`, `sn_py_random_shuffle`: the generators' states go in
+and come back advanced exactly as numpy / `random` would have left them).
 """
+import ctypes as C
 import random
 
+import numpy as np
 import torch
 from torch.utils.data import ConcatDataset, DataLoader, TensorDataset
 
-from .noniid_partition import non_iid_partition_with_dirichlet_distribution
+from .noniid_partition import _native_lib, non_iid_partition_with_dirichlet_distribution
+
+
+def py_random_shuffle(ids, native=None):
+    """`random.shuffle(ids)` on a list of sample ids, in place, on Python's global generator."""
+    lib = _native_lib() if native is not False else None
+    if lib is None:
+        if native:
+            raise RuntimeError("native shuffle needs libsplitnn.so")
+        random.shuffle(ids)
+        return
+    version, internal, gauss_next = random.getstate()
+    key = np.array(internal[:624], dtype=np.uint32)
+    pos = C.c_int(internal[624])
+    arr = np.asarray(ids, dtype=np.int64)
+    if lib.sn_py_random_shuffle(arr.ctypes.data, arr.shape[0], key.ctypes.data, C.byref(pos)) != 0:
+        raise ValueError("sn_py_random_shuffle: invalid argument")
+    random.setstate((version, tuple(key.tolist()) + (pos.value,), gauss_next))
+    ids[:] = arr.tolist()
 
 
 def _split_clients(args, data, label_list, test_partition):
@@ -29,7 +51,7 @@ def _split_clients(args, data, label_list, test_partition):
         n_client = len(ids)
         n_train = int(n_client * (1 - test_partition))
         train_sizes[client] = n_train
-        random.shuffle(ids)
+        py_random_shuffle(ids)
         head, tail = ids[:n_train], ids[n_train:]
         train_set = TensorDataset(data[head], labels[head])
         test_set = TensorDataset(data[tail], labels[tail])

@@ -24,14 +24,15 @@ KAT = {
 }
 
 
+@pytest.mark.parametrize("native", [False, True])
 @pytest.mark.parametrize("K", [1, 3, 4, 7])
-def test_lda_partition_known_answers(K):
+def test_lda_partition_known_answers(K, native):
     from splitlearning_b200.data.noniid_partition import non_iid_partition_with_dirichlet_distribution as part
     labels = np.random.RandomState(1234).randint(0, 10, size=70000)
     assert hashlib.sha256(labels.astype(np.int64).tobytes()).hexdigest() == \
         "51cfabb574dbfd600bb2efc08db687688c119041674d97a10ad1378dc9e75b0a"
     np.random.seed(0)
-    m = part(torch.LongTensor(labels.tolist()), K, 10, 0.5, task='task')
+    m = part(torch.LongTensor(labels.tolist()), K, 10, 0.5, task='task', native=native)
     h = hashlib.sha256()
     for k in range(K):
         h.update(np.asarray(m[k], np.int64).tobytes())
@@ -53,8 +54,49 @@ def test_lda_partition_edge_cases():
     assert min(len(m[k]) for k in range(4)) >= 10
 
 
-def test_train_test_split_known_answer():
+@pytest.mark.parametrize("n,K,classes,alpha,warm", [
+    (5000, 10, 10, 0.1, 0),       # skewed: some clients fill up and are masked out
+    (600, 5, 3, 0.3, 0),          # the min-size loop restarts
+    (3000, 16, 10, 2.5, 1),       # alpha > 1: Marsaglia-Tsang gammas, starting with a cached gaussian
+    (2000, 9, 7, 1.0, 0),         # alpha == 1: exponentials
+    (40000, 150, 10, 5.0, 2),     # > 128 clients: the renormalising sum recurses pairwise
+])
+def test_native_lda_partition_is_numpys(n, K, classes, alpha, warm):
+    """csrc/lda_partition.cpp against the numpy implementation: the same shards, and the generator is
+    left at the same position (the next uniform and the next gaussian agree)."""
+    from splitlearning_b200.data.noniid_partition import non_iid_partition_with_dirichlet_distribution as part
+    labels = np.random.RandomState(100 + n).randint(0, classes, n)
+    a, b = np.random.RandomState(n), np.random.RandomState(n)
+    for _ in range(warm):
+        a.normal(), b.normal()
+    ra = part(labels, K, classes, alpha, rng=a, native=False)
+    rb = part(labels, K, classes, alpha, rng=b, native=True)
+    assert ra == rb
+    assert a.random_sample() == b.random_sample() and a.normal() == b.normal()
+    sa, sb = a.get_state(), b.get_state()
+    assert np.array_equal(sa[1], sb[1]) and sa[2:] == sb[2:]
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 17, 1000, 48000])
+def test_native_py_shuffle_is_random_shuffle(n):
+    from splitlearning_b200.data.relational_table_preprocessor import py_random_shuffle
+    random.seed(n + 3)
+    want = list(range(n))
+    random.shuffle(want)
+    after = random.getstate()
+    random.seed(n + 3)
+    got = list(range(n))
+    py_random_shuffle(got, native=True)
+    assert got == want and random.getstate() == after
+
+
+@pytest.mark.parametrize("native", [False, True])
+def test_train_test_split_known_answer(native, monkeypatch):
+    from splitlearning_b200.data import noniid_partition, relational_table_preprocessor
     from splitlearning_b200.data.relational_table_preprocessor import image_preprocess_dl
+    if not native:          # the numpy / `random` path: as if the library were not there
+        monkeypatch.setattr(noniid_partition, "_native_lib", lambda: None)
+        monkeypatch.setattr(relational_table_preprocessor, "_native_lib", lambda: None)
     N = 4000
     lab = np.random.RandomState(1234).randint(0, 10, size=N)
     data = np.arange(N, dtype=np.float64).reshape(N, 1, 1, 1)

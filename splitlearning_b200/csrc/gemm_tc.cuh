@@ -146,6 +146,23 @@ __device__ __forceinline__ void mma_commit(unsigned long long* bar) {
 
 enum { EPI_FWD = 0, EPI_GATE = 1, EPI_UPDATE = 2 };
 
+__device__ __forceinline__ void cp16(float* smem, const float* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+#define SN_TMEM_LD32(r, taddr)                                                                                          \
+  asm volatile(                                                                                                         \
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,"  \
+      "%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"                                                        \
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),     \
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),          \
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),         \
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])                       \
+      : "r"(taddr))
+
 struct Epilogue {
   // EPI_FWD: C = act(acc + bias) * dropout
   const float* bias;       // [N], nullable
@@ -283,6 +300,88 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
     mbar_wait(&sm.tmem_full_bar, 0);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    if constexpr (EPI == EPI_UPDATE) {
+      // dW + optimizer.  The tile's weights and optimizer state are a pure read-modify-write stream
+      // (16-24 bytes per element against 2*B flops), so what matters is bytes in flight, and registers
+      // cannot hold enough of them (the register-staged form: 16-24 KB per SM, 1.5-1.9 TB/s).  The
+      // operand ring is idle once the accumulator is complete, so each warp streams its 32 rows through
+      // its quarter of it: chunks of 32 columns x {W, s1, (s2)} arrive by cp.async (rows padded to 36
+      // floats: float4 accesses by row are conflict-free), D chunks in flight; the lane that owns the
+      // accumulator row updates the chunk in place, then the warp copies it out row-contiguously.
+      constexpr int NA = (OPT == 2) ? 3 : 2;
+      constexpr int kRowF = 36, kArrF = 32 * kRowF, kChunkF = NA * kArrF;
+      constexpr int kRingF = kStages * (BM * BK + BN * BK) * (X3 ? 2 : 1);
+      constexpr int NC = BN / 32;
+      constexpr int D = (kRingF / 4 / kChunkF) < NC ? (kRingF / 4 / kChunkF) : NC;
+      static_assert(D >= 1, "operand ring too small for one staged chunk");
+      float* stage = reinterpret_cast<float*>(&sm.a[0][0]) + q * (kRingF / 4);
+      const int rows = min(32, M - (m0 + q * 32));
+      const int lrow = lane >> 3, lc4 = (lane & 7) * 4;
+      const size_t row0 = (size_t)(m0 + q * 32);
+      auto issue = [&](int c) {
+        float* dst = stage + (c % D) * kChunkF + lrow * kRowF + lc4;
+        const int n = n0 + c * 32 + lc4;
+        if (c < NC && n < N) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if (i * 4 + lrow < rows) {
+              const size_t o = (row0 + i * 4 + lrow) * ldc + n;
+              cp16(dst + i * 4 * kRowF, C + o);
+              cp16(dst + kArrF + i * 4 * kRowF, ep.s1 + o);
+              if (OPT == 2) cp16(dst + 2 * kArrF + i * 4 * kRowF, ep.s2 + o);
+            }
+          }
+        }
+        cp_commit();
+      };
+#pragma unroll
+      for (int c = 0; c < D; ++c) issue(c);
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        unsigned r[32];
+        const unsigned taddr = tmem_d + ((unsigned)(q * 32) << 16) + (unsigned)(c * 32);
+        SN_TMEM_LD32(r, taddr);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        cp_wait<D - 1>();
+        __syncwarp();
+        float* slot = stage + (c % D) * kChunkF;
+        if (lane < rows) {
+          float* pw = slot + lane * kRowF;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (n0 + c * 32 + j * 4 < N) {
+              float4 p = *reinterpret_cast<float4*>(pw + j * 4);
+              float4 a = *reinterpret_cast<float4*>(pw + kArrF + j * 4);
+              float4 b = (OPT == 2) ? *reinterpret_cast<float4*>(pw + 2 * kArrF + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+              opt_update<OPT>(ep.op, p.x, __uint_as_float(r[j * 4 + 0]), a.x, b.x);
+              opt_update<OPT>(ep.op, p.y, __uint_as_float(r[j * 4 + 1]), a.y, b.y);
+              opt_update<OPT>(ep.op, p.z, __uint_as_float(r[j * 4 + 2]), a.z, b.z);
+              opt_update<OPT>(ep.op, p.w, __uint_as_float(r[j * 4 + 3]), a.w, b.w);
+              *reinterpret_cast<float4*>(pw + j * 4) = p;
+              *reinterpret_cast<float4*>(pw + kArrF + j * 4) = a;
+              if (OPT == 2) *reinterpret_cast<float4*>(pw + 2 * kArrF + j * 4) = b;
+            }
+          }
+        }
+        __syncwarp();
+        const int n = n0 + c * 32 + lc4;
+        if (n < N) {
+          const float* src = slot + lrow * kRowF + lc4;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if (i * 4 + lrow < rows) {
+              const size_t o = (row0 + i * 4 + lrow) * ldc + n;
+              *reinterpret_cast<float4*>(C + o) = *reinterpret_cast<const float4*>(src + i * 4 * kRowF);
+              *reinterpret_cast<float4*>(ep.s1 + o) = *reinterpret_cast<const float4*>(src + kArrF + i * 4 * kRowF);
+              if (OPT == 2) *reinterpret_cast<float4*>(ep.s2 + o) = *reinterpret_cast<const float4*>(src + 2 * kArrF + i * 4 * kRowF);
+            }
+          }
+        }
+        __syncwarp();
+        issue(c + D);                          // refill the slot just drained (an empty group past the last chunk)
+      }
+      cp_wait<0>();
+    } else {
     // The operand ring is idle once the accumulator is complete: reuse it as a per-warp 32x33
     // transpose tile, so that global accesses are row-contiguous (lane = column) instead of one
     // row per lane.
@@ -291,53 +390,13 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     for (int c0 = 0; c0 < BN; c0 += 32) {
       unsigned r[32];
       const unsigned taddr = tmem_d + ((unsigned)(q * 32) << 16) + (unsigned)c0;
-      asm volatile(
-          "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,"
-          "%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-            "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-            "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-            "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-          : "r"(taddr));
+      SN_TMEM_LD32(r, taddr);
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
       for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(r[j]);     // lane holds row q*32+lane
       __syncwarp();
       const int n = n0 + c0 + lane;                                                // now lane = column
-      if (EPI == EPI_UPDATE) {
-        // dW + optimizer: the tile's weights and optimizer state are a pure read-modify-write stream
-        // (16-24 bytes per element against 2*B flops), so what matters is bytes in flight.  All 32 rows'
-        // loads of a chunk are issued before the first update (the row-at-a-time form kept ~5 KB in
-        // flight per SM and ran the batch-256 step 17x off its HBM floor).
-        if (n < N) {
-          constexpr int RB = 16;                                   // rows per batch of loads
-          const int rows = min(32, M - (m0 + q * 32));
-#pragma unroll 1
-          for (int r0 = 0; r0 < 32; r0 += RB) {
-            float pv[RB], av[RB], bv[OPT == 2 ? RB : 1];
-            float* cp = C + (size_t)(m0 + q * 32 + r0) * ldc + n;
-            float* s1p = ep.s1 + (size_t)(m0 + q * 32 + r0) * ldc + n;
-            float* s2p = (OPT == 2) ? ep.s2 + (size_t)(m0 + q * 32 + r0) * ldc + n : nullptr;
-#pragma unroll
-            for (int rr = 0; rr < RB; ++rr) {
-              const bool ok = r0 + rr < rows;
-              pv[rr] = ok ? cp[(size_t)rr * ldc] : 0.f;
-              av[rr] = ok ? s1p[(size_t)rr * ldc] : 0.f;
-              if (OPT == 2) bv[OPT == 2 ? rr : 0] = ok ? s2p[(size_t)rr * ldc] : 0.f;
-            }
-#pragma unroll
-            for (int rr = 0; rr < RB; ++rr) {
-              if (r0 + rr < rows) {
-                float b2 = (OPT == 2) ? bv[OPT == 2 ? rr : 0] : 0.f;
-                opt_update<OPT>(ep.op, pv[rr], tile[(r0 + rr) * 33 + lane], av[rr], b2);
-                cp[(size_t)rr * ldc] = pv[rr];
-                s1p[(size_t)rr * ldc] = av[rr];
-                if (OPT == 2) s2p[(size_t)rr * ldc] = b2;
-              }
-            }
-          }
-        }
-      } else if (n < N) {
+      if (n < N) {
         const float bias_v = (EPI == EPI_FWD && ep.bias) ? ep.bias[n] : 0.f;
 #pragma unroll 4
         for (int rr = 0; rr < 32; ++rr) {
@@ -366,6 +425,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         }
       }
       __syncwarp();
+    }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }

@@ -68,6 +68,13 @@ int sn_get_skinny_tensor_forward(void);
  * selectable, with its parity tests, as that measured answer.  (No counterpart in the reference.) */
 int sn_set_persistent_tail(int on);
 int sn_get_persistent_tail(void);
+/* Batches of 17..rows rows run their backward as fp32 weight-stream traversals in tiles of 16 with a
+ * gradient buffer (the round-1 form); larger ones as tcgen05 GEMMs with the optimizer in the dW GEMM's
+ * epilogue.  Default 16: the GEMMs are faster from 17 rows up and each is exact to ~1e-6 (the forward
+ * of batches <= 64 stays on the fp32 FMA kernels either way, so no ReLU gate can flip).  rows in
+ * [16, 64]; SN_BWD_TILED_MAX sets the initial value.  (No counterpart in the reference.) */
+int sn_set_bwd_tiled_max(int rows);
+int sn_get_bwd_tiled_max(void);
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 uint64_t sn_launch_count(void);
 

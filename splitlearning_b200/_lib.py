@@ -25,6 +25,8 @@ SIGNATURES = {
     "sn_get_skinny_tensor_forward": (_i, []),
     "sn_set_persistent_tail": (_i, [_i]),
     "sn_get_persistent_tail": (_i, []),
+    "sn_set_bwd_tiled_max": (_i, [_i]),
+    "sn_get_bwd_tiled_max": (_i, []),
     "sn_conv_pool_forward": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "sn_conv_weights_copy": (_i, [_vp, _vp, _vp, _vp, _vp]),
     "sn_conv_pool_backward_scratch_bytes": (_sz, [_i]),

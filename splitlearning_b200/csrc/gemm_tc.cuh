@@ -37,25 +37,33 @@ namespace tc {
 constexpr int BM = 128, BK = 32;                    // BK floats = 128 bytes = one swizzle row
 // tile width BN is a template parameter: 128 (3 stages, two CTAs per SM: one's epilogue overlaps the
 // other's main loop) or 256 (4 stages, one CTA per SM, half the A traffic per flop)
-constexpr int stages_for(int bn, bool x3) { return (bn == 256 && !x3) ? 4 : 3; }
+__host__ __device__ constexpr int stages_for(int bn, bool x3) { return (x3 || bn == 256) ? 4 : 3; }
 constexpr int kTileBytes = BM * BK * 4;             // 16 KB per A tile per stage
 constexpr int kThreads = 192;
 
-// X3 = 3xTF32: every operand tile also has a "lo" twin holding x - trunc_tf32(x), written by the
-// epilogue warps while they wait for the accumulator; D = hi.hi + lo.hi + hi.lo recovers fp32
-// accuracy (~1e-5 relative: the tensor core's own fp32 accumulation is the floor) at 3x the MMAs.
+// X3 = 3xTF32: every operand also has a "lo" twin holding x - trunc_tf32(x); D = lo.hi + hi.lo + hi.hi
+// recovers fp32 accuracy (~1e-5 relative: the tensor core's own fp32 accumulation is the floor) at 3x
+// the MMAs.  Shared-memory bandwidth decides how that runs: a 128x128x8 TF32 MMA with both operands
+// in shared memory reads 8 KB in ~67 clocks, i.e. all of the SM's 128 B/clk by itself; with hi and lo
+// tiles of both operands in shared memory (the first version) a k block of 32 cost 96 KB of MMA
+// reads + 64 KB of twin traffic = 1250 clocks against 800 clocks of tensor time, and measured 1 us.
+// So the M operand goes through TENSOR MEMORY: the four operand warps read each row of the A tile once
+// (thread = row), and write it and its lo twin with tcgen05.st; the MMAs then read only B (and its lo
+// twin) from shared memory - 48 + 48 KB per k block.  The TMEM operand buffer of stage s needs no
+// barrier of its own: the TMA refill of stage s is issued after the MMAs that read it have committed.
 template <bool X3, int BN>
 struct __align__(1024) SmemT {
   static constexpr int kStages = stages_for(BN, X3);
   float a[kStages][BM * BK];
   float b[kStages][BN * BK];
-  float a_lo[X3 ? kStages : 1][X3 ? BM * BK : 4];
   float b_lo[X3 ? kStages : 1][X3 ? BN * BK : 4];
   unsigned long long full_bar[kStages];
   unsigned long long split_bar[kStages];
   unsigned long long empty_bar[kStages];
   unsigned long long tmem_full_bar;
   unsigned tmem_base;
+  // floats of the operand ring (a, b and b_lo are contiguous): the epilogues reuse it as staging space
+  static constexpr int kRingFloats = kStages * (BM * BK + BN * BK * (X3 ? 2 : 1));
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -181,27 +189,57 @@ struct Epilogue {
   OptParams op;
 };
 
+// D[tmem] (+)= A[tmem] * B[smem descriptor]: the M operand comes from tensor memory (lane = row,
+// one 32-bit column per k), so the MMA reads no shared memory for it
+__device__ __forceinline__ void mma_tf32_ts(unsigned tmem_d, unsigned tmem_a, unsigned long long bdesc, unsigned idesc,
+                                            unsigned accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+__device__ __forceinline__ void tmem_st32(unsigned taddr, const unsigned (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,"
+      "%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+      "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]),
+      "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]),
+      "r"(r[31])
+      : "memory");
+}
 __device__ __forceinline__ float tf32_lo(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 
 template <bool AMN, bool BMN, int EPI, int OPT, bool X3, int BN>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, (X3 || BN == 256) ? 1 : 2)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
-                 int K, float* __restrict__ C, int ldc, Epilogue ep) {
+                 int K, float* __restrict__ C, int ldc, Epilogue ep, int kb_per_split, size_t split_stride) {
   extern __shared__ unsigned char smem_raw[];
   using Smem = SmemT<X3, BN>;
   constexpr int kStages = Smem::kStages;
-  constexpr int kTmemCols = BN;                     // fp32 accumulator: 128 lanes x BN columns
+  // fp32 accumulator: 128 lanes x BN columns; X3: + per stage 32 hi and 32 lo columns of the A operand
+  constexpr int kTmemCols = X3 ? 512 : BN;
+  static_assert(!X3 || BN + kStages * 64 <= 512, "A operand buffers do not fit tensor memory");
   Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-  const int kblocks = (K + BK - 1) / BK;
+  // split-K: grid.z slices of kb_per_split k blocks each, slice z writing its partial tile to
+  // C + z * split_stride (the host then launches the reduction as a separate element-wise kernel)
+  const int kb0 = (int)blockIdx.z * kb_per_split;
+  const int kblocks = min((K + BK - 1) / BK - kb0, kb_per_split);
+  C += (size_t)blockIdx.z * split_stride;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&sm.full_bar[s], 1);
-      mbar_init(&sm.split_bar[s], 128);
+      mbar_init(&sm.split_bar[s], 4);               // one arrival per operand warp
       mbar_init(&sm.empty_bar[s], 1);
     }
     mbar_init(&sm.tmem_full_bar, 1);
@@ -228,41 +266,41 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const unsigned ph = (kb / kStages) & 1;
         mbar_wait(&sm.empty_bar[s], ph ^ 1);
         mbar_expect_tx(&sm.full_bar[s], kTileBytes + BN * BK * 4);
-        if (!AMN) tma_load_2d(sm.a[s], &map_a, &sm.full_bar[s], kb * BK, m0);
+        if (!AMN) tma_load_2d(sm.a[s], &map_a, &sm.full_bar[s], (kb0 + kb) * BK, m0);
         else
 #pragma unroll
-          for (int j = 0; j < BM / 32; ++j) tma_load_2d(sm.a[s] + j * 1024, &map_a, &sm.full_bar[s], m0 + 32 * j, kb * BK);
-        if (!BMN) tma_load_2d(sm.b[s], &map_b, &sm.full_bar[s], kb * BK, n0);
+          for (int j = 0; j < BM / 32; ++j) tma_load_2d(sm.a[s] + j * 1024, &map_a, &sm.full_bar[s], m0 + 32 * j, (kb0 + kb) * BK);
+        if (!BMN) tma_load_2d(sm.b[s], &map_b, &sm.full_bar[s], (kb0 + kb) * BK, n0);
         else
 #pragma unroll
-          for (int j = 0; j < BN / 32; ++j) tma_load_2d(sm.b[s] + j * 1024, &map_b, &sm.full_bar[s], n0 + 32 * j, kb * BK);
+          for (int j = 0; j < BN / 32; ++j) tma_load_2d(sm.b[s] + j * 1024, &map_b, &sm.full_bar[s], n0 + 32 * j, (kb0 + kb) * BK);
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      const unsigned idesc = make_idesc_tf32(BM, BN, AMN, BMN);
+      const unsigned idesc = make_idesc_tf32(BM, BN, X3 ? false : AMN, BMN);
       for (int kb = 0; kb < kblocks; ++kb) {
         const int s = kb % kStages;
         const unsigned ph = (kb / kStages) & 1;
-        mbar_wait(X3 ? &sm.split_bar[s] : &sm.full_bar[s], ph);     // X3: the lo tiles are written too
+        mbar_wait(X3 ? &sm.split_bar[s] : &sm.full_bar[s], ph);     // X3: the operand warps have done their part
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const unsigned long long ad = AMN ? make_desc_mnmajor_sw128(sm.a[s]) : make_desc_kmajor_sw128(sm.a[s]);
         const unsigned long long bd = BMN ? make_desc_mnmajor_sw128(sm.b[s]) : make_desc_kmajor_sw128(sm.b[s]);
         // one instruction consumes 8 reduction steps: K-major +32 B (2 x 16 B), MN-major +8 rows of
-        // 128 B (64 x 16 B)
+        // 128 B (64 x 16 B); an operand in tensor memory +8 columns
         constexpr unsigned long long astep = AMN ? 64 : 2, bstep = BMN ? 64 : 2;
         if (!X3) {
+          const unsigned long long ad = AMN ? make_desc_mnmajor_sw128(sm.a[s]) : make_desc_kmajor_sw128(sm.a[s]);
 #pragma unroll
           for (int k = 0; k < BK / 8; ++k)
             mma_tf32(tmem_d, ad + astep * k, bd + bstep * k, idesc, (kb | k) != 0);
         } else {
-          const unsigned long long al = AMN ? make_desc_mnmajor_sw128(sm.a_lo[s]) : make_desc_kmajor_sw128(sm.a_lo[s]);
           const unsigned long long bl = BMN ? make_desc_mnmajor_sw128(sm.b_lo[s]) : make_desc_kmajor_sw128(sm.b_lo[s]);
+          const unsigned a_hi = tmem_d + (unsigned)(BN + s * 64), a_lo = a_hi + 32;
 #pragma unroll
           for (int k = 0; k < BK / 8; ++k) {
-            mma_tf32(tmem_d, al + astep * k, bd + bstep * k, idesc, (kb | k) != 0);   // small terms first
-            mma_tf32(tmem_d, ad + astep * k, bl + bstep * k, idesc, 1);
-            mma_tf32(tmem_d, ad + astep * k, bd + bstep * k, idesc, 1);
+            mma_tf32_ts(tmem_d, a_lo + 8 * k, bd + bstep * k, idesc, (kb | k) != 0);   // small terms first
+            mma_tf32_ts(tmem_d, a_hi + 8 * k, bl + bstep * k, idesc, 1);
+            mma_tf32_ts(tmem_d, a_hi + 8 * k, bd + bstep * k, idesc, 1);
           }
         }
         mma_commit(&sm.empty_bar[s]);          // slot free once these MMAs have read it
@@ -273,29 +311,54 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     // epilogue warps 2..5: TMEM lane quarter = warp % 4
     const int q = warp & 3;
     if (X3) {
-      // while the main loop runs these 128 threads write the lo twins of every stage: same
-      // (swizzled) offsets as the hi tile, so the layout needs no decoding
+      // operand warps: thread = row of the A tile.  It reads its row's 32 reduction values of the stage
+      // (K-major: 8 LDS.128 through the 128-byte swizzle; MN-major: 32 LDS.32, a warp reading one
+      // 128-byte line per value) and writes them and their lo twins into the stage's tensor-memory
+      // operand buffer; the 128 threads together write B's lo twin (same swizzled offsets as the hi
+      // tile, so the layout needs no decoding).
       const int t = threadIdx.x - 64;
+      const int r = q * 32 + lane;
+      const unsigned lane_addr = (unsigned)(q * 32) << 16;
       for (int kb = 0; kb < kblocks; ++kb) {
         const int s = kb % kStages;
         const unsigned ph = (kb / kStages) & 1;
         mbar_wait(&sm.full_bar[s], ph);
-        const float4* ah = reinterpret_cast<const float4*>(sm.a[s]);
+        unsigned hi[32], lo[32];
+        if (!AMN) {
+          const float4* rowp = reinterpret_cast<const float4*>(sm.a[s]) + r * 8;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const float4 v = rowp[c ^ (r & 7)];
+            hi[4 * c + 0] = __float_as_uint(v.x); hi[4 * c + 1] = __float_as_uint(v.y);
+            hi[4 * c + 2] = __float_as_uint(v.z); hi[4 * c + 3] = __float_as_uint(v.w);
+          }
+        } else {
+          // column block q (32 rows of the tile), line kk = reduction index, 32-byte chunks XOR-ed with kk mod 4
+          const float* blk = sm.a[s] + q * 1024;
+#pragma unroll
+          for (int kk = 0; kk < 32; ++kk)
+            hi[kk] = __float_as_uint(blk[kk * 32 + ((((lane >> 3) ^ (kk & 3)) << 3) | (lane & 7))]);
+        }
+#pragma unroll
+        for (int e = 0; e < 32; ++e) lo[e] = __float_as_uint(tf32_lo(__uint_as_float(hi[e])));
         const float4* bh = reinterpret_cast<const float4*>(sm.b[s]);
-        float4* alo = reinterpret_cast<float4*>(sm.a_lo[s]);
         float4* blo = reinterpret_cast<float4*>(sm.b_lo[s]);
-#pragma unroll 4
-        for (int i = t; i < BM * BK / 4; i += 128) {
-          const float4 v = ah[i];
-          alo[i] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
+#pragma unroll
+        for (int i = 0; i < BN * BK / 4 / 128; ++i) {
+          const float4 w = bh[t + 128 * i];
+          blo[t + 128 * i] = make_float4(tf32_lo(w.x), tf32_lo(w.y), tf32_lo(w.z), tf32_lo(w.w));
         }
-#pragma unroll 4
-        for (int i = t; i < BN * BK / 4; i += 128) {
-          const float4 w = bh[i];
-          blo[i] = make_float4(tf32_lo(w.x), tf32_lo(w.y), tf32_lo(w.z), tf32_lo(w.w));
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic-proxy writes -> tensor core reads
-        mbar_arrive(&sm.split_bar[s]);
+        // the operand buffer of stage s was last read by the MMAs of k block kb - kStages; the TMA
+        // load this thread has just seen land was issued after their commit
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const unsigned a_hi = tmem_d + lane_addr + (unsigned)(BN + s * 64);
+        tmem_st32(a_hi, hi);
+        tmem_st32(a_hi + 32, lo);
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // b_lo: generic-proxy writes -> tensor core reads
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.split_bar[s]);
       }
     }
     mbar_wait(&sm.tmem_full_bar, 0);
@@ -310,7 +373,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       // accumulator row updates the chunk in place, then the warp copies it out row-contiguously.
       constexpr int NA = (OPT == 2) ? 3 : 2;
       constexpr int kRowF = 36, kArrF = 32 * kRowF, kChunkF = NA * kArrF;
-      constexpr int kRingF = kStages * (BM * BK + BN * BK) * (X3 ? 2 : 1);
+      constexpr int kRingF = Smem::kRingFloats;
       constexpr int NC = BN / 32;
       constexpr int D = (kRingF / 4 / kChunkF) < NC ? (kRingF / 4 / kChunkF) : NC;
       static_assert(D >= 1, "operand ring too small for one staged chunk");
@@ -384,47 +447,80 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     } else {
     // The operand ring is idle once the accumulator is complete: reuse it as a per-warp 32x33
     // transpose tile, so that global accesses are row-contiguous (lane = column) instead of one
-    // row per lane.
+    // row per lane.  What the element-wise step READS (the ReLU gate of dX, the keep bytes of a forward
+    // under teacher-forced masks) is requested for all 32 rows of a chunk at once, before the chunk's
+    // accumulator is fetched: row-at-a-time it was eight dependent round trips per chunk with nothing
+    // to hide behind (one CTA per SM).
     float* tile = reinterpret_cast<float*>(&sm.a[0][0]) + q * (32 * 33);
-#pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
+    constexpr int NC = BN / 32;
+    const bool has_side = (EPI == EPI_GATE) ? ep.gate != nullptr : ep.mask != nullptr;
+    auto load_side = [&](int c, float (&g)[32]) {
+      const int n = n0 + c * 32 + lane;
+      if (!has_side || c >= NC || n >= N) return;
+#pragma unroll
+      for (int rr = 0; rr < 32; ++rr) {
+        const int row = m0 + q * 32 + rr;
+        if (row < M) {
+          if (EPI == EPI_GATE) g[rr] = ep.gate[(size_t)row * ep.ldgate + n];
+          else g[rr] = (float)ep.mask[(size_t)row * N + n];
+        }
+      }
+    };
+    // one chunk: accumulator columns [32c, 32c+32) -> transpose tile -> element-wise step, row-contiguous stores
+    auto chunk = [&](int c, const float (&g)[32]) {
       unsigned r[32];
-      const unsigned taddr = tmem_d + ((unsigned)(q * 32) << 16) + (unsigned)c0;
+      const unsigned taddr = tmem_d + ((unsigned)(q * 32) << 16) + (unsigned)(c * 32);
       SN_TMEM_LD32(r, taddr);
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
       for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(r[j]);     // lane holds row q*32+lane
       __syncwarp();
-      const int n = n0 + c0 + lane;                                                // now lane = column
+      const int n = n0 + c * 32 + lane;                                            // now lane = column
       if (n < N) {
         const float bias_v = (EPI == EPI_FWD && ep.bias) ? ep.bias[n] : 0.f;
+        if (has_side) {
+#pragma unroll
+          for (int rr = 0; rr < 32; ++rr) {
+            const int row = m0 + q * 32 + rr;
+            if (row < M) {
+              float v = tile[rr * 33 + lane];
+              if (EPI == EPI_FWD) {
+                v += bias_v;
+                if (ep.relu) v = fmaxf(v, 0.f);
+                v = g[rr] != 0.f ? v * ep.scale : 0.f;
+                C[(size_t)row * ldc + n] = v;
+                if (ep.out2) ep.out2[(size_t)row * N + n] = v;
+              } else {
+                C[(size_t)row * ldc + n] = g[rr] > 0.f ? v * ep.scale : 0.f;
+              }
+            }
+          }
+        } else {
 #pragma unroll 4
-        for (int rr = 0; rr < 32; ++rr) {
-          const int row = m0 + q * 32 + rr;
-          if (row >= M) break;
-          float v = tile[rr * 33 + lane];
-          if (EPI == EPI_FWD) {
-            v += bias_v;
-            if (ep.relu) v = fmaxf(v, 0.f);
-            const size_t idx = (size_t)row * N + n;
-            if (ep.mask) v = ep.mask[idx] ? v * ep.scale : 0.f;
-            else if (ep.keep_prob < 1.f) v = philox_keep(ep.seed, ep.offset, ep.layer, idx, ep.keep_prob) ? v * ep.scale : 0.f;
-            C[(size_t)row * ldc + n] = v;
-            if (ep.out2) ep.out2[idx] = v;
-          } else if (EPI == EPI_GATE) {
-            if (ep.gate) v = ep.gate[(size_t)row * ep.ldgate + n] > 0.f ? v * ep.scale : 0.f;
-            C[(size_t)row * ldc + n] = v;
-          } else {
-            const size_t o = (size_t)row * ldc + n;
-            float p = C[o], a = ep.s1[o], b2 = (OPT == 2) ? ep.s2[o] : 0.f;
-            opt_update<OPT>(ep.op, p, v, a, b2);
-            C[o] = p;
-            ep.s1[o] = a;
-            if (OPT == 2) ep.s2[o] = b2;
+          for (int rr = 0; rr < 32; ++rr) {
+            const int row = m0 + q * 32 + rr;
+            if (row >= M) break;
+            float v = tile[rr * 33 + lane];
+            if (EPI == EPI_FWD) {
+              v += bias_v;
+              if (ep.relu) v = fmaxf(v, 0.f);
+              const size_t idx = (size_t)row * N + n;
+              if (ep.keep_prob < 1.f) v = philox_keep(ep.seed, ep.offset, ep.layer, idx, ep.keep_prob) ? v * ep.scale : 0.f;
+              C[(size_t)row * ldc + n] = v;
+              if (ep.out2) ep.out2[idx] = v;
+            } else {
+              C[(size_t)row * ldc + n] = v;
+            }
           }
         }
       }
       __syncwarp();
+    };
+    float side[32];
+#pragma unroll 1
+    for (int c = 0; c < NC; ++c) {
+      load_side(c, side);          // in flight while the accumulator chunk is fetched and transposed
+      chunk(c, side);
     }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -487,30 +583,6 @@ __device__ __forceinline__ void tma_load_2d_hint(void* dst, const CUtensorMap* m
       : "memory");
 }
 
-// D[tmem] (+)= A[tmem] * B[smem descriptor]: the M operand comes from tensor memory (lane = row,
-// one 32-bit column per k), so the MMA reads no shared memory for it
-__device__ __forceinline__ void mma_tf32_ts(unsigned tmem_d, unsigned tmem_a, unsigned long long bdesc, unsigned idesc,
-                                            unsigned accumulate) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "setp.ne.b32 p, %4, 0;\n"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n"
-      "}\n" ::"r"(tmem_d),
-      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-
-__device__ __forceinline__ void tmem_st32(unsigned taddr, const unsigned (&r)[32]) {
-  asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,"
-      "%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr),
-      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
-      "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]),
-      "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]),
-      "r"(r[31])
-      : "memory");
-}
 __device__ __forceinline__ void tmem_ld16(unsigned taddr, unsigned (&v)[16]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"

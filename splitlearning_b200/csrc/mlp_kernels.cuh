@@ -1383,6 +1383,31 @@ __global__ void bwd_epilogue_kernel(const float* __restrict__ PA, int nsplit, in
                     first_cols);
 }
 
+// dst[b][k..k+3] = (sum_s P[s][b][k..]) gated by H (nullable) - the reduction behind a split-K dX GEMM
+// (K % 4 == 0; slices are dense [B][K] slabs `slab` floats apart; fixed add order)
+__global__ void splitk_gate_kernel(const float* __restrict__ P, int nsplit, size_t slab, int B, int K,
+                                   const float* __restrict__ H, int ldh, float scale, float* __restrict__ dst, int ldd) {
+  pdl_wait();
+  pdl_launch();
+  const size_t total4 = (size_t)B * K / 4;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t e = i * 4;
+    const int b = (int)(e / K), k = (int)(e - (size_t)b * K);
+    float4 hv = make_float4(1.f, 1.f, 1.f, 1.f);
+    if (H) hv = *reinterpret_cast<const float4*>(H + (size_t)b * ldh + k);
+    float4 acc = __ldcg(reinterpret_cast<const float4*>(P + e));
+    for (int s = 1; s < nsplit; ++s) {
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(P + s * slab + e));
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    if (H) {
+      acc.x = hv.x > 0.f ? acc.x * scale : 0.f; acc.y = hv.y > 0.f ? acc.y * scale : 0.f;
+      acc.z = hv.z > 0.f ? acc.z * scale : 0.f; acc.w = hv.w > 0.f ? acc.w * scale : 0.f;
+    }
+    *reinterpret_cast<float4*>(dst + (size_t)b * ldd + k) = acc;
+  }
+}
+
 // dst = src * (out > 0)  (ReLU on the last layer, U-shape model2)
 __global__ void relu_gate_kernel(const float* __restrict__ src, const float* __restrict__ out, size_t n,
                                  float* __restrict__ dst) {

@@ -55,11 +55,20 @@ static int fwd_rows() {
   return r;
 }
 
-// largest batch whose backward still goes through the fp32 traversal in tiles of 16 rows with a
-// gradient buffer (above it: tcgen05 GEMMs); SN_BWD_TILED_MAX overrides, for the config-5 sweep
+// largest batch whose backward goes through the fp32 traversal in tiles of 16 rows with a gradient
+// buffer; above it: tcgen05 GEMMs (3xTF32, each exact to ~1e-6).  Default 16, i.e. the tiled form is
+// off: since the dW GEMM's optimizer epilogue streams through shared memory the GEMMs win from 17 rows
+// up (H 8192: 0.46 vs 0.67 ms at 32 rows, 0.60 vs 1.12 ms at 64).  sn_set_bwd_tiled_max /
+// SN_BWD_TILED_MAX (<= 64) bring it back for A/B runs and its parity test.
+std::atomic<int> g_bwd_tiled_max{-1};
 static int bwd_tiled_max() {
-  static const int v = getenv("SN_BWD_TILED_MAX") ? atoi(getenv("SN_BWD_TILED_MAX")) : kSkinnyFwdMaxB;
-  return std::min(v, kSkinnyFwdMaxB);
+  int v = g_bwd_tiled_max.load();
+  if (v < 0) {
+    v = getenv("SN_BWD_TILED_MAX") ? atoi(getenv("SN_BWD_TILED_MAX")) : kBT;
+    v = std::max(kBT, std::min(v, kSkinnyFwdMaxB));
+    g_bwd_tiled_max.store(v);
+  }
+  return v;
 }
 
 static FwdPlan plan_fwd(int K, int N, int sms) {
@@ -233,29 +242,43 @@ static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t 
 // MN-major = [R, extent] row-major; lda/ldb are the row strides of those matrices.
 template <bool AMN, bool BMN, int EPI, int OPT, bool X3, int BN>
 static int launch_tc_gemm_p(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
-                            const tc::Epilogue& ep, cudaStream_t st) {
+                            const tc::Epilogue& ep, cudaStream_t st, int splits = 1, size_t split_stride = 0) {
   CUtensorMap ma, mb;
   if (AMN ? tc::make_map(&ma, A, R, M, lda, 32, true) : tc::make_map(&ma, A, M, R, lda, tc::BM)) return 1;
   if (BMN ? tc::make_map(&mb, Bm, R, N, ldb, 32, true) : tc::make_map(&mb, Bm, N, R, ldb, BN)) return 1;
   auto kern = tc::gemm_tf32_kernel<AMN, BMN, EPI, OPT, X3, BN>;
   if (set_smem(kern, tc::smem_bytes<X3, BN>())) return 1;
-  dim3 grid(ceil_div(N, BN), ceil_div(M, tc::BM));
-  launch_k(kern, grid, dim3(tc::kThreads), tc::smem_bytes<X3, BN>(), st, ma, mb, M, N, R, C, ldc, ep);
+  const int kblocks = ceil_div(R, tc::BK);
+  const int per = ceil_div(kblocks, std::max(1, splits));
+  dim3 grid(ceil_div(N, BN), ceil_div(M, tc::BM), ceil_div(kblocks, per));
+  launch_k(kern, grid, dim3(tc::kThreads), tc::smem_bytes<X3, BN>(), st, ma, mb, M, N, R, C, ldc, ep, per, split_stride);
   SN_LAUNCH_CHECK();
   return 0;
 }
 // precision 1 = TF32 (one pass), anything else that reaches here = 3xTF32 (fp32-accurate)
 template <bool AMN, bool BMN, int EPI, int OPT>
 static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
-                          const tc::Epilogue& ep, cudaStream_t st) {
+                          const tc::Epilogue& ep, cudaStream_t st, int splits = 1, size_t split_stride = 0) {
   if (g_matmul_precision.load() == 1) {
     // wide tiles once there is enough work to fill the SMs with them (SN_TC_BN=128 forces narrow)
     static const bool wide_ok = !(getenv("SN_TC_BN") && atoi(getenv("SN_TC_BN")) == 128);
     if (wide_ok && (long long)ceil_div(N, 256) * ceil_div(M, tc::BM) >= 148 && R >= 256)
-      return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false, 256>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
-    return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
+      return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false, 256>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
+    return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
   }
-  return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
+  return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
+}
+
+// Split-K for GEMMs whose output has too few 128x128 tiles to occupy the SMs (a narrow layer at a
+// moderate batch: 26 tiles for [256 x 1636]): number of reduction slices, each at least 8 k blocks deep.
+// The slices write raw partial tiles; an element-wise launch adds them and applies the epilogue.
+static int plan_splitk(int M, int N, int R, int sms, size_t scratch_floats) {
+  static const bool off = getenv("SN_NO_SPLITK") && atoi(getenv("SN_NO_SPLITK")) == 1;
+  const int tiles = ceil_div(M, tc::BM) * ceil_div(N, 128), kblocks = ceil_div(R, tc::BK);
+  if (off || tiles * 2 > sms) return 1;
+  int s = std::min(sms / tiles, kblocks / 8);
+  while (s > 1 && (size_t)s * M * N > scratch_floats) --s;
+  return std::max(1, s);
 }
 
 // tcgen05 skinny forward (gemm_tc.cuh): grid and partial-slot count for a [N x K] layer
@@ -297,7 +320,7 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
                              uint64_t offset, int layer, float* H, int ldh, float* out2, float* P, int sms,
                              cudaStream_t st, Profiler* prof = nullptr, const CeTail* ce = nullptr,
                              bool* ce_fused = nullptr, int l2_keep_w = 0, bool prefetch_w = false,
-                             int skinny_max = kSkinnyFwdMaxB) {
+                             int skinny_max = kSkinnyFwdMaxB, float* sk = nullptr, size_t sk_floats = 0) {
   // skinny_max: batches up to this many rows go through the fp32 weight-stream kernels in row tiles
   // of 16 (every row's arithmetic is then independent of the batch it arrives in)
   if (ce_fused) *ce_fused = false;
@@ -353,7 +376,20 @@ static int launch_linear_fwd(const float* X, int ldx, int B, const float* W, con
     ep.bias = bias; ep.relu = relu; ep.mask = mask; ep.keep_prob = keep_prob; ep.scale = scale;
     ep.seed = seed; ep.offset = offset; ep.layer = layer; ep.out2 = out2;
     cudaEvent_t pe = prof ? prof->begin(st, 0, layer) : nullptr;
-    int rc = launch_tc_gemm<false, false, tc::EPI_FWD, 0>(X, ldx, B, W, K, N, K, H, ldh, ep, st);
+    const int splits = sk ? plan_splitk(B, N, K, sms, sk_floats) : 1;
+    int rc;
+    if (splits > 1) {
+      tc::Epilogue raw{};
+      rc = launch_tc_gemm<false, false, tc::EPI_GATE, 0>(X, ldx, B, W, K, N, K, sk, N, raw, st, splits, (size_t)B * N);
+      if (!rc) {
+        const int nsl = ceil_div(ceil_div(K, tc::BK), ceil_div(ceil_div(K, tc::BK), splits));
+        launch_k(fwd_epilogue_kernel, dim3(ew_grid((size_t)B * N, sms)), dim3(256), 0, st, sk, nsl, B, B, N, bias, relu, mask, keep_prob,
+                 scale, seed, offset, layer, H, ldh, out2, 0, 0);
+        SN_LAUNCH_CHECK();
+      }
+    } else {
+      rc = launch_tc_gemm<false, false, tc::EPI_FWD, 0>(X, ldx, B, W, K, N, K, H, ldh, ep, st);
+    }
     Profiler::end(pe, st);
     if (rc) return rc;
   } else {
@@ -417,6 +453,8 @@ struct sn_bob {
   float* P = nullptr;          // forward split-K partials
   int stream_rows = kSkinnyFwdMaxB;   // forward batches up to this many rows use the weight-stream kernels
   float* PA = nullptr;         // backward dA partials
+  float* SK = nullptr;         // split-K partial tiles of the tcgen05 GEMMs (max_batch > 16)
+  size_t SK_floats = 0;
   size_t PA_floats = 0;
   float* dWbuf = nullptr;      // general-batch path only (lazy)
   float* row_loss = nullptr;
@@ -525,6 +563,12 @@ int sn_set_persistent_tail(int on) {
   return 0;
 }
 int sn_get_persistent_tail(void) { return tail_enabled() ? 1 : 0; }
+int sn_set_bwd_tiled_max(int rows) {
+  SN_REQUIRE(rows >= kBT && rows <= kSkinnyFwdMaxB, "sn_set_bwd_tiled_max: rows must be in [16, 64]");
+  g_bwd_tiled_max.store(rows);
+  return 0;
+}
+int sn_get_bwd_tiled_max(void) { return bwd_tiled_max(); }
 const char* sn_last_error(void) { return g_last_error.c_str(); }
 uint64_t sn_launch_count(void) { return g_launches.load(); }
 
@@ -737,6 +781,11 @@ int sn_bob_create(sn_bob** out, int device, const int* dims, int n_layers, int r
   }
   if ((e = cudaMalloc(&h->P, p_floats * 4)) != cudaSuccess) return fail_free(e);
   if ((e = cudaMalloc(&h->PA, pa_floats * 4)) != cudaSuccess) return fail_free(e);
+  if (max_batch > kBT) {
+    // a split GEMM has at most sms / slices tiles, so sms full tiles hold any set of partials
+    h->SK_floats = (size_t)h->sms * tc::BM * 128;
+    if ((e = cudaMalloc(&h->SK, h->SK_floats * 4)) != cudaSuccess) return fail_free(e);
+  }
   h->row_loss_rows = h->Bpad;
   if ((e = cudaMalloc(&h->row_loss, (size_t)h->Bpad * 4)) != cudaSuccess) return fail_free(e);
   if ((e = cudaMalloc(&h->ticket, 256)) != cudaSuccess) return fail_free(e);
@@ -772,6 +821,7 @@ int sn_bob_destroy(sn_bob* h) {
   for (auto p : h->dZ) cudaFree(p);
   cudaFree(h->P);
   cudaFree(h->PA);
+  cudaFree(h->SK);
   cudaFree(h->dWbuf);
   cudaFree(h->PF);
   cudaFree(h->Ptail);
@@ -917,7 +967,7 @@ static int bob_forward_impl(sn_bob* h, const float* act, int B, int train, const
     } else if (launch_linear_fwd(X, ldx, B, h->W[l], h->b[l], K, N, relu, mask, kp, scale, seed, offset, l, h->H[l + 1], N,
                                  last ? out : nullptr, h->P, h->sms, st, &h->prof, last ? ce : nullptr,
                                  last ? ce_fused : nullptr, h->l2_keep[l], !just_written(h->W[l], (size_t)N * K * 4),
-                                 skinny_max))
+                                 skinny_max, h->SK, h->SK_floats))
       return 1;
     X = h->H[l + 1];
     ldx = N;
@@ -1084,7 +1134,20 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         tc::Epilogue ep{};
         ep.gate = gateH; ep.ldgate = K; ep.scale = gscale;
         cudaEvent_t pe = h->prof.begin(st, 2, l);
-        int rc = launch_tc_gemm<false, true, tc::EPI_GATE, 0>(dZ, N, B, h->W[l], K, K, N, dst, K, ep, st);
+        const int splits = h->SK ? plan_splitk(B, K, N, h->sms, h->SK_floats) : 1;
+        int rc;
+        if (splits > 1) {
+          tc::Epilogue raw{};
+          rc = launch_tc_gemm<false, true, tc::EPI_GATE, 0>(dZ, N, B, h->W[l], K, K, N, h->SK, K, raw, st, splits, (size_t)B * K);
+          if (!rc) {
+            const int nsl = ceil_div(ceil_div(N, tc::BK), ceil_div(ceil_div(N, tc::BK), splits));
+            launch_k(splitk_gate_kernel, dim3(ew_grid((size_t)B * K / 4, h->sms)), dim3(256), 0, st, h->SK, nsl, (size_t)B * K, B, K, gateH,
+                     K, gscale, dst, K);
+            SN_LAUNCH_CHECK();
+          }
+        } else {
+          rc = launch_tc_gemm<false, true, tc::EPI_GATE, 0>(dZ, N, B, h->W[l], K, K, N, dst, K, ep, st);
+        }
         Profiler::end(pe, st);
         if (rc) return rc;
       }

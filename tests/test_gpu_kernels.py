@@ -408,21 +408,22 @@ def test_ushape_steps(eng):
         check_summary(g, f"s{step}_new_m1.conv1.weight", gw, TOL)
 
 
-@pytest.mark.parametrize("mode", [0, 2])
-def test_general_batch_path_matches_oracle(eng, mode):
+@pytest.mark.parametrize("mode,width", [(0, 256), (2, 256), (0, 1024)])
+def test_general_batch_path_matches_oracle(eng, mode, width):
     """B > 16 takes the general-batch kernels - 3xTF32 tcgen05 GEMMs by default (mode 0), the fp32
-    SIMT fallback in mode 2; same oracle, same 1e-4 bound, small widths."""
+    SIMT fallback in mode 2; same oracle, same 1e-4 bound, small widths.  At these sizes the forward
+    GEMMs are split along K (few output tiles); width 1024 also splits the input-gradient GEMM."""
     eng.set_matmul_precision(mode)
     try:
-        _general_batch_body(eng, mode)
+        _general_batch_body(eng, mode, width)
     finally:
         eng.set_matmul_precision(0)
 
 
-def _general_batch_body(eng, mode):
+def _general_batch_body(eng, mode, width):
     rng = np.random.RandomState(77)
-    dims = [5408, 256, 52, 100]
-    shapes = [(256, 5408), (256,), (52, 256), (52,), (100, 52), (100,)]
+    dims = [5408, width, 52, 100]
+    shapes = [(width, 5408), (width,), (52, width), (52,), (100, 52), (100,)]
     b = T(seeded_weights(shapes, 21))
     spec = R.BobSpec(tuple(dims), False, 0.5)
     gp = [cu(p.numpy()) for p in b]
@@ -431,7 +432,7 @@ def _general_batch_body(eng, mode):
     for step, B in enumerate([80, 48]):
         act = (rng.rand(B, 5408) * 40 * (rng.rand(B, 5408) < 0.6)).astype(np.float32)
         y = rng.randint(0, 10, size=B).astype(np.int64)
-        masks = seeded_masks(B, (256, 52), 50 + step)
+        masks = seeded_masks(B, (width, 52), 50 + step)
         bl = [p.detach().clone().requires_grad_(True) for p in b]
         at = torch.from_numpy(act).requires_grad_(True)
         logits_ref = R.bob_forward(at, bl, spec, T(masks))
@@ -671,12 +672,25 @@ def test_skinny_forward_on_tensor_cores_matches_fma_kernel(eng):
         assert rel_err(tc, ref) <= 1e-5                 # 3xTF32 + fp32 tensor-core accumulation
 
 
+@pytest.mark.parametrize("tiled", [False, True])
 @pytest.mark.parametrize("B", [17, 33, 64])
-def test_mid_batch_tiled_backward_sgd(eng, B):
-    """17..64 rows go through the fp32 weight-stream kernels in tiles of 16 with the per-tile dW
-    added into a gradient buffer (OPT=3) and one optimizer pass at the end: one SGD-momentum step
-    (momentum buffers pre-loaded) against the oracle, including a ragged last tile and the cut
-    gradient; then a second step to see the buffer is re-armed."""
+def test_mid_batch_backward_sgd(eng, B, tiled):
+    """17..64 rows: the forward stays on the fp32 weight-stream kernels (row tiles of 16); the backward
+    runs as tcgen05 GEMMs with the optimizer in the dW GEMM's epilogue (default), or - tiled - as fp32
+    traversals in tiles of 16 with the per-tile dW added into a gradient buffer (OPT=3) and one optimizer
+    pass at the end.  One SGD-momentum step (momentum buffers pre-loaded) against the oracle, including
+    a ragged last tile and the cut gradient; then a second step to see the buffers are re-armed."""
+    from splitlearning_b200 import _lib
+    lib = _lib.load()
+    was = lib.sn_get_bwd_tiled_max()
+    _lib.check(lib.sn_set_bwd_tiled_max(64 if tiled else 16))
+    try:
+        _mid_batch_body(eng, B)
+    finally:
+        _lib.check(lib.sn_set_bwd_tiled_max(was))
+
+
+def _mid_batch_body(eng, B):
     rng = np.random.RandomState(B)
     dims = [5408, 320, 60, 100]
     shapes = [(320, 5408), (320,), (60, 320), (60,), (100, 60), (100,)]
@@ -693,9 +707,11 @@ def test_mid_batch_tiled_backward_sgd(eng, B):
         at = torch.from_numpy(act).requires_grad_(True)
         loss_ref = R.cross_entropy(R.bob_forward(at, bl, spec, T(masks)), torch.from_numpy(y))
         loss_ref.backward()
+        w_old = [p.clone() for p in b]
         R.sgd_momentum_(b, [p.grad for p in bl], opt, 1e-3, 0.9)
         loss, cut, _ = bob.train_step(cu(act), cu(y), masks=[cu(m) for m in masks])
         assert abs(loss.item() - loss_ref.item()) <= TOL * abs(loss_ref.item())
         assert rel_err(cut.cpu(), at.grad) <= TOL
-        for p_ref, p in zip(b, gp):
+        for p_ref, p, p0 in zip(b, gp, w_old):
             assert rel_err(p.cpu(), p_ref) <= 1e-5
+            assert rel_err(p.cpu() - p0, p_ref - p0) <= TOL          # the applied step itself

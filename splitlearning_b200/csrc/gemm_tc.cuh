@@ -51,9 +51,9 @@ constexpr int kThreads = 192;
 // (thread = row), and write it and its lo twin with tcgen05.st; the MMAs then read only B (and its lo
 // twin) from shared memory - 48 + 48 KB per k block.  The TMEM operand buffer of stage s needs no
 // barrier of its own: the TMA refill of stage s is issued after the MMAs that read it have committed.
-template <bool X3, int BN>
+template <bool X3, int BN, int STG = stages_for(BN, X3)>
 struct __align__(1024) SmemT {
-  static constexpr int kStages = stages_for(BN, X3);
+  static constexpr int kStages = STG;
   float a[kStages][BM * BK];
   float b[kStages][BN * BK];
   float b_lo[X3 ? kStages : 1][X3 ? BN * BK : 4];
@@ -215,15 +215,18 @@ __device__ __forceinline__ void tmem_st32(unsigned taddr, const unsigned (&r)[32
 }
 __device__ __forceinline__ float tf32_lo(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 
-template <bool AMN, bool BMN, int EPI, int OPT, bool X3, int BN>
-__global__ void __launch_bounds__(kThreads, (X3 || BN == 256) ? 1 : 2)
+// STG = ring depth.  The 3xTF32 dW + optimizer form runs with STG = 2: half the shared memory and half
+// the tensor memory per CTA, so two CTAs share an SM and one's read-modify-write epilogue (most of
+// its time: the reduction is only `batch` deep) overlaps the other's main loop.
+template <bool AMN, bool BMN, int EPI, int OPT, bool X3, int BN, int STG>
+__global__ void __launch_bounds__(kThreads, ((X3 && STG > 2) || BN == 256) ? 1 : 2)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
                  int K, float* __restrict__ C, int ldc, Epilogue ep, int kb_per_split, size_t split_stride) {
   extern __shared__ unsigned char smem_raw[];
-  using Smem = SmemT<X3, BN>;
+  using Smem = SmemT<X3, BN, STG>;
   constexpr int kStages = Smem::kStages;
   // fp32 accumulator: 128 lanes x BN columns; X3: + per stage 32 hi and 32 lo columns of the A operand
-  constexpr int kTmemCols = X3 ? 512 : BN;
+  constexpr int kTmemCols = !X3 ? BN : (BN + kStages * 64 <= 256 ? 256 : 512);
   static_assert(!X3 || BN + kStages * 64 <= 512, "A operand buffers do not fit tensor memory");
   Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -832,8 +835,8 @@ inline bool usable(const float* A, int lda, const float* B, int ldb, int K) {
   return (K % 4) == 0 && (lda % 4) == 0 && (ldb % 4) == 0 && ((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0;
 }
 
-template <bool X3, int BN>
-constexpr size_t smem_bytes() { return sizeof(SmemT<X3, BN>) + 1024; }
+template <bool X3, int BN, int STG = stages_for(BN, X3)>
+constexpr size_t smem_bytes() { return sizeof(SmemT<X3, BN, STG>) + 1024; }
 
 }  // namespace tc
 }  // namespace sn

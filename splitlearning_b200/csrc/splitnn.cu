@@ -240,18 +240,19 @@ static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t 
 // ---------------------------------------------------------------- shared launch helpers
 // C[M,N] (+epilogue) = sum_r A(m,r) B(n,r).  Operand memory: K-major = [extent, R] row-major,
 // MN-major = [R, extent] row-major; lda/ldb are the row strides of those matrices.
-template <bool AMN, bool BMN, int EPI, int OPT, bool X3, int BN>
+template <bool AMN, bool BMN, int EPI, int OPT, bool X3, int BN, int STG = tc::stages_for(BN, X3)>
 static int launch_tc_gemm_p(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
                             const tc::Epilogue& ep, cudaStream_t st, int splits = 1, size_t split_stride = 0) {
   CUtensorMap ma, mb;
   if (AMN ? tc::make_map(&ma, A, R, M, lda, 32, true) : tc::make_map(&ma, A, M, R, lda, tc::BM)) return 1;
   if (BMN ? tc::make_map(&mb, Bm, R, N, ldb, 32, true) : tc::make_map(&mb, Bm, N, R, ldb, BN)) return 1;
-  auto kern = tc::gemm_tf32_kernel<AMN, BMN, EPI, OPT, X3, BN>;
-  if (set_smem(kern, tc::smem_bytes<X3, BN>())) return 1;
+  auto kern = tc::gemm_tf32_kernel<AMN, BMN, EPI, OPT, X3, BN, STG>;
+  constexpr size_t smem = tc::smem_bytes<X3, BN, STG>();
+  if (set_smem(kern, smem)) return 1;
   const int kblocks = ceil_div(R, tc::BK);
   const int per = ceil_div(kblocks, std::max(1, splits));
   dim3 grid(ceil_div(N, BN), ceil_div(M, tc::BM), ceil_div(kblocks, per));
-  launch_k(kern, grid, dim3(tc::kThreads), tc::smem_bytes<X3, BN>(), st, ma, mb, M, N, R, C, ldc, ep, per, split_stride);
+  launch_k(kern, grid, dim3(tc::kThreads), smem, st, ma, mb, M, N, R, C, ldc, ep, per, split_stride);
   SN_LAUNCH_CHECK();
   return 0;
 }
@@ -265,6 +266,11 @@ static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int l
     if (wide_ok && (long long)ceil_div(N, 256) * ceil_div(M, tc::BM) >= 148 && R >= 256)
       return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false, 256>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
     return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
+  }
+  if constexpr (EPI == tc::EPI_UPDATE) {
+    // two CTAs per SM with a 2-deep ring each (SN_DW_STAGES=4: one CTA with a 4-deep ring)
+    static const bool deep = getenv("SN_DW_STAGES") && atoi(getenv("SN_DW_STAGES")) == 4;
+    if (!deep) return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128, 2>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
   }
   return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
 }

@@ -3,8 +3,8 @@ optimizer) over batch and hidden width, Bob dims [5408, H, H/5 (rounded to 4), 1
 
 One GPU:   python profiles/sweep.py [--quick] > profiles/r2_sweep.jsonl
     Every batch size is run at REFERENCE PRECISION - the credited column ("credited": true): the fp32
-    weight-stream kernels up to 64 rows, 3xTF32 on tcgen05 above (fp32-accurate, inside the 1e-4
-    parity bound).  Batches >= 128 are also run in one-pass TF32 ("credited": false: 5e-4 on the
+    weight-stream kernels up to 16 rows; 17..64 rows the fp32 forward and 3xTF32 tcgen05 GEMMs for the
+    backward; 3xTF32 on tcgen05 throughout above that (fp32-accurate, inside the 1e-4 parity bound).  Batches >= 128 are also run in one-pass TF32 ("credited": false: 5e-4 on the
     logits, outside the bound; shown as the tensor-pipe ceiling only).
     Per point: time per step, samples/s, model TFLOP/s (6*P_w*B) and the fraction of the
     relevant roofline: HBM (16*P bytes per step, SGD) for the weight-streaming regime, TF32 tensor
@@ -61,11 +61,19 @@ def run_point(B, H, mode, steps):
     return dims, pw, ms, float(loss.item())
 
 
+def precision_name(B, mode):
+    if mode:
+        return "tf32-tcgen05"
+    if B <= 16:
+        return "fp32"
+    return "fp32-forward+3xtf32-backward" if B <= 64 else "3xtf32-tcgen05"
+
+
 def main():
     quick = "--quick" in sys.argv
     hbm, tf32_peak, src = peaks()
     Hs = [256, 1024, 4096, 8192] if quick else [256, 512, 1024, 2048, 4096, 8192]
-    Bs = [16, 64, 256, 1024, 4096] if quick else [16, 64, 256, 1024, 4096, 16384, 65536]
+    Bs = [16, 64, 256, 1024, 4096] if quick else [16, 32, 64, 256, 1024, 4096, 16384, 65536]
     for H in Hs:
         for B in Bs:
             for mode in ([0] if B < 128 else [0, 1]):
@@ -80,7 +88,7 @@ def main():
                 flops = 6.0 * pw * B
                 tfl = flops / (ms * 1e-3) / 1e12
                 gbs = 16.0 * pw / (ms * 1e-3) / 1e9
-                prec = "tf32-tcgen05" if mode else ("fp32" if B <= 64 else "3xtf32-tcgen05")
+                prec = precision_name(B, mode)
                 print(json.dumps({"B": B, "H": H, "dims": dims, "precision": prec, "credited": mode == 0,
                                   "ms_per_step": round(ms, 4), "samples_per_s": round(B / (ms * 1e-3), 1),
                                   "tflops": round(tfl, 2), "frac_tf32_peak": round(tfl / tf32_peak, 4),
@@ -96,7 +104,7 @@ def point_record(B, H, mode, steps=None):
     dims, pw, ms, loss = run_point(B, H, mode, steps)
     tfl = 6.0 * pw * B / (ms * 1e-3) / 1e12
     gbs = 16.0 * pw / (ms * 1e-3) / 1e9
-    return {"B": B, "H": H, "precision": "tf32-tcgen05" if mode else ("fp32" if B <= 64 else "3xtf32-tcgen05"),
+    return {"B": B, "H": H, "precision": precision_name(B, mode),
             "credited": mode == 0, "ms_per_step": round(ms, 4), "samples_per_s": round(B / (ms * 1e-3), 1),
             "tflops": round(tfl, 2), "frac_tf32_peak": round(tfl / tf32_peak, 4), "frac_hbm": round(gbs / hbm, 4)}
 

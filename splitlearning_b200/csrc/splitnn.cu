@@ -271,6 +271,13 @@ static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int l
     // two CTAs per SM with a 2-deep ring each (SN_DW_STAGES=4: one CTA with a 4-deep ring)
     static const bool deep = getenv("SN_DW_STAGES") && atoi(getenv("SN_DW_STAGES")) == 4;
     if (!deep) return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128, 2>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
+  } else {
+    // the same pairing pays for the other forms once the grid is several waves deep (batch 4096, H 8192:
+    // 186 -> 220 TFLOP/s); on a grid of one or two waves it only halves the SMs in use
+    static const int force = getenv("SN_X3_STAGES") ? atoi(getenv("SN_X3_STAGES")) : 0;
+    const long long ctas = (long long)ceil_div(N, 128) * ceil_div(M, tc::BM) * std::max(1, splits);
+    if (force == 2 || (force == 0 && ctas >= 4LL * 148))
+      return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128, 2>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
   }
   return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
 }

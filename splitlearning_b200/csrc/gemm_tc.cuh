@@ -213,24 +213,72 @@ __device__ __forceinline__ void tmem_st32(unsigned taddr, const unsigned (&r)[32
       "r"(r[31])
       : "memory");
 }
+// ---- CTA pairs (cta_group::2): two CTAs of a 2-cluster on one TPC run ONE 256-row MMA; each holds its
+// 128 rows of A (here: in its tensor memory) and HALF of the B tile in its shared memory, and each
+// half is read once for both tensor cores.  Only the pair's rank-0 CTA issues MMAs and commits.
+__device__ __forceinline__ unsigned cluster_ctarank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(unsigned long long* bar, unsigned rank) {
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(rank)
+      : "memory");
+}
+__device__ __forceinline__ void mma_tf32_ts_pair(unsigned tmem_d, unsigned tmem_a, unsigned long long bdesc, unsigned idesc,
+                                                 unsigned accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0u)
+      : "memory");
+}
+// completion of the pair's MMAs so far -> one arrival on the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void mma_commit_pair(unsigned long long* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                   smem_u32(bar)),
+               "h"((unsigned short)3)
+               : "memory");
+}
+
 __device__ __forceinline__ float tf32_lo(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 
 // STG = ring depth.  The 3xTF32 dW + optimizer form runs with STG = 2: half the shared memory and half
 // the tensor memory per CTA, so two CTAs share an SM and one's read-modify-write epilogue (most of
 // its time: the reduction is only `batch` deep) overlaps the other's main loop.
-template <bool AMN, bool BMN, int EPI, int OPT, bool X3, int BN, int STG>
+// CG = 2 (3xTF32 only): CTA pairs, 256 x 256 output tile per pair; BN is the accumulator width (256),
+// each CTA stages BN / 2 columns of B.  Launched as clusters of (2,1,1): blockIdx.x = row tile of 128.
+template <bool AMN, bool BMN, int EPI, int OPT, bool X3, int BN, int STG, int CG = 1>
 __global__ void __launch_bounds__(kThreads, ((X3 && STG > 2) || BN == 256) ? 1 : 2)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
                  int K, float* __restrict__ C, int ldc, Epilogue ep, int kb_per_split, size_t split_stride) {
   extern __shared__ unsigned char smem_raw[];
-  using Smem = SmemT<X3, BN, STG>;
+  static_assert(CG == 1 || (CG == 2 && X3 && BN == 256), "CTA pairs: 3xTF32, 256-wide accumulator");
+  constexpr int BNS = BN / CG;                      // columns of B staged by this CTA
+  using Smem = SmemT<X3, BNS, STG>;
   constexpr int kStages = Smem::kStages;
   // fp32 accumulator: 128 lanes x BN columns; X3: + per stage 32 hi and 32 lo columns of the A operand
   constexpr int kTmemCols = !X3 ? BN : (BN + kStages * 64 <= 256 ? 256 : 512);
   static_assert(!X3 || BN + kStages * 64 <= 512, "A operand buffers do not fit tensor memory");
   Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const unsigned rank = CG == 2 ? cluster_ctarank() : 0u;
+  const int m0 = (CG == 2 ? blockIdx.x : blockIdx.y) * BM, n0 = (CG == 2 ? blockIdx.y : blockIdx.x) * BN;
+  const int nb0 = n0 + (int)rank * BNS;             // first B column this CTA stages
   // split-K: grid.z slices of kb_per_split k blocks each, slice z writing its partial tile to
   // C + z * split_stride (the host then launches the reduction as a separate element-wise kernel)
   const int kb0 = (int)blockIdx.z * kb_per_split;
@@ -242,20 +290,27 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&sm.full_bar[s], 1);
-      mbar_init(&sm.split_bar[s], 4);               // one arrival per operand warp
+      mbar_init(&sm.split_bar[s], 4 * CG);          // one arrival per operand warp (of both CTAs of a pair)
       mbar_init(&sm.empty_bar[s], 1);
     }
     mbar_init(&sm.tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 1) {   // one warp allocates TMEM and later frees it
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)),
-                 "r"(kTmemCols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  if (warp == 1) {   // one warp allocates TMEM and later frees it (pairs: the same warp of both CTAs)
+    if (CG == 2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)),
+                   "r"(kTmemCols)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)),
+                   "r"(kTmemCols)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const unsigned tmem_d = sm.tmem_base;
 
@@ -268,20 +323,20 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const int s = kb % kStages;
         const unsigned ph = (kb / kStages) & 1;
         mbar_wait(&sm.empty_bar[s], ph ^ 1);
-        mbar_expect_tx(&sm.full_bar[s], kTileBytes + BN * BK * 4);
+        mbar_expect_tx(&sm.full_bar[s], kTileBytes + BNS * BK * 4);
         if (!AMN) tma_load_2d(sm.a[s], &map_a, &sm.full_bar[s], (kb0 + kb) * BK, m0);
         else
 #pragma unroll
           for (int j = 0; j < BM / 32; ++j) tma_load_2d(sm.a[s] + j * 1024, &map_a, &sm.full_bar[s], m0 + 32 * j, (kb0 + kb) * BK);
-        if (!BMN) tma_load_2d(sm.b[s], &map_b, &sm.full_bar[s], (kb0 + kb) * BK, n0);
+        if (!BMN) tma_load_2d(sm.b[s], &map_b, &sm.full_bar[s], (kb0 + kb) * BK, nb0);
         else
 #pragma unroll
-          for (int j = 0; j < BN / 32; ++j) tma_load_2d(sm.b[s] + j * 1024, &map_b, &sm.full_bar[s], n0 + 32 * j, (kb0 + kb) * BK);
+          for (int j = 0; j < BNS / 32; ++j) tma_load_2d(sm.b[s] + j * 1024, &map_b, &sm.full_bar[s], nb0 + 32 * j, (kb0 + kb) * BK);
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const unsigned idesc = make_idesc_tf32(BM, BN, X3 ? false : AMN, BMN);
+    if (lane == 0 && rank == 0) {
+      const unsigned idesc = make_idesc_tf32(BM * CG, BN, X3 ? false : AMN, BMN);
       for (int kb = 0; kb < kblocks; ++kb) {
         const int s = kb % kStages;
         const unsigned ph = (kb / kStages) & 1;
@@ -301,14 +356,22 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           const unsigned a_hi = tmem_d + (unsigned)(BN + s * 64), a_lo = a_hi + 32;
 #pragma unroll
           for (int k = 0; k < BK / 8; ++k) {
-            mma_tf32_ts(tmem_d, a_lo + 8 * k, bd + bstep * k, idesc, (kb | k) != 0);   // small terms first
-            mma_tf32_ts(tmem_d, a_hi + 8 * k, bl + bstep * k, idesc, 1);
-            mma_tf32_ts(tmem_d, a_hi + 8 * k, bd + bstep * k, idesc, 1);
+            if (CG == 2) {
+              mma_tf32_ts_pair(tmem_d, a_lo + 8 * k, bd + bstep * k, idesc, (kb | k) != 0);
+              mma_tf32_ts_pair(tmem_d, a_hi + 8 * k, bl + bstep * k, idesc, 1);
+              mma_tf32_ts_pair(tmem_d, a_hi + 8 * k, bd + bstep * k, idesc, 1);
+            } else {
+              mma_tf32_ts(tmem_d, a_lo + 8 * k, bd + bstep * k, idesc, (kb | k) != 0);   // small terms first
+              mma_tf32_ts(tmem_d, a_hi + 8 * k, bl + bstep * k, idesc, 1);
+              mma_tf32_ts(tmem_d, a_hi + 8 * k, bd + bstep * k, idesc, 1);
+            }
           }
         }
-        mma_commit(&sm.empty_bar[s]);          // slot free once these MMAs have read it
+        if (CG == 2) mma_commit_pair(&sm.empty_bar[s]);
+        else mma_commit(&sm.empty_bar[s]);          // slot free once these MMAs have read it
       }
-      mma_commit(&sm.tmem_full_bar);           // accumulator complete
+      if (CG == 2) mma_commit_pair(&sm.tmem_full_bar);
+      else mma_commit(&sm.tmem_full_bar);           // accumulator complete
     }
   } else {
     // epilogue warps 2..5: TMEM lane quarter = warp % 4
@@ -347,7 +410,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const float4* bh = reinterpret_cast<const float4*>(sm.b[s]);
         float4* blo = reinterpret_cast<float4*>(sm.b_lo[s]);
 #pragma unroll
-        for (int i = 0; i < BN * BK / 4 / 128; ++i) {
+        for (int i = 0; i < BNS * BK / 4 / 128; ++i) {
           const float4 w = bh[t + 128 * i];
           blo[t + 128 * i] = make_float4(tf32_lo(w.x), tf32_lo(w.y), tf32_lo(w.z), tf32_lo(w.w));
         }
@@ -361,7 +424,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // b_lo: generic-proxy writes -> tensor core reads
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.split_bar[s]);
+        if (lane == 0) {                       // the MMA issuer lives in the pair's rank-0 CTA
+          if (CG == 2 && rank != 0) mbar_arrive_remote(&sm.split_bar[s], 0);
+          else mbar_arrive(&sm.split_bar[s]);
+        }
       }
     }
     mbar_wait(&sm.tmem_full_bar, 0);
@@ -528,10 +594,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(kTmemCols) : "memory");
+    if (CG == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(kTmemCols) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(kTmemCols) : "memory");
   }
 }
 

@@ -217,8 +217,9 @@ static inline bool just_written(const void* p, size_t bytes) {
   return g_written[d].lo && lo < g_written[d].hi && g_written[d].lo < lo + bytes;
 }
 
+// cluster_x > 1: thread-block clusters of (cluster_x, 1, 1) (the tcgen05 CTA pairs)
 template <typename... P, typename... A>
-static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args) {
+static inline void launch_kc(void (*kernel)(P...), int cluster_x, dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args) {
   static const bool pdl = getenv("SN_NO_PDL") == nullptr;
   {
     const int d = cur_device();
@@ -229,12 +230,27 @@ static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t 
   cfg.blockDim = block;
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  if (pdl) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = cluster_x;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = pdl ? 1 : 0;
+  cfg.numAttrs = n;
   g_launch_status = cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);
+}
+template <typename... P, typename... A>
+static inline void launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args) {
+  launch_kc(kernel, 1, grid, block, smem, st, args...);
 }
 
 // ---------------------------------------------------------------- shared launch helpers
@@ -256,6 +272,22 @@ static int launch_tc_gemm_p(const float* A, int lda, int M, const float* Bm, int
   SN_LAUNCH_CHECK();
   return 0;
 }
+// 3xTF32 on CTA pairs (cta_group::2): 256 x 256 output tile per pair, each CTA staging half of B
+template <bool AMN, bool BMN, int EPI, int OPT>
+static int launch_tc_gemm_pair(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
+                               const tc::Epilogue& ep, cudaStream_t st) {
+  CUtensorMap ma, mb;
+  if (AMN ? tc::make_map(&ma, A, R, M, lda, 32, true) : tc::make_map(&ma, A, M, R, lda, tc::BM)) return 1;
+  if (BMN ? tc::make_map(&mb, Bm, R, N, ldb, 32, true) : tc::make_map(&mb, Bm, N, R, ldb, 128)) return 1;
+  auto kern = tc::gemm_tf32_kernel<AMN, BMN, EPI, OPT, true, 256, 4, 2>;
+  constexpr size_t smem = tc::smem_bytes<true, 128, 4>();
+  if (set_smem(kern, smem)) return 1;
+  const int kblocks = ceil_div(R, tc::BK);
+  dim3 grid(2 * ceil_div(M, 256), ceil_div(N, 256), 1);
+  launch_kc(kern, 2, grid, dim3(tc::kThreads), smem, st, ma, mb, M, N, R, C, ldc, ep, kblocks, (size_t)0);
+  SN_LAUNCH_CHECK();
+  return 0;
+}
 // precision 1 = TF32 (one pass), anything else that reaches here = 3xTF32 (fp32-accurate)
 template <bool AMN, bool BMN, int EPI, int OPT>
 static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
@@ -272,6 +304,16 @@ static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int l
     static const bool deep = getenv("SN_DW_STAGES") && atoi(getenv("SN_DW_STAGES")) == 4;
     if (!deep) return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128, 2>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
   } else {
+    // CTA pairs (256 x 256 per pair) when whole waves of them cost less than whole waves of single
+    // 128 x 128 tiles: measured per k block of a wave 1.32 us against 0.76 us for a quarter of the
+    // work (H 8192, batch 1024 and 4096; profiles/r2y_gemm_breakdown_pairs.txt).  SN_X3_PAIR=1 forces
+    // pairs, 0 disables them.
+    static const int pair = getenv("SN_X3_PAIR") ? atoi(getenv("SN_X3_PAIR")) : -1;
+    const long long pair_ctas = 2LL * ceil_div(M, 256) * ceil_div(N, 256);
+    const long long single_ctas = (long long)ceil_div(M, tc::BM) * ceil_div(N, 128);
+    const double cost_pair = 1.32 * (double)((pair_ctas + 147) / 148), cost_single = 0.76 * (double)((single_ctas + 147) / 148);
+    if (splits <= 1 && (pair == 1 || (pair < 0 && cost_pair < cost_single)))
+      return launch_tc_gemm_pair<AMN, BMN, EPI, OPT>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
     // the same pairing pays for the other forms once the grid is several waves deep (batch 4096, H 8192:
     // 186 -> 220 TFLOP/s); on a grid of one or two waves it only halves the SMs in use
     static const int force = getenv("SN_X3_STAGES") ? atoi(getenv("SN_X3_STAGES")) : 0;

@@ -4,6 +4,8 @@ Tolerance: BASELINE.json asks for logits/losses within 1e-4 relative per step; m
 norm-wise, ||cuda - ref||_F / ||ref||_F <= 1e-4 (per-element relative error is
 ill-posed, fp32 itself misses it near zero).  Integer results (eval counters) are exact.
 """
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -14,6 +16,7 @@ from tests.helpers import check_adam_weights, check_grad_through_relu, check_sum
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-4
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 A_SHAPES = [(32, 1, 3, 3), (32,)]
 B_SHAPES = [(5000, 5408), (5000,), (1000, 5000), (1000,), (100, 1000), (100,)]
@@ -418,6 +421,21 @@ def test_general_batch_path_matches_oracle(eng, mode, width):
         _general_batch_body(eng, mode, width)
     finally:
         eng.set_matmul_precision(0)
+
+
+def test_general_batch_path_on_cta_pairs():
+    """The same oracle check with every unsplit 3xTF32 forward / input-gradient GEMM forced onto CTA
+    pairs (tcgen05 cta_group::2, 256 x 256 per pair): SN_X3_PAIR is read once per process, so this
+    runs in a child."""
+    import subprocess
+    import sys
+    env = dict(os.environ, SN_X3_PAIR="1")
+    code = ("import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+            "import tests.test_gpu_kernels as t\n"
+            "from splitlearning_b200 import engine as E\n"
+            "t._general_batch_body(E, 0, 256); t._general_batch_body(E, 0, 1024); print('PAIR_OK')\n") % (ROOT, os.path.join(ROOT, "tests"))
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "PAIR_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 def _general_batch_body(eng, mode, width):

@@ -247,6 +247,27 @@ __device__ __forceinline__ void mma_tf32_ts_pair(unsigned tmem_d, unsigned tmem_
       "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0u)
       : "memory");
 }
+__device__ __forceinline__ void mma_tf32_ss_pair(unsigned tmem_d, unsigned long long adesc, unsigned long long bdesc, unsigned idesc,
+                                                 unsigned accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0u)
+      : "memory");
+}
+// TMA load whose completion bytes are counted on the barrier at this offset in the pair's rank-0 CTA
+// (bit 24 of a shared::cluster address selects the CTA of the pair): the MMA issuer there waits for
+// the operands of both CTAs on one barrier.  Source: this GPU's memory only.
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, unsigned long long* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+      : "memory");
+}
 // completion of the pair's MMAs so far -> one arrival on the barrier at this offset in BOTH CTAs
 __device__ __forceinline__ void mma_commit_pair(unsigned long long* bar) {
   asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
@@ -267,7 +288,7 @@ __global__ void __launch_bounds__(kThreads, ((X3 && STG > 2) || BN == 256) ? 1 :
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
                  int K, float* __restrict__ C, int ldc, Epilogue ep, int kb_per_split, size_t split_stride) {
   extern __shared__ unsigned char smem_raw[];
-  static_assert(CG == 1 || (CG == 2 && X3 && BN == 256), "CTA pairs: 3xTF32, 256-wide accumulator");
+  static_assert(CG == 1 || (CG == 2 && BN == 256), "CTA pairs: 256-wide accumulator");
   constexpr int BNS = BN / CG;                      // columns of B staged by this CTA
   using Smem = SmemT<X3, BNS, STG>;
   constexpr int kStages = Smem::kStages;
@@ -323,15 +344,23 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const int s = kb % kStages;
         const unsigned ph = (kb / kStages) & 1;
         mbar_wait(&sm.empty_bar[s], ph ^ 1);
-        mbar_expect_tx(&sm.full_bar[s], kTileBytes + BNS * BK * 4);
-        if (!AMN) tma_load_2d(sm.a[s], &map_a, &sm.full_bar[s], (kb0 + kb) * BK, m0);
+        // one-pass pairs: the operands of both CTAs are counted on the rank-0 CTA's barrier (its MMA
+        // thread is their only consumer); 3xTF32: each CTA's operand warps consume their own loads
+        constexpr bool kLeaderBar = CG == 2 && !X3;
+        if (!kLeaderBar) mbar_expect_tx(&sm.full_bar[s], kTileBytes + BNS * BK * 4);
+        else if (rank == 0) mbar_expect_tx(&sm.full_bar[s], 2 * (kTileBytes + BNS * BK * 4));
+        auto load = [&](float* dst, const CUtensorMap* map, int c0, int c1) {
+          if (kLeaderBar) tma_load_2d_pair(dst, map, &sm.full_bar[s], c0, c1);
+          else tma_load_2d(dst, map, &sm.full_bar[s], c0, c1);
+        };
+        if (!AMN) load(sm.a[s], &map_a, (kb0 + kb) * BK, m0);
         else
 #pragma unroll
-          for (int j = 0; j < BM / 32; ++j) tma_load_2d(sm.a[s] + j * 1024, &map_a, &sm.full_bar[s], m0 + 32 * j, (kb0 + kb) * BK);
-        if (!BMN) tma_load_2d(sm.b[s], &map_b, &sm.full_bar[s], (kb0 + kb) * BK, nb0);
+          for (int j = 0; j < BM / 32; ++j) load(sm.a[s] + j * 1024, &map_a, m0 + 32 * j, (kb0 + kb) * BK);
+        if (!BMN) load(sm.b[s], &map_b, (kb0 + kb) * BK, nb0);
         else
 #pragma unroll
-          for (int j = 0; j < BNS / 32; ++j) tma_load_2d(sm.b[s] + j * 1024, &map_b, &sm.full_bar[s], nb0 + 32 * j, (kb0 + kb) * BK);
+          for (int j = 0; j < BNS / 32; ++j) load(sm.b[s] + j * 1024, &map_b, nb0 + 32 * j, (kb0 + kb) * BK);
       }
     }
   } else if (warp == 1) {
@@ -349,8 +378,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if (!X3) {
           const unsigned long long ad = AMN ? make_desc_mnmajor_sw128(sm.a[s]) : make_desc_kmajor_sw128(sm.a[s]);
 #pragma unroll
-          for (int k = 0; k < BK / 8; ++k)
-            mma_tf32(tmem_d, ad + astep * k, bd + bstep * k, idesc, (kb | k) != 0);
+          for (int k = 0; k < BK / 8; ++k) {
+            if (CG == 2) mma_tf32_ss_pair(tmem_d, ad + astep * k, bd + bstep * k, idesc, (kb | k) != 0);
+            else mma_tf32(tmem_d, ad + astep * k, bd + bstep * k, idesc, (kb | k) != 0);
+          }
         } else {
           const unsigned long long bl = BMN ? make_desc_mnmajor_sw128(sm.b_lo[s]) : make_desc_kmajor_sw128(sm.b_lo[s]);
           const unsigned a_hi = tmem_d + (unsigned)(BN + s * 64), a_lo = a_hi + 32;

@@ -272,15 +272,17 @@ static int launch_tc_gemm_p(const float* A, int lda, int M, const float* Bm, int
   SN_LAUNCH_CHECK();
   return 0;
 }
-// 3xTF32 on CTA pairs (cta_group::2): 256 x 256 output tile per pair, each CTA staging half of B
-template <bool AMN, bool BMN, int EPI, int OPT>
+// CTA pairs (cta_group::2): 256 x 256 output tile per pair, each CTA staging half of B.  3xTF32: A through
+// tensor memory, 4-deep ring; one-pass TF32: both operands from shared memory, 6-deep ring.
+template <bool AMN, bool BMN, int EPI, int OPT, bool X3>
 static int launch_tc_gemm_pair(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
                                const tc::Epilogue& ep, cudaStream_t st) {
   CUtensorMap ma, mb;
   if (AMN ? tc::make_map(&ma, A, R, M, lda, 32, true) : tc::make_map(&ma, A, M, R, lda, tc::BM)) return 1;
   if (BMN ? tc::make_map(&mb, Bm, R, N, ldb, 32, true) : tc::make_map(&mb, Bm, N, R, ldb, 128)) return 1;
-  auto kern = tc::gemm_tf32_kernel<AMN, BMN, EPI, OPT, true, 256, 4, 2>;
-  constexpr size_t smem = tc::smem_bytes<true, 128, 4>();
+  constexpr int STG = X3 ? 4 : 6;
+  auto kern = tc::gemm_tf32_kernel<AMN, BMN, EPI, OPT, X3, 256, STG, 2>;
+  constexpr size_t smem = tc::smem_bytes<X3, 128, STG>();
   if (set_smem(kern, smem)) return 1;
   const int kblocks = ceil_div(R, tc::BK);
   dim3 grid(2 * ceil_div(M, 256), ceil_div(N, 256), 1);
@@ -293,6 +295,10 @@ template <bool AMN, bool BMN, int EPI, int OPT>
 static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
                           const tc::Epilogue& ep, cudaStream_t st, int splits = 1, size_t split_stride = 0) {
   if (g_matmul_precision.load() == 1) {
+    // CTA pairs once a wave of them exists (SN_TF32_PAIR=0 disables, 1 forces)
+    static const int tpair = getenv("SN_TF32_PAIR") ? atoi(getenv("SN_TF32_PAIR")) : -1;
+    if (splits <= 1 && (tpair == 1 || (tpair < 0 && 2LL * ceil_div(M, 256) * ceil_div(N, 256) >= 148 && R >= 256)))
+      return launch_tc_gemm_pair<AMN, BMN, EPI, OPT, false>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
     // wide tiles once there is enough work to fill the SMs with them (SN_TC_BN=128 forces narrow)
     static const bool wide_ok = !(getenv("SN_TC_BN") && atoi(getenv("SN_TC_BN")) == 128);
     if (wide_ok && (long long)ceil_div(N, 256) * ceil_div(M, tc::BM) >= 148 && R >= 256)
@@ -313,7 +319,7 @@ static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int l
     const long long single_ctas = (long long)ceil_div(M, tc::BM) * ceil_div(N, 128);
     const double cost_pair = 1.32 * (double)((pair_ctas + 147) / 148), cost_single = 0.76 * (double)((single_ctas + 147) / 148);
     if (splits <= 1 && (pair == 1 || (pair < 0 && cost_pair < cost_single)))
-      return launch_tc_gemm_pair<AMN, BMN, EPI, OPT>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
+      return launch_tc_gemm_pair<AMN, BMN, EPI, OPT, true>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
     // the same pairing pays for the other forms once the grid is several waves deep (batch 4096, H 8192:
     // 186 -> 220 TFLOP/s); on a grid of one or two waves it only halves the SMs in use
     static const int force = getenv("SN_X3_STAGES") ? atoi(getenv("SN_X3_STAGES")) : 0;

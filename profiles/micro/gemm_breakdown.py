@@ -15,7 +15,8 @@ dev = torch.device("cuda", 0)
 g = torch.Generator().manual_seed(1)
 Ws = [(torch.randn(dims[i + 1], dims[i], generator=g) / dims[i] ** 0.5).to(dev) for i in range(3)]
 bs = [torch.zeros(dims[i + 1], device=dev) for i in range(3)]
-bob = E.BobEngine(dims, Ws, bs, optimizer=E.SN_OPT_SGD_MOMENTUM, lr=1e-4, momentum=0.9, max_batch=B)
+bob = E.BobEngine(dims, Ws, bs, optimizer=E.SN_OPT_SGD_MOMENTUM, lr=1e-4, momentum=0.9, max_batch=B,
+                  dropout_p=float(os.environ.get("DROPOUT", "0.5")))
 x = (torch.rand(B, 5408, device=dev) * 100) * (torch.rand(B, 5408, device=dev) < 0.6)
 y = torch.randint(0, 10, (B,), device=dev)
 E.set_matmul_precision(mode)

@@ -203,13 +203,17 @@ __device__ __forceinline__ uint4 philox4x32(uint4 ctr, uint2 key) {
   }
   return ctr;
 }
+// the four 32-bit words that decide elements 4*idx4 .. 4*idx4+3 of dropout layer `layer` at step `offset`
+__device__ __forceinline__ uint4 philox_words(uint64_t seed, uint64_t offset, int layer, uint64_t idx4) {
+  uint4 c = make_uint4((uint32_t)idx4, (uint32_t)(idx4 >> 32), (uint32_t)offset, ((uint32_t)(offset >> 32) << 4) | (uint32_t)layer);
+  return philox4x32(c, make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+}
+__device__ __forceinline__ bool philox_word_keeps(uint32_t v, float keep_prob) { return (v >> 8) * (1.0f / 16777216.0f) < keep_prob; }
 // keep-decision for element `idx` of dropout layer `layer` at step `offset`
 __device__ __forceinline__ bool philox_keep(uint64_t seed, uint64_t offset, int layer, uint64_t idx, float keep_prob) {
-  uint4 c = make_uint4((uint32_t)(idx >> 2), (uint32_t)(idx >> 34), (uint32_t)offset,
-                       ((uint32_t)(offset >> 32) << 4) | (uint32_t)layer);
-  uint4 r = philox4x32(c, make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+  uint4 r = philox_words(seed, offset, layer, idx >> 2);
   uint32_t v = (idx & 3) == 0 ? r.x : (idx & 3) == 1 ? r.y : (idx & 3) == 2 ? r.z : r.w;
-  return (v >> 8) * (1.0f / 16777216.0f) < keep_prob;
+  return philox_word_keeps(v, keep_prob);
 }
 
 }  // namespace sn

@@ -295,7 +295,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   // fp32 accumulator: 128 lanes x BN columns; X3: + per stage 32 hi and 32 lo columns of the A operand
   constexpr int kTmemCols = !X3 ? BN : (BN + kStages * 64 <= 256 ? 256 : 512);
   static_assert(!X3 || BN + kStages * 64 <= 512, "A operand buffers do not fit tensor memory");
-  Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  // 1 KB alignment by pointer arithmetic on the __shared__ array (an integer round trip would turn every
+  // access below into a generic load/store)
+  Smem& sm = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned rank = CG == 2 ? cluster_ctarank() : 0u;
   const int m0 = (CG == 2 ? blockIdx.x : blockIdx.y) * BM, n0 = (CG == 2 ? blockIdx.y : blockIdx.x) * BN;
@@ -595,6 +597,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
               }
             }
           }
+        } else if (EPI == EPI_FWD && ep.keep_prob < 1.f && (N & 3) == 0) {
+          // handled below: every lane takes part (the Philox words are shared inside quads of lanes)
         } else {
 #pragma unroll 4
           for (int rr = 0; rr < 32; ++rr) {
@@ -610,6 +614,35 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
               if (ep.out2) ep.out2[idx] = v;
             } else {
               C[(size_t)row * ldc + n] = v;
+            }
+          }
+        }
+      }
+      if (EPI == EPI_FWD && !has_side && ep.keep_prob < 1.f && (N & 3) == 0) {
+        // Philox dropout: one Philox4x32-10 decides four consecutive elements of a row, i.e. the four
+        // columns of a quad of lanes.  Lane j of a quad evaluates it for row 4t + j, and four xor-shuffles
+        // hand every lane the word of its own column for each of the four rows (per element the Philox
+        // cost the epilogue 27 us per 256 x 256 tile against 47 us of main loop in one-pass TF32).
+        const float bias_v = (ep.bias && n < N) ? ep.bias[n] : 0.f;
+        const int j = lane & 3;
+        uint4 w[8];                                                  // eight independent Philox chains in flight
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+          w[t] = philox_words(ep.seed, ep.offset, ep.layer, ((size_t)(m0 + q * 32 + 4 * t + j) * N + (n & ~3)) >> 2);
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+#pragma unroll
+          for (int sft = 0; sft < 4; ++sft) {
+            const int k = j ^ sft;                                   // word this lane gives away = column of its partner
+            const uint32_t lo = (k & 1) ? w[t].y : w[t].x, hi = (k & 1) ? w[t].w : w[t].z;
+            const uint32_t got = __shfl_xor_sync(0xffffffffu, (k & 2) ? hi : lo, sft);   // partner's word for MY column, row 4t + k
+            const int rr = 4 * t + k, row = m0 + q * 32 + rr;
+            float v = tile[rr * 33 + lane] + bias_v;
+            if (ep.relu) v = fmaxf(v, 0.f);
+            v = philox_word_keeps(got, ep.keep_prob) ? v * ep.scale : 0.f;
+            if (n < N && row < M) {
+              C[(size_t)row * ldc + n] = v;
+              if (ep.out2) ep.out2[(size_t)row * N + n] = v;
             }
           }
         }
@@ -699,7 +732,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 skinny_fwd_x3_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x, int N, int K,
                      int B, float* __restrict__ P, int Bpad, int qmax, int prefetch_early, int l2_keep_w) {
   extern __shared__ unsigned char smem_raw[];
-  SkSmem& sm = *reinterpret_cast<SkSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  SkSmem& sm = *reinterpret_cast<SkSmem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long KB = (K + BK - 1) / BK, RT = (N + BM - 1) / BM, U = KB * RT, G = gridDim.x;
   const long long u0 = (long long)blockIdx.x * U / G, u1 = (long long)(blockIdx.x + 1) * U / G;

@@ -733,3 +733,32 @@ def _mid_batch_body(eng, B):
         for p_ref, p, p0 in zip(b, gp, w_old):
             assert rel_err(p.cpu(), p_ref) <= 1e-5
             assert rel_err(p.cpu() - p0, p_ref - p0) <= TOL          # the applied step itself
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_philox_dropout_is_the_same_function_on_every_forward_path(eng, mode):
+    """The keep decision of an element depends on (seed, step, layer, element index) only: a 96-row
+    training-mode forward through the tcgen05 GEMMs (Philox words shared inside quads of lanes in the
+    epilogue; also split along K where the output has few tiles) keeps exactly the elements the fp32
+    weight-stream kernels keep (row tiles of 16, one Philox evaluation per element), for hidden widths
+    that are and are not whole 128-column tiles."""
+    rng = np.random.RandomState(11)
+    dims = [5408, 320, 200, 100]
+    shapes = [(320, 5408), (320,), (200, 320), (200,), (100, 200), (100,)]
+    w = [cu(a) for a in seeded_weights(shapes, 91)]
+    # positive biases keep most pre-activations away from the ReLU kink, so zeros mark dropped elements
+    w[1] += 3.0
+    w[3] += 3.0
+    B = 96
+    x = cu((rng.rand(B, 5408) * 2).astype(np.float32))
+    a = eng.BobEngine(dims, w[0::2], w[1::2], optimizer=eng.SN_OPT_NONE, max_batch=B, dropout_p=0.5, relu_last=True)
+    b = eng.BobEngine(dims, w[0::2], w[1::2], optimizer=eng.SN_OPT_NONE, max_batch=B, dropout_p=0.5, relu_last=True)
+    assert a.set_stream_rows(B) >= B                     # a: fp32 weight-stream kernels; b: GEMMs (B > 64)
+    eng.set_matmul_precision(mode)
+    try:
+        for off in (0, 5):
+            ya = a.forward(x, train_mode=True, seed=1234, offset=off).cpu()
+            yb = b.forward(x, train_mode=True, seed=1234, offset=off).cpu()
+            assert rel_err(yb, ya) <= (TOL if mode == 0 else 5e-3)
+    finally:
+        eng.set_matmul_precision(0)

@@ -69,6 +69,11 @@ def precision_name(B, mode):
     return "fp32-forward+3xtf32-backward" if B <= 64 else "3xtf32-tcgen05"
 
 
+def ceiling_frac(B, mode, tfl, tf32_peak):
+    """3xTF32 executes three TF32 products per useful one: its ceiling is a third of the TF32 peak."""
+    return round(tfl / (tf32_peak / 3.0), 4) if (mode == 0 and B > 64) else None
+
+
 def main():
     quick = "--quick" in sys.argv
     hbm, tf32_peak, src = peaks()
@@ -92,6 +97,7 @@ def main():
                 print(json.dumps({"B": B, "H": H, "dims": dims, "precision": prec, "credited": mode == 0,
                                   "ms_per_step": round(ms, 4), "samples_per_s": round(B / (ms * 1e-3), 1),
                                   "tflops": round(tfl, 2), "frac_tf32_peak": round(tfl / tf32_peak, 4),
+                                  "frac_3xtf32_ceiling": ceiling_frac(B, mode, tfl, tf32_peak),
                                   "weight_stream_gbs": round(gbs, 1), "frac_hbm": round(gbs / hbm, 4),
                                   "peaks": src, "loss": loss}), flush=True)
                 torch.cuda.empty_cache()
@@ -106,7 +112,8 @@ def point_record(B, H, mode, steps=None):
     gbs = 16.0 * pw / (ms * 1e-3) / 1e9
     return {"B": B, "H": H, "precision": precision_name(B, mode),
             "credited": mode == 0, "ms_per_step": round(ms, 4), "samples_per_s": round(B / (ms * 1e-3), 1),
-            "tflops": round(tfl, 2), "frac_tf32_peak": round(tfl / tf32_peak, 4), "frac_hbm": round(gbs / hbm, 4)}
+            "tflops": round(tfl, 2), "frac_tf32_peak": round(tfl / tf32_peak, 4),
+            "frac_3xtf32_ceiling": ceiling_frac(B, mode, tfl, tf32_peak), "frac_hbm": round(gbs / hbm, 4)}
 
 
 def main_tp():

@@ -39,16 +39,16 @@ enum { SN_OPT_NONE = 0, SN_OPT_SGD_MOMENTUM = 1, SN_OPT_ADAM = 2 };
 
 int sn_version(void);
 const char* sn_last_error(void);
-/* Arithmetic of the LARGE-batch (B > 64) matrix products; process-wide.  All three run on the
- * same tcgen05 kernel except mode 2.
+/* Arithmetic of the tensor-core matrix products (forward of batches > 64, backward of batches > 16);
+ * process-wide.  All three run on the same tcgen05 kernel except mode 2.
  *   0 (default) 3xTF32: each fp32 operand is split into hi + lo TF32 halves on the fly and the
  *               product is formed as hi*hi + lo*hi + hi*lo with fp32 accumulation: ~1e-5 relative,
  *               inside the 1e-4 parity bound, at one third of the TF32 rate.
  *   1           TF32, one pass: ~5e-4 relative on this model's logits, outside the parity bound;
  *               for throughput runs (BASELINE.json config 5 sweep).
  *   2           plain fp32 FMA (a simple tiled SGEMM): slow, kept as an independent check.
- * Batches <= 64 always use the fp32 weight-streaming kernels, which are HBM-bound and gain
- * nothing from tensor cores.  (No counterpart in the reference: one CPU fp32 path.) */
+ * The forward of batches <= 64 and the whole step of batches <= 16 always use the fp32
+ * weight-streaming kernels.  (No counterpart in the reference: one CPU fp32 path.) */
 int sn_set_matmul_precision(int mode);
 int sn_get_matmul_precision(void);
 /* Route the weight stream of big layers at batch <= 16 through the tensor cores (1) or the CUDA

@@ -11,21 +11,24 @@
 //                                                 updated in place; dW is never written to memory)
 //   so no operand is ever transposed or copied: nn.Linear's [out,in] weights serve all three.
 //
-// One 128x128 output tile per CTA, warp-specialised:
+// One 128x128 output tile per CTA (or, on CTA pairs, one 256x256 tile per pair: see CG below),
+// warp-specialised:
 //   warp 0      TMA producer: cp.async.bulk.tensor 2-D loads of 128x32-float tiles (128-byte rows,
 //               SWIZZLE_128B) of A and B into a kStages-deep shared-memory ring, mbarrier complete_tx
-//   warp 1      TMEM allocation + single-thread tcgen05.mma.kind::tf32 issue (M=128,N=128,K=8 per
-//               instruction, fp32 accumulation in TMEM), tcgen05.commit releases ring slots
-//   warps 2..5  epilogue: tcgen05.ld the accumulator (32 lanes x 32 columns per instruction),
-//               transpose through shared memory so every global access is a contiguous row
-//               segment, then bias/ReLU/dropout, the ReLU/dropout gate, or the optimizer update
+//   warp 1      TMEM allocation + single-thread tcgen05.mma.kind::tf32 issue (K=8 per instruction,
+//               fp32 accumulation in TMEM), tcgen05.commit releases ring slots
+//   warps 2..5  3xTF32: operand warps during the main loop (A rows and their lo twins -> tensor
+//               memory, B's lo twin -> shared memory); then the epilogue: tcgen05.ld the accumulator
+//               (32 lanes x 32 columns per instruction), through shared memory so every global access
+//               is a contiguous row segment, then bias/ReLU/dropout, the ReLU/dropout gate, or the
+//               optimizer update streamed through the idle operand ring
 // Out-of-range rows/columns/k are zero-filled by TMA and masked in the epilogue, so any M, N and
-// any K that is a multiple of 4 work.
+// any K that is a multiple of 4 work.  Split-K (grid.z) writes raw partial tiles for the host to reduce.
 //
 // Precision: kind::tf32 reads the fp32 bit patterns and uses the top 19 bits (10-bit mantissa).
-// That is ~5e-4 relative on the logits of this model - outside the 1e-4 parity
-// bound - so this path is the PERF mode for large batches (sn_set_matmul_precision(1)); the fp32
-// path stays the default.
+// One pass is ~5e-4 relative on the logits of this model - outside the 1e-4 parity
+// bound - so one-pass TF32 is the PERF mode (sn_set_matmul_precision(1)); the default is 3xTF32
+// (X3 below), which is fp32-accurate.
 #pragma once
 #include <cuda.h>
 
@@ -35,8 +38,9 @@ namespace sn {
 namespace tc {
 
 constexpr int BM = 128, BK = 32;                    // BK floats = 128 bytes = one swizzle row
-// tile width BN is a template parameter: 128 (3 stages, two CTAs per SM: one's epilogue overlaps the
-// other's main loop) or 256 (4 stages, one CTA per SM, half the A traffic per flop)
+// accumulator width BN is a template parameter: 128 (one-pass: 3 stages, two CTAs per SM, one's epilogue
+// overlaps the other's main loop; 3xTF32: 4 stages, or 2 with two CTAs per SM) or 256 (one-pass, one CTA
+// per SM, half the A traffic per flop; and the CTA-pair forms, whose CTAs stage 128 columns each)
 __host__ __device__ constexpr int stages_for(int bn, bool x3) { return (x3 || bn == 256) ? 4 : 3; }
 constexpr int kTileBytes = BM * BK * 4;             // 16 KB per A tile per stage
 constexpr int kThreads = 192;

@@ -670,6 +670,31 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   }
 }
 
+// W, state <- optimizer(W, sum_s P[s]) - the reduction behind a split-K dW GEMM (n4 = elements / 4; slices
+// are dense slabs `slab` floats apart; fixed add order)
+template <int OPT>
+__global__ void splitk_opt_kernel(float* __restrict__ W, const float* __restrict__ P, int nsplit, size_t slab, float* __restrict__ s1,
+                                  float* __restrict__ s2, size_t n4, OptParams op) {
+  pdl_wait();
+  pdl_launch();
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    float4 g = __ldcg(reinterpret_cast<const float4*>(P) + i);
+    for (int s = 1; s < nsplit; ++s) {
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(P + s * slab) + i);
+      g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+    }
+    float4 w = reinterpret_cast<float4*>(W)[i], a = reinterpret_cast<float4*>(s1)[i];
+    float4 b = (OPT == 2) ? reinterpret_cast<float4*>(s2)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    opt_update<OPT>(op, w.x, g.x, a.x, b.x);
+    opt_update<OPT>(op, w.y, g.y, a.y, b.y);
+    opt_update<OPT>(op, w.z, g.z, a.z, b.z);
+    opt_update<OPT>(op, w.w, g.w, a.w, b.w);
+    reinterpret_cast<float4*>(W)[i] = w;
+    reinterpret_cast<float4*>(s1)[i] = a;
+    if (OPT == 2) reinterpret_cast<float4*>(s2)[i] = b;
+  }
+}
+
 // =====================================================================================
 // Skinny forward on tensor cores: P[q][b][n] = partial sums of X[b][:] . W[n][:] for B <= 16.
 //

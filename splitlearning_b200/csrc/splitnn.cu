@@ -1218,7 +1218,22 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
       tc::Epilogue eu{};
       eu.s1 = s.s1[2 * l]; eu.s2 = s.s2[2 * l]; eu.op = op;
       cudaEvent_t pe = h->prof.begin(st, 1, l);
-      int rc = launch_tc_gemm<true, true, tc::EPI_UPDATE, OPT>(dZ, N, N, A, K, K, B, h->W[l], K, eu, st);
+      // a narrow layer at a huge batch (e.g. [48 x 256] at 65536 rows: 2 tiles, 2048 k blocks): split the
+      // reduction, then reduce the slices and apply the optimizer in one element-wise pass
+      const int splits_w = h->SK ? plan_splitk(N, K, B, h->sms, h->SK_floats) : 1;
+      int rc;
+      if (splits_w > 1) {
+        tc::Epilogue raw{};
+        rc = launch_tc_gemm<true, true, tc::EPI_GATE, 0>(dZ, N, N, A, K, K, B, h->SK, K, raw, st, splits_w, (size_t)N * K);
+        if (!rc) {
+          const int nsl = ceil_div(ceil_div(B, tc::BK), ceil_div(ceil_div(B, tc::BK), splits_w));
+          launch_k(tc::splitk_opt_kernel<OPT>, dim3(ew_grid((size_t)N * K / 4, h->sms)), dim3(256), 0, st, h->W[l], (const float*)h->SK, nsl,
+                   (size_t)N * K, s.s1[2 * l], s.s2[2 * l], (size_t)N * K / 4, op);
+          SN_LAUNCH_CHECK();
+        }
+      } else {
+        rc = launch_tc_gemm<true, true, tc::EPI_UPDATE, OPT>(dZ, N, N, A, K, K, B, h->W[l], K, eu, st);
+      }
       Profiler::end(pe, st);
       if (rc) return rc;
       mark_written(h->W[l], wbytes);

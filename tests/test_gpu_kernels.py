@@ -762,3 +762,47 @@ def test_philox_dropout_is_the_same_function_on_every_forward_path(eng, mode):
             assert rel_err(yb, ya) <= (TOL if mode == 0 else 5e-3)
     finally:
         eng.set_matmul_precision(0)
+
+
+_SPLITK_CHILD = r"""
+import sys
+sys.path.insert(0, %r)
+import numpy as np, torch
+from splitlearning_b200 import engine as E
+from tests.helpers import seeded_weights, seeded_masks
+rng = np.random.RandomState(3)
+dims = [5408, 128, 104, 100]
+shapes = [(128, 5408), (128,), (104, 128), (104,), (100, 104), (100,)]
+gp = [torch.from_numpy(a.copy()).cuda() for a in seeded_weights(shapes, 44)]
+B = 1200
+bob = E.BobEngine(dims, gp[0::2], gp[1::2], optimizer=E.SN_OPT_SGD_MOMENTUM, lr=1e-3, momentum=0.9, max_batch=B)
+act = torch.from_numpy((rng.rand(B, 5408) * 4 * (rng.rand(B, 5408) < 0.6)).astype(np.float32)).cuda()
+y = torch.from_numpy(rng.randint(0, 10, size=B).astype(np.int64)).cuda()
+masks = [torch.from_numpy(m).cuda() for m in seeded_masks(B, (128, 104), 9)]
+for step in range(2):
+    loss, cut, _ = bob.train_step(act, y, masks=masks)
+torch.cuda.synchronize()
+np.savez(sys.argv[1], loss=loss.cpu().numpy(), cut=cut.cpu().numpy(), **{"p%%d" %% i: p.cpu().numpy() for i, p in enumerate(gp)})
+"""
+
+
+def test_split_k_gemms_equal_the_unsplit_ones(tmp_path):
+    """Narrow layers at a large batch split the reduction of all three GEMM forms (forward, input
+    gradient, dW + optimizer through a slice buffer and `splitk_opt_kernel`): two SGD-momentum steps
+    with and without the split (SN_NO_SPLITK=1, read once per process, hence children) agree to the
+    summation-order level."""
+    import subprocess
+    import sys
+    out = {}
+    for tag, env in (("split", {}), ("whole", {"SN_NO_SPLITK": "1"})):
+        path = str(tmp_path / (tag + ".npz"))
+        r = subprocess.run([sys.executable, "-c", _SPLITK_CHILD % ROOT, path], env=dict(os.environ, **env), capture_output=True,
+                           text=True, timeout=300)
+        assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+        out[tag] = np.load(path)
+    a, b = out["split"], out["whole"]
+    assert abs(float(a["loss"]) - float(b["loss"])) <= 1e-5 * abs(float(b["loss"]))
+    assert rel_err(a["cut"], b["cut"]) <= 1e-4
+    w0 = seeded_weights([(128, 5408), (128,), (104, 128), (104,), (100, 104), (100,)], 44)
+    for i in range(6):
+        assert rel_err(a["p%d" % i] - w0[i], b["p%d" % i] - w0[i]) <= 1e-4, i

@@ -670,6 +670,44 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   }
 }
 
+// Bias gradient of a large batch in two fixed-order stages (the one-thread-per-column loop over all rows
+// costs 3.7 ms at 65536 rows when the layer is 256 wide: one CTA): part[c][n] = sum of rows
+// [c*rpc, (c+1)*rpc) of column n - block (32 columns, 8 row lanes), lanes combined in order - then one
+// thread per column adds the chunks in order and applies the optimizer.
+__global__ void bias_grad_partial_kernel(const float* __restrict__ dZ, int ldz, int B, int N, int rpc, float* __restrict__ part) {
+  pdl_wait();
+  pdl_launch();
+  __shared__ float red[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int n = blockIdx.x * 32 + tx, r0 = blockIdx.y * rpc, r1 = min(B, r0 + rpc);
+  float acc = 0.f;
+  if (n < N)
+    for (int b = r0 + ty; b < r1; b += 8) acc += __ldg(dZ + (size_t)b * ldz + n);
+  red[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && n < N) {
+    float s = red[0][tx];
+#pragma unroll
+    for (int j = 1; j < 8; ++j) s += red[j][tx];
+    part[(size_t)blockIdx.y * N + n] = s;
+  }
+}
+template <int OPT>
+__global__ void bias_opt_from_partials_kernel(const float* __restrict__ part, int chunks, int N, float* __restrict__ bias,
+                                              float* __restrict__ s1, float* __restrict__ s2, OptParams op) {
+  pdl_wait();
+  pdl_launch();
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float db = 0.f;
+  for (int c = 0; c < chunks; ++c) db += __ldcg(part + (size_t)c * N + n);
+  float pv = bias[n], a = s1[n], q = (OPT == 2) ? s2[n] : 0.f;
+  opt_update<OPT>(op, pv, db, a, q);
+  bias[n] = pv;
+  s1[n] = a;
+  if (OPT == 2) s2[n] = q;
+}
+
 // W, state <- optimizer(W, sum_s P[s]) - the reduction behind a split-K dW GEMM (n4 = elements / 4; slices
 // are dense slabs `slab` floats apart; fixed add order)
 template <int OPT>

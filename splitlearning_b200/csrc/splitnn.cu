@@ -516,6 +516,7 @@ struct sn_bob {
   float* PA = nullptr;         // backward dA partials
   float* SK = nullptr;         // split-K partial tiles of the tcgen05 GEMMs (max_batch > 16)
   size_t SK_floats = 0;
+  float* BG = nullptr;         // bias-gradient chunk sums [<= 128 chunks][widest layer] (max_batch > 16)
   size_t PA_floats = 0;
   float* dWbuf = nullptr;      // general-batch path only (lazy)
   float* row_loss = nullptr;
@@ -846,6 +847,9 @@ int sn_bob_create(sn_bob** out, int device, const int* dims, int n_layers, int r
     // a split GEMM has at most sms / slices tiles, so sms full tiles hold any set of partials
     h->SK_floats = (size_t)h->sms * tc::BM * 128;
     if ((e = cudaMalloc(&h->SK, h->SK_floats * 4)) != cudaSuccess) return fail_free(e);
+    int widest = 0;
+    for (int l = 1; l <= n_layers; ++l) widest = std::max(widest, dims[l]);
+    if ((e = cudaMalloc(&h->BG, (size_t)129 * widest * 4)) != cudaSuccess) return fail_free(e);
   }
   h->row_loss_rows = h->Bpad;
   if ((e = cudaMalloc(&h->row_loss, (size_t)h->Bpad * 4)) != cudaSuccess) return fail_free(e);
@@ -883,6 +887,7 @@ int sn_bob_destroy(sn_bob* h) {
   cudaFree(h->P);
   cudaFree(h->PA);
   cudaFree(h->SK);
+  cudaFree(h->BG);
   cudaFree(h->dWbuf);
   cudaFree(h->PF);
   cudaFree(h->Ptail);
@@ -1212,8 +1217,16 @@ static int bob_backward_impl(sn_bob* h, int slot, const float* act, int B, float
         Profiler::end(pe, st);
         if (rc) return rc;
       }
-      launch_k(bias_grad_update_kernel<OPT>, dim3(ceil_div(N, 256)), dim3(256), 0, st, dZ, N, B, N, h->b[l],
-               s.s1[2 * l + 1], s.s2[2 * l + 1], op);
+      if (h->BG) {
+        const int rpc = std::max(64, round_up(ceil_div(B, 128), 8)), chunks = ceil_div(B, rpc);
+        launch_k(tc::bias_grad_partial_kernel, dim3(ceil_div(N, 32), chunks), dim3(256), 0, st, dZ, N, B, N, rpc, h->BG);
+        SN_LAUNCH_CHECK();
+        launch_k(tc::bias_opt_from_partials_kernel<OPT>, dim3(ceil_div(N, 256)), dim3(256), 0, st, (const float*)h->BG, chunks, N, h->b[l],
+                 s.s1[2 * l + 1], s.s2[2 * l + 1], op);
+      } else {
+        launch_k(bias_grad_update_kernel<OPT>, dim3(ceil_div(N, 256)), dim3(256), 0, st, dZ, N, B, N, h->b[l],
+                 s.s1[2 * l + 1], s.s2[2 * l + 1], op);
+      }
       SN_LAUNCH_CHECK();
       tc::Epilogue eu{};
       eu.s1 = s.s1[2 * l]; eu.s2 = s.s2[2 * l]; eu.op = op;

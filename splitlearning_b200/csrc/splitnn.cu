@@ -294,14 +294,15 @@ static int launch_tc_gemm_pair(const float* A, int lda, int M, const float* Bm, 
 template <bool AMN, bool BMN, int EPI, int OPT>
 static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int ldb, int N, int R, float* C, int ldc,
                           const tc::Epilogue& ep, cudaStream_t st, int splits = 1, size_t split_stride = 0) {
+  const long long sms = sm_count(cur_device());
   if (g_matmul_precision.load() == 1) {
     // CTA pairs once a wave of them exists (SN_TF32_PAIR=0 disables, 1 forces)
     static const int tpair = getenv("SN_TF32_PAIR") ? atoi(getenv("SN_TF32_PAIR")) : -1;
-    if (splits <= 1 && (tpair == 1 || (tpair < 0 && 2LL * ceil_div(M, 256) * ceil_div(N, 256) >= 148 && R >= 256)))
+    if (splits <= 1 && (tpair == 1 || (tpair < 0 && 2LL * ceil_div(M, 256) * ceil_div(N, 256) >= sms && R >= 256)))
       return launch_tc_gemm_pair<AMN, BMN, EPI, OPT, false>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
     // wide tiles once there is enough work to fill the SMs with them (SN_TC_BN=128 forces narrow)
     static const bool wide_ok = !(getenv("SN_TC_BN") && atoi(getenv("SN_TC_BN")) == 128);
-    if (wide_ok && (long long)ceil_div(N, 256) * ceil_div(M, tc::BM) >= 148 && R >= 256)
+    if (wide_ok && (long long)ceil_div(N, 256) * ceil_div(M, tc::BM) >= sms && R >= 256)
       return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false, 256>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
     return launch_tc_gemm_p<AMN, BMN, EPI, OPT, false, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
   }
@@ -317,14 +318,14 @@ static int launch_tc_gemm(const float* A, int lda, int M, const float* Bm, int l
     static const int pair = getenv("SN_X3_PAIR") ? atoi(getenv("SN_X3_PAIR")) : -1;
     const long long pair_ctas = 2LL * ceil_div(M, 256) * ceil_div(N, 256);
     const long long single_ctas = (long long)ceil_div(M, tc::BM) * ceil_div(N, 128);
-    const double cost_pair = 1.32 * (double)((pair_ctas + 147) / 148), cost_single = 0.76 * (double)((single_ctas + 147) / 148);
+    const double cost_pair = 1.32 * (double)((pair_ctas + sms - 1) / sms), cost_single = 0.76 * (double)((single_ctas + sms - 1) / sms);
     if (splits <= 1 && (pair == 1 || (pair < 0 && cost_pair < cost_single)))
       return launch_tc_gemm_pair<AMN, BMN, EPI, OPT, true>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st);
     // the same pairing pays for the other forms once the grid is several waves deep (batch 4096, H 8192:
     // 186 -> 220 TFLOP/s); on a grid of one or two waves it only halves the SMs in use
     static const int force = getenv("SN_X3_STAGES") ? atoi(getenv("SN_X3_STAGES")) : 0;
     const long long ctas = (long long)ceil_div(N, 128) * ceil_div(M, tc::BM) * std::max(1, splits);
-    if (force == 2 || (force == 0 && ctas >= 4LL * 148))
+    if (force == 2 || (force == 0 && ctas >= 4 * sms))
       return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128, 2>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);
   }
   return launch_tc_gemm_p<AMN, BMN, EPI, OPT, true, 128>(A, lda, M, Bm, ldb, N, R, C, ldc, ep, st, splits, split_stride);

@@ -438,6 +438,21 @@ def test_general_batch_path_on_cta_pairs():
     assert r.returncode == 0 and "PAIR_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
+def test_large_batch_step_on_one_pass_cta_pairs():
+    """The one-pass TF32 step (forward, dX, dW + optimizer in the epilogue) with every unsplit GEMM forced
+    onto CTA pairs (SS operands, both CTAs' TMA bytes counted on the leader's barrier): same oracle
+    bounds as the single-CTA form.  SN_TF32_PAIR is read once per process, so this runs in a child."""
+    import subprocess
+    import sys
+    env = dict(os.environ, SN_TF32_PAIR="1")
+    code = ("import sys; sys.path.insert(0, %r)\n"
+            "import tests.test_gpu_kernels as t\n"
+            "from splitlearning_b200 import engine as E\n"
+            "t.test_tcgen05_large_batch_train_step(E, 'sgd'); t.test_tcgen05_large_batch_train_step(E, 'adam'); print('PAIR_OK')\n") % ROOT
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "PAIR_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
 def _general_batch_body(eng, mode, width):
     rng = np.random.RandomState(77)
     dims = [5408, width, 52, 100]

@@ -743,6 +743,13 @@ def bench_vanilla(args, B, n_alices, turn, config, peak):
     import bench as bench_mod
     run_vanilla_schedule(rank, world, bob, mine, lambda i: (xs[i % nb], ys[i % nb]), n_alices, 1, 0, bench_mod.PREHEAT, B,
                          device, None, link)
+    # A schedule that starts again at step 0 has no hand-off in front of its first step, i.e. nothing that
+    # orders its first Alice behind the previous schedule's LAST Alice on another rank: she would store
+    # her batch into Bob's one mailbox (and raise its flag) while Bob still works through the others'
+    # steps.  Drain every rank before restarting.  (timed() does the same in front of the timed steps.)
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
     run_vanilla_schedule(rank, world, bob, mine, lambda i: (xs[i % nb], ys[i % nb]), n_alices,
                          max(1, min(turn, W // (n_alices + 1))), 0, W, B, device, None, link)
     l0 = lib.sn_launch_count()

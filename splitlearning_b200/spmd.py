@@ -53,7 +53,13 @@ def run_vanilla_schedule(rank, world, bob, alices, batch_fn, n_alices, turn, fir
     a short last batch (the reference's DataLoader has no drop_last).  None = every batch has B rows,
     and a batch_fn that returns anything else is refused.
     link: a peer.PeerLink (CUDA IPC mailboxes: the kernels write straight into the consumer's GPU and
-    4-byte flags order the streams) or None for send/recv messages (NCCL; gloo in the CPU tests)."""
+    4-byte flags order the streams) or None for send/recv messages (NCCL; gloo in the CPU tests).
+
+    Calling it again on the same link: inside one call an Alice on another rank is ordered behind her
+    predecessor by the weight hand-off in front of her turn.  A call whose FIRST step has no hand-off
+    in front of it (step 0, or a step inside a turn) has no such edge to the previous call's last
+    Alice: drain first (`torch.cuda.synchronize(); dist.barrier()` on every rank), or her batch lands in
+    Bob's mailbox - one buffer, one flag - while Bob still works on the previous call's steps."""
     msg, act_view, lab_view = pack_message(B, device)
     cut = torch.empty(B, D0, dtype=torch.float32, device=device)
     wbuf = torch.empty(320, dtype=torch.float32, device=device)
